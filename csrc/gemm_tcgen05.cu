@@ -1,0 +1,423 @@
+// tcgen05 / TMEM / TMA GEMM with fused epilogues for the ALBERT + SwAV-head hot ops
+// (BASELINE.json north-star "no library GEMM").
+//
+//   C[M,N] = epilogue( sum_k A[m,k] * B[n,k] )        bf16 (or fp16) inputs, fp32 accumulation in TMEM
+//
+// Operand layouts (runtime flags, so one kernel serves forward, dgrad and wgrad without transposes):
+//   A K-major : stored [M,K] row-major          A MN-major : stored [K,M] row-major
+//   B K-major : stored [N,K] row-major (nn.Linear weight)   B MN-major : stored [K,N] row-major
+//
+// Structure (one persistent CTA per SM, 256 threads):
+//   warp 0      TMA producer: cp.async.bulk.tensor (SWIZZLE_128B) into a 4-stage smem ring
+//   warp 1      MMA issuer: one elected lane issues tcgen05.mma.cta_group::1.kind::f16 (128 x BN x 16),
+//               tcgen05.commit releases smem stages and publishes finished accumulators
+//   warp 2      TMEM allocator (2 accumulator stages x BN columns = up to all 512 columns)
+//   warps 4..7  epilogue: tcgen05.ld (32x32b) -> registers -> fused bias / gelu_new / gelu' / residual /
+//               scaling -> bf16 or fp32 stores, or fp32 red.add for split-K weight-gradient accumulation
+// so the epilogue of tile i overlaps the mainloop of tile i+1 (double-buffered accumulators).
+#include <cuda.h>
+#include "common.cuh"
+#include "../include/dedloc_b200.h"
+
+namespace dedloc {
+
+constexpr int kGemmThreads = 256;
+constexpr int BM = 128;
+constexpr int BK = 64;  // 64 x 2 bytes = 128 B = one SWIZZLE_128B row
+constexpr int kStagesBN256 = 4;
+constexpr int kStagesBN128 = 6;
+
+struct GemmKernelParams {
+  int M, N, K;
+  int a_mn, b_mn;       // operand majors
+  int splits;           // split-K factor (output must be an atomic-add epilogue when > 1)
+  int kb_per_split;
+  int epi;              // DEDLOC_EPI_* flags
+  int out_kind;         // 0 bf16 store, 1 fp32 store, 2 fp32 atomic add
+  int fmt;              // 1 = bf16 inputs, 0 = fp16 inputs
+  float alpha;
+  void* C;              // [M, ldc]
+  long long ldc;
+  const void* bias;     // [N], bf16 or fp32 (epi flag)
+  const void* residual; // [M, ld_res] bf16
+  long long ld_res;
+  const void* aux_in;   // [M, ld_aux] bf16: pre-activation for the gelu' epilogue
+  long long ld_aux;
+  void* pre_out;        // [M, ld_pre] bf16: pre-activation saved by the forward gelu epilogue
+  long long ld_pre;
+};
+
+template <int BN>
+struct GemmSmem {
+  static constexpr int kStages = (BN == 256) ? kStagesBN256 : kStagesBN128;
+  static constexpr int kABytes = BM * BK * 2;
+  static constexpr int kBBytes = BN * BK * 2;
+  static constexpr int kStageBytes = kABytes + kBBytes;
+  static constexpr int kBarBytes = 256;
+  static constexpr int kTotal = kStages * kStageBytes + kBarBytes + 1024;  // +1024 alignment slack
+};
+
+template <int BN>
+__global__ void __launch_bounds__(kGemmThreads, 1)
+gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b,
+                    const __grid_constant__ GemmKernelParams p) {
+  using S = GemmSmem<BN>;
+  constexpr int kStages = S::kStages;
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + kStages * S::kStageBytes);
+  uint64_t* full_bar = bars;                   // [kStages]
+  uint64_t* empty_bar = bars + kStages;        // [kStages]
+  uint64_t* tmem_full = bars + 2 * kStages;    // [2]
+  uint64_t* tmem_empty = bars + 2 * kStages + 2;  // [2]
+  uint32_t* tmem_base_slot = reinterpret_cast<uint32_t*>(bars + 2 * kStages + 4);
+
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+
+  const int m_tiles = (p.M + BM - 1) / BM;
+  const int n_tiles = (p.N + BN - 1) / BN;
+  const int kb_total = p.K / BK;
+  const int total_tiles = m_tiles * n_tiles * p.splits;
+
+  if (warp == 0 && lane == 0) {
+    tma_prefetch_desc(&tmap_a);
+    tma_prefetch_desc(&tmap_b);
+  }
+  if (warp == 1 && lane == 0) {
+    for (int s = 0; s < kStages; ++s) { mbar_init(&full_bar[s], 1); mbar_init(&empty_bar[s], 1); }
+    for (int s = 0; s < 2; ++s) { mbar_init(&tmem_full[s], 1); mbar_init(&tmem_empty[s], 4); }
+    mbar_fence_init();
+  }
+  if (warp == 2) {
+    tmem_alloc(tmem_base_slot, 2 * BN);
+    tmem_relinquish();
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_base_slot;
+
+  if (warp == 0) {
+    // ===================== TMA producer =====================
+    if (lane == 0) {
+      int stage = 0;
+      uint32_t phase = 0;
+      for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
+        const int split = tile / (m_tiles * n_tiles);
+        const int rem = tile - split * (m_tiles * n_tiles);
+        const int m0 = (rem % m_tiles) * BM;
+        const int n0 = (rem / m_tiles) * BN;
+        const int kb0 = split * p.kb_per_split;
+        const int kb1 = min(kb_total, kb0 + p.kb_per_split);
+        for (int kb = kb0; kb < kb1; ++kb) {
+          mbar_wait(&empty_bar[stage], phase ^ 1);
+          uint8_t* sa = smem + stage * S::kStageBytes;
+          uint8_t* sb = sa + S::kABytes;
+          mbar_expect_tx(&full_bar[stage], S::kStageBytes);
+          const int k0 = kb * BK;
+          if (!p.a_mn) {
+            tma_load_2d(sa, &tmap_a, &full_bar[stage], k0, m0);
+          } else {
+#pragma unroll
+            for (int i = 0; i < BM / 64; ++i)
+              tma_load_2d(sa + i * (BK * 128), &tmap_a, &full_bar[stage], m0 + 64 * i, k0);
+          }
+          if (!p.b_mn) {
+            tma_load_2d(sb, &tmap_b, &full_bar[stage], k0, n0);
+          } else {
+#pragma unroll
+            for (int i = 0; i < BN / 64; ++i)
+              tma_load_2d(sb + i * (BK * 128), &tmap_b, &full_bar[stage], n0 + 64 * i, k0);
+          }
+          if (++stage == kStages) { stage = 0; phase ^= 1; }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ===================== MMA issuer =====================
+    const uint32_t idesc = make_idesc_f16(BM, BN, p.a_mn, p.b_mn, p.fmt);
+    int stage = 0;
+    uint32_t phase = 0;
+    int acc = 0;
+    uint32_t acc_phase = 0;
+    for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
+      const int split = tile / (m_tiles * n_tiles);
+      const int kb0 = split * p.kb_per_split;
+      const int kb1 = min(kb_total, kb0 + p.kb_per_split);
+      mbar_wait(&tmem_empty[acc], acc_phase ^ 1);
+      tc_fence_after();
+      const uint32_t tmem_d = tmem_base + acc * BN;
+      for (int kb = kb0; kb < kb1; ++kb) {
+        mbar_wait(&full_bar[stage], phase);
+        tc_fence_after();
+        if (lane == 0) {
+          const uint32_t sa = smem_u32(smem + stage * S::kStageBytes);
+          const uint32_t sb = sa + S::kABytes;
+#pragma unroll
+          for (int j = 0; j < BK / 16; ++j) {
+            // K-major: 16 elements = 32 B further along the swizzled 128 B row.
+            // MN-major: 16 k-rows = 2 groups of 8 rows x 128 B = 2048 B further.
+            const uint64_t da = p.a_mn ? make_smem_desc_sw128(sa + j * 2048, BK * 128, 1024)
+                                       : make_smem_desc_sw128(sa + j * 32, 16, 1024);
+            const uint64_t db = p.b_mn ? make_smem_desc_sw128(sb + j * 2048, BK * 128, 1024)
+                                       : make_smem_desc_sw128(sb + j * 32, 16, 1024);
+            umma_f16_ss(tmem_d, da, db, idesc, (kb > kb0 || j > 0) ? 1u : 0u);
+          }
+          umma_commit(&empty_bar[stage]);                   // smem stage reusable once these MMAs retire
+          if (kb == kb1 - 1) umma_commit(&tmem_full[acc]);  // accumulator complete
+        }
+        __syncwarp();
+        if (++stage == kStages) { stage = 0; phase ^= 1; }
+      }
+      if (++acc == 2) { acc = 0; acc_phase ^= 1; }
+    }
+  } else if (warp >= 4) {
+    // ===================== epilogue =====================
+    const int quad = warp & 3;  // TMEM lane quadrant this warp may read
+    int acc = 0;
+    uint32_t acc_phase = 0;
+    const bool has_bias = (p.epi & DEDLOC_EPI_BIAS) != 0;
+    const bool bias_f32 = (p.epi & DEDLOC_EPI_BIAS_F32) != 0;
+    const bool do_gelu = (p.epi & DEDLOC_EPI_GELU) != 0;
+    const bool do_dgelu = (p.epi & DEDLOC_EPI_DGELU) != 0;
+    const bool has_res = (p.epi & DEDLOC_EPI_RESIDUAL) != 0;
+    const bool save_pre = (p.epi & DEDLOC_EPI_SAVE_PRE) != 0;
+    for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
+      const int rem = tile % (m_tiles * n_tiles);
+      const int m0 = (rem % m_tiles) * BM;
+      const int n0 = (rem / m_tiles) * BN;
+      mbar_wait(&tmem_full[acc], acc_phase);
+      tc_fence_after();
+      const int row = m0 + quad * 32 + lane;
+      const bool row_ok = row < p.M;
+      const uint32_t taddr = tmem_base + ((uint32_t)(quad * 32) << 16) + acc * BN;
+#pragma unroll 1
+      for (int cb = 0; cb < BN; cb += 32) {
+        uint32_t r[32];
+        tmem_ld_32x32b_x32(taddr + cb, r);
+        tmem_ld_wait();
+        const int col0 = n0 + cb;
+        if (col0 >= p.N) continue;  // warp-uniform
+        float v[32];
+#pragma unroll
+        for (int i = 0; i < 32; ++i) v[i] = __uint_as_float(r[i]) * p.alpha;
+        const bool full_cols = (col0 + 32 <= p.N);
+        if (has_bias) {
+          if (bias_f32) {
+            const float* b = reinterpret_cast<const float*>(p.bias) + col0;
+#pragma unroll
+            for (int i = 0; i < 32; ++i) if (full_cols || col0 + i < p.N) v[i] += __ldg(b + i);
+          } else {
+            const __nv_bfloat16* b = reinterpret_cast<const __nv_bfloat16*>(p.bias) + col0;
+#pragma unroll
+            for (int i = 0; i < 32; ++i) if (full_cols || col0 + i < p.N) v[i] += __bfloat162float(b[i]);
+          }
+        }
+        if (row_ok) {
+          if (save_pre) {
+            __nv_bfloat16* po = reinterpret_cast<__nv_bfloat16*>(p.pre_out) + (size_t)row * p.ld_pre + col0;
+            if (full_cols) {
+#pragma unroll
+              for (int i = 0; i < 32; i += 8)
+                *reinterpret_cast<uint4*>(po + i) = make_uint4(pack_bf16x2(v[i], v[i + 1]), pack_bf16x2(v[i + 2], v[i + 3]),
+                                                               pack_bf16x2(v[i + 4], v[i + 5]), pack_bf16x2(v[i + 6], v[i + 7]));
+            } else {
+              for (int i = 0; i < 32 && col0 + i < p.N; ++i) po[i] = __float2bfloat16(v[i]);
+            }
+          }
+          if (do_gelu) {
+#pragma unroll
+            for (int i = 0; i < 32; ++i) v[i] = gelu_tanh(v[i]);
+          }
+          if (do_dgelu) {
+            const __nv_bfloat16* ai = reinterpret_cast<const __nv_bfloat16*>(p.aux_in) + (size_t)row * p.ld_aux + col0;
+            if (full_cols) {
+#pragma unroll
+              for (int i = 0; i < 32; i += 8) {
+                const uint4 u = *reinterpret_cast<const uint4*>(ai + i);
+                float2 t;
+                t = unpack_bf16x2(u.x); v[i] *= gelu_tanh_grad(t.x); v[i + 1] *= gelu_tanh_grad(t.y);
+                t = unpack_bf16x2(u.y); v[i + 2] *= gelu_tanh_grad(t.x); v[i + 3] *= gelu_tanh_grad(t.y);
+                t = unpack_bf16x2(u.z); v[i + 4] *= gelu_tanh_grad(t.x); v[i + 5] *= gelu_tanh_grad(t.y);
+                t = unpack_bf16x2(u.w); v[i + 6] *= gelu_tanh_grad(t.x); v[i + 7] *= gelu_tanh_grad(t.y);
+              }
+            } else {
+              for (int i = 0; i < 32 && col0 + i < p.N; ++i) v[i] *= gelu_tanh_grad(__bfloat162float(ai[i]));
+            }
+          }
+          if (has_res) {
+            const __nv_bfloat16* rs = reinterpret_cast<const __nv_bfloat16*>(p.residual) + (size_t)row * p.ld_res + col0;
+            if (full_cols) {
+#pragma unroll
+              for (int i = 0; i < 32; i += 8) {
+                const uint4 u = *reinterpret_cast<const uint4*>(rs + i);
+                float2 t;
+                t = unpack_bf16x2(u.x); v[i] += t.x; v[i + 1] += t.y;
+                t = unpack_bf16x2(u.y); v[i + 2] += t.x; v[i + 3] += t.y;
+                t = unpack_bf16x2(u.z); v[i + 4] += t.x; v[i + 5] += t.y;
+                t = unpack_bf16x2(u.w); v[i + 6] += t.x; v[i + 7] += t.y;
+              }
+            } else {
+              for (int i = 0; i < 32 && col0 + i < p.N; ++i) v[i] += __bfloat162float(rs[i]);
+            }
+          }
+          if (p.out_kind == 0) {
+            __nv_bfloat16* co = reinterpret_cast<__nv_bfloat16*>(p.C) + (size_t)row * p.ldc + col0;
+            if (full_cols) {
+#pragma unroll
+              for (int i = 0; i < 32; i += 8)
+                *reinterpret_cast<uint4*>(co + i) = make_uint4(pack_bf16x2(v[i], v[i + 1]), pack_bf16x2(v[i + 2], v[i + 3]),
+                                                               pack_bf16x2(v[i + 4], v[i + 5]), pack_bf16x2(v[i + 6], v[i + 7]));
+            } else {
+              for (int i = 0; i < 32 && col0 + i < p.N; ++i) co[i] = __float2bfloat16(v[i]);
+            }
+          } else if (p.out_kind == 1) {
+            float* co = reinterpret_cast<float*>(p.C) + (size_t)row * p.ldc + col0;
+            if (full_cols) {
+#pragma unroll
+              for (int i = 0; i < 32; i += 4) *reinterpret_cast<float4*>(co + i) = make_float4(v[i], v[i + 1], v[i + 2], v[i + 3]);
+            } else {
+              for (int i = 0; i < 32 && col0 + i < p.N; ++i) co[i] = v[i];
+            }
+          } else {
+            float* co = reinterpret_cast<float*>(p.C) + (size_t)row * p.ldc + col0;
+            if (full_cols) {
+#pragma unroll
+              for (int i = 0; i < 32; i += 4)
+                asm volatile("red.global.add.v4.f32 [%0], {%1,%2,%3,%4};" ::"l"(co + i), "f"(v[i]), "f"(v[i + 1]),
+                             "f"(v[i + 2]), "f"(v[i + 3])
+                             : "memory");
+            } else {
+              for (int i = 0; i < 32 && col0 + i < p.N; ++i) atomicAdd(co + i, v[i]);
+            }
+          }
+        }
+      }
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&tmem_empty[acc]);
+      if (++acc == 2) { acc = 0; acc_phase ^= 1; }
+    }
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 2) {
+    tc_fence_after();
+    tmem_dealloc(tmem_base, 2 * BN);
+  }
+}
+
+// ------------------------------------------------------------------------------------------------
+// Host side: tensor maps through the driver entry point (no link-time libcuda dependency).
+// ------------------------------------------------------------------------------------------------
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                  const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
+                                  CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+static EncodeTiledFn get_encode_fn() {
+  static EncodeTiledFn fn = nullptr;
+  if (!fn) {
+    void* f = nullptr;
+    cudaDriverEntryPointQueryResult qres;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &f, cudaEnableDefault, &qres) == cudaSuccess &&
+        qres == cudaDriverEntryPointSuccess)
+      fn = (EncodeTiledFn)f;
+  }
+  return fn;
+}
+
+// 2-D tensor map over a row-major [rows, cols] 16-bit matrix with row stride ld (elements).
+int make_tmap_2d_16bit(CUtensorMap* map, const void* base, long long rows, long long cols, long long ld,
+                       int box_cols, int box_rows, int is_bf16) {
+  EncodeTiledFn fn = get_encode_fn();
+  if (!fn) {
+    set_last_error("cuTensorMapEncodeTiled driver entry point not available");
+    return DEDLOC_EUNSUPPORTED;
+  }
+  cuuint64_t gdim[2] = {(cuuint64_t)cols, (cuuint64_t)rows};
+  cuuint64_t gstride[1] = {(cuuint64_t)ld * 2};
+  cuuint32_t box[2] = {(cuuint32_t)box_cols, (cuuint32_t)box_rows};
+  cuuint32_t estr[2] = {1, 1};
+  CUresult r = fn(map, is_bf16 ? CU_TENSOR_MAP_DATA_TYPE_BFLOAT16 : CU_TENSOR_MAP_DATA_TYPE_FLOAT16, 2,
+                  const_cast<void*>(base), gdim, gstride, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                  CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                  CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) {
+    set_last_error("cuTensorMapEncodeTiled failed with %d (base %p rows %lld cols %lld ld %lld box %dx%d)", (int)r,
+                   base, rows, cols, ld, box_cols, box_rows);
+    return DEDLOC_EINVAL;
+  }
+  return 0;
+}
+
+template <int BN>
+static int launch_gemm(const DedlocGemmArgs& g, cudaStream_t st) {
+  GemmKernelParams kp;
+  kp.M = g.M; kp.N = g.N; kp.K = g.K;
+  kp.a_mn = g.a_mn_major; kp.b_mn = g.b_mn_major;
+  kp.epi = g.epilogue; kp.out_kind = g.out_kind; kp.fmt = g.is_fp16 ? 0 : 1;
+  kp.alpha = g.alpha;
+  kp.C = g.C; kp.ldc = g.ldc;
+  kp.bias = g.bias; kp.residual = g.residual; kp.ld_res = g.ld_residual;
+  kp.aux_in = g.aux_in; kp.ld_aux = g.ld_aux; kp.pre_out = g.pre_out; kp.ld_pre = g.ld_pre;
+  const int kb_total = g.K / BK;
+  int splits = g.split_k < 1 ? 1 : g.split_k;
+  if (splits > kb_total) splits = kb_total;
+  int kb_per = (kb_total + splits - 1) / splits;
+  splits = (kb_total + kb_per - 1) / kb_per;
+  kp.splits = splits;
+  kp.kb_per_split = kb_per;
+  DEDLOC_REQUIRE(splits == 1 || g.out_kind == 2, "gemm: split-K needs the fp32 atomic-add output");
+
+  CUtensorMap ta, tb;
+  int rc;
+  if (!g.a_mn_major) rc = make_tmap_2d_16bit(&ta, g.A, g.M, g.K, g.lda, BK, BM, !g.is_fp16);
+  else rc = make_tmap_2d_16bit(&ta, g.A, g.K, g.M, g.lda, 64, BK, !g.is_fp16);
+  if (rc) return rc;
+  if (!g.b_mn_major) rc = make_tmap_2d_16bit(&tb, g.B, g.N, g.K, g.ldb, BK, BN, !g.is_fp16);
+  else rc = make_tmap_2d_16bit(&tb, g.B, g.K, g.N, g.ldb, 64, BK, !g.is_fp16);
+  if (rc) return rc;
+
+  static int sms = 0;
+  static bool attr_set = false;
+  if (!attr_set) {
+    int dev = 0;
+    DEDLOC_CUDA_CHECK(cudaGetDevice(&dev));
+    DEDLOC_CUDA_CHECK(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
+    DEDLOC_CUDA_CHECK(cudaFuncSetAttribute(gemm_tcgen05_kernel<BN>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                           GemmSmem<BN>::kTotal));
+    attr_set = true;
+  }
+  const int m_tiles = (g.M + BM - 1) / BM, n_tiles = (g.N + BN - 1) / BN;
+  const int total = m_tiles * n_tiles * splits;
+  int grid = total < sms ? total : sms;
+  if (g.max_ctas > 0 && g.max_ctas < grid) grid = g.max_ctas;
+  gemm_tcgen05_kernel<BN><<<grid, kGemmThreads, GemmSmem<BN>::kTotal, st>>>(ta, tb, kp);
+  count_launch();
+  DEDLOC_CUDA_CHECK(cudaGetLastError());
+  return 0;
+}
+
+}  // namespace dedloc
+
+using namespace dedloc;
+
+extern "C" int dedloc_gemm(const DedlocGemmArgs* gp, void* stream) {
+  const DedlocGemmArgs& g = *gp;
+  DEDLOC_REQUIRE(g.M > 0 && g.N > 0 && g.K > 0, "gemm: empty problem %dx%dx%d", g.M, g.N, g.K);
+  DEDLOC_REQUIRE(g.K % BK == 0, "gemm: K (%d) must be a multiple of %d", g.K, BK);
+  DEDLOC_REQUIRE(g.N % 8 == 0, "gemm: N (%d) must be a multiple of 8", g.N);
+  DEDLOC_REQUIRE(g.lda % 8 == 0 && g.ldb % 8 == 0, "gemm: lda/ldb must be multiples of 8 elements (16 B)");
+  DEDLOC_REQUIRE(((uintptr_t)g.A & 15) == 0 && ((uintptr_t)g.B & 15) == 0 && ((uintptr_t)g.C & 15) == 0,
+                 "gemm: A, B, C must be 16-byte aligned");
+  DEDLOC_REQUIRE(g.ldc % 8 == 0, "gemm: ldc must be a multiple of 8");
+  if (g.a_mn_major) DEDLOC_REQUIRE(g.M % 8 == 0, "gemm: MN-major A needs M %% 8 == 0");
+  cudaStream_t st = (cudaStream_t)stream;
+  const int bn = g.block_n ? g.block_n : (g.N <= 128 ? 128 : 256);
+  if (bn == 128) return launch_gemm<128>(g, st);
+  if (bn == 256) return launch_gemm<256>(g, st);
+  set_last_error("gemm: block_n must be 128 or 256");
+  return DEDLOC_EINVAL;
+}

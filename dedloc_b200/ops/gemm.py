@@ -1,0 +1,145 @@
+"""tcgen05/TMEM/TMA GEMM (csrc/gemm_tcgen05.cu) and the autograd functions built on it.
+
+`gemm()` is the raw launcher. `linear()` / `linear_gelu()` / `linear_residual()` are differentiable and cover
+ALBERT's QKV, attention-out, FFN-up (+gelu_new) and FFN-down projections plus the SwAV head (SURVEY C2, C4,
+C5, C6, C13): forward is one kernel with the bias / activation / residual fused in the epilogue, dgrad is one
+kernel (optionally with gelu' fused), and wgrad accumulates split-K partial products straight into an fp32
+main-gradient buffer with red.add -- which is exactly what ALBERT's 24-fold weight sharing needs.
+"""
+from __future__ import annotations
+
+import ctypes as C
+from typing import Optional
+
+import torch
+
+from .. import lib as native
+
+_SM_COUNT = {}
+
+
+def _sms(device) -> int:
+    idx = device.index if device.index is not None else torch.cuda.current_device()
+    if idx not in _SM_COUNT:
+        _SM_COUNT[idx] = torch.cuda.get_device_properties(idx).multi_processor_count
+    return _SM_COUNT[idx]
+
+
+def gemm(a: torch.Tensor, b: torch.Tensor, out: torch.Tensor, *, a_mn_major: bool = False,
+         b_mn_major: bool = False, bias: Optional[torch.Tensor] = None, gelu: bool = False,
+         dgelu_aux: Optional[torch.Tensor] = None, residual: Optional[torch.Tensor] = None,
+         pre_out: Optional[torch.Tensor] = None, accumulate: bool = False, alpha: float = 1.0,
+         split_k: int = 1, block_n: int = 0, max_ctas: int = 0) -> torch.Tensor:
+    """out[M,N] = epilogue(A . B^T).
+
+    a: [M,K] (K-major) or [K,M] (a_mn_major); b: [N,K] (K-major, nn.Linear weight) or [K,N] (b_mn_major).
+    out: bf16 [M,N]; or fp32 [M,N] (store, or `accumulate=True` for out += with red.add and optional split-K).
+    """
+    assert a.is_cuda and a.dim() == 2 and b.dim() == 2 and out.dim() == 2
+    assert a.dtype == b.dtype and a.dtype in (torch.bfloat16, torch.float16)
+    assert a.stride(1) == 1 and b.stride(1) == 1 and out.stride(1) == 1
+    M, N = out.shape
+    K = a.shape[0] if a_mn_major else a.shape[1]
+    assert (a.shape[1] if a_mn_major else a.shape[0]) == M, "A shape mismatch"
+    assert (b.shape == (K, N)) if b_mn_major else (b.shape == (N, K)), "B shape mismatch"
+    g = native.GemmArgs()
+    g.A, g.B, g.C = a.data_ptr(), b.data_ptr(), out.data_ptr()
+    g.M, g.N, g.K = M, N, K
+    g.lda, g.ldb, g.ldc = a.stride(0), b.stride(0), out.stride(0)
+    g.a_mn_major, g.b_mn_major = int(a_mn_major), int(b_mn_major)
+    g.is_fp16 = int(a.dtype == torch.float16)
+    epi = 0
+    if bias is not None:
+        epi |= native.EPI_BIAS
+        if bias.dtype == torch.float32:
+            epi |= native.EPI_BIAS_F32
+        else:
+            assert bias.dtype == torch.bfloat16
+        g.bias = bias.data_ptr()
+    if gelu:
+        epi |= native.EPI_GELU
+    if dgelu_aux is not None:
+        epi |= native.EPI_DGELU
+        g.aux_in, g.ld_aux = dgelu_aux.data_ptr(), dgelu_aux.stride(0)
+    if residual is not None:
+        epi |= native.EPI_RESIDUAL
+        g.residual, g.ld_residual = residual.data_ptr(), residual.stride(0)
+    if pre_out is not None:
+        epi |= native.EPI_SAVE_PRE
+        g.pre_out, g.ld_pre = pre_out.data_ptr(), pre_out.stride(0)
+    g.epilogue = epi
+    if out.dtype == torch.bfloat16:
+        g.out_kind = native.OUT_BF16
+        assert not accumulate
+    else:
+        assert out.dtype == torch.float32
+        g.out_kind = native.OUT_F32_ATOMIC if accumulate else native.OUT_F32
+    g.alpha = alpha
+    g.split_k, g.block_n, g.max_ctas = split_k, block_n, max_ctas
+    with torch.cuda.device(a.device):
+        native.check(native.lib().dedloc_gemm(C.byref(g), torch.cuda.current_stream(a.device).cuda_stream), "gemm")
+    return out
+
+
+def pick_split_k(m_out: int, n_out: int, k_red: int, sms: int, block_n: int = 256) -> int:
+    """Split the reduction so that (tiles x splits) fills the machine (wgrad has few output tiles)."""
+    tiles = ((m_out + 127) // 128) * ((n_out + block_n - 1) // block_n)
+    kb = max(k_red // 64, 1)
+    if tiles >= sms:
+        return 1
+    return max(1, min(kb, sms // tiles))
+
+
+class _LinearFn(torch.autograd.Function):
+    """y = act(x W^T + b) (+ residual). Weight/bias gradients are ACCUMULATED into `.main_grad` (fp32)."""
+
+    @staticmethod
+    def forward(ctx, x, weight, bias, act: str, residual, wgrad_out, bgrad_out):
+        x2 = x.reshape(-1, x.shape[-1])
+        if not x2.is_contiguous():
+            x2 = x2.contiguous()
+        M, K = x2.shape
+        N = weight.shape[0]
+        out = torch.empty(M, N, dtype=x.dtype, device=x.device)
+        pre = None
+        if act == "gelu":
+            pre = torch.empty(M, N, dtype=x.dtype, device=x.device)
+        res2 = residual.reshape(M, N) if residual is not None else None
+        gemm(x2, weight, out, bias=bias, gelu=(act == "gelu"), pre_out=pre, residual=res2)
+        ctx.save_for_backward(x2, weight, pre)
+        ctx.act = act
+        ctx.has_bias = bias is not None
+        ctx.has_res = residual is not None
+        ctx.wgrad_out, ctx.bgrad_out = wgrad_out, bgrad_out
+        ctx.x_shape = x.shape
+        return out.view(*x.shape[:-1], N)
+
+    @staticmethod
+    def backward(ctx, dy):
+        x2, weight, pre = ctx.saved_tensors
+        M, K = x2.shape
+        N = weight.shape[0]
+        dy2 = dy.reshape(M, N)
+        if not dy2.is_contiguous():
+            dy2 = dy2.contiguous()
+        dres = dy if ctx.has_res else None
+        if ctx.act == "gelu":
+            # dpre = dy * gelu'(pre): small elementwise pass, then both GEMMs consume dpre
+            from .elementwise import dgelu_mul
+            dy2 = dgelu_mul(dy2, pre)
+        # dgrad: dx[M,K] = dy[M,N] . W[N,K]  -> B operand is W stored [N,K] = [K_red, N_out] MN-major
+        dx = torch.empty(M, K, dtype=x2.dtype, device=x2.device)
+        gemm(dy2, weight, dx, b_mn_major=True)
+        # wgrad: dW[N,K] += dy^T[N,M] . x[M,K]  -> both operands MN-major, reduction over tokens
+        wg = ctx.wgrad_out
+        sk = pick_split_k(N, K, M, _sms(x2.device))
+        gemm(dy2, x2, wg, a_mn_major=True, b_mn_major=True, accumulate=True, split_k=sk)
+        if ctx.has_bias:
+            ctx.bgrad_out.add_(dy2.sum(dim=0, dtype=torch.float32))
+        return dx.view(ctx.x_shape), None, None, None, dres, None, None
+
+
+def linear(x, weight, bias=None, *, act: str = "none", residual=None, wgrad_out=None, bgrad_out=None):
+    """Differentiable fused linear. `wgrad_out`/`bgrad_out` are fp32 buffers that receive dW / db (+=)."""
+    assert wgrad_out is not None, "fused linear accumulates weight gradients into an fp32 main_grad buffer"
+    return _LinearFn.apply(x, weight, bias, act, residual, wgrad_out, bgrad_out)

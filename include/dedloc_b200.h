@@ -1,0 +1,131 @@
+/* dedloc_b200 -- C ABI of the native sm_100a library (libdedloc_b200.so).
+ *
+ * Every entry point returns 0 on success, a positive cudaError_t, or a negative DEDLOC_E* code;
+ * dedloc_last_error() gives the message for the calling thread. `stream` is a cudaStream_t.
+ * Python binds these with ctypes (dedloc_b200/lib/__init__.py); nothing here depends on PyTorch.
+ * Citations name the part of the reference (/root/reference) whose behaviour the
+ * entry point provides.
+ */
+#ifndef DEDLOC_B200_H_
+#define DEDLOC_B200_H_
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define DEDLOC_MAX_PEERS 16
+#define DEDLOC_IPC_HANDLE_BYTES 64
+
+/* ---- library ---------------------------------------------------------------------------------- */
+const char* dedloc_last_error(void);
+long long dedloc_launch_count(void);          /* kernels launched by this library since load */
+int dedloc_device_info(int* sm_count, int* cc_major, int* cc_minor, long long* total_mem);
+
+/* ---- symmetric peer memory over CUDA IPC (SURVEY 5.8 data plane; replaces hivemind's gRPC tensors) */
+int dedloc_symm_alloc(long long bytes, void** ptr, unsigned char handle[DEDLOC_IPC_HANDLE_BYTES]);
+int dedloc_symm_open(const unsigned char handle[DEDLOC_IPC_HANDLE_BYTES], void** ptr);
+int dedloc_symm_close(void* ptr);
+int dedloc_symm_free(void* ptr);
+int dedloc_enable_peer_access(int peer_device);
+int dedloc_memset_async(void* ptr, int value, long long bytes, void* stream);
+int dedloc_memcpy_async(void* dst, const void* src, long long bytes, void* stream);
+int dedloc_memcpy_peer_async(void* dst, int dst_device, const void* src, int src_device, long long bytes,
+                             void* stream);
+
+/* ---- flat gradient path (albert/run_trainer.py:279 HF Trainer clip + hivemind grad accumulation) */
+int dedloc_sumsq(const void* x, int is_bf16, long long n, float* scratch, int scratch_floats, float* out,
+                 void* stream);
+int dedloc_accumulate_clip(float* acc, void* grad, int is_bf16, long long n, const float* normsq,
+                           float max_norm, int zero_grad, void* stream);
+/* wire codecs (hivemind CompressionType, albert/arguments.py:75-77); see csrc/codec.cuh */
+int dedloc_encode(int codec, const float* src, long long n, float scale, void* payload, float* aux,
+                  void* stream);
+long long dedloc_codec_aux_floats(int codec, long long n);
+int dedloc_codec_payload_bytes_per_elem(int codec);
+int dedloc_chunk_elems(void);
+
+/* ---- fused butterfly all-reduce + optimizer (hivemind averager.step + torch_optimizer.Lamb /
+ *      apex LARC+SGD; albert/run_trainer.py:86-94,251-264; sgd_collaborative.py:135-157) ---------- */
+enum { DEDLOC_AR_MEAN = 0, DEDLOC_AR_LAMB = 1, DEDLOC_AR_LARS = 2 };
+enum { DEDLOC_TF_FROZEN = 1, DEDLOC_TF_NO_LARS = 2, DEDLOC_TF_ROWNORM128 = 4 };
+
+typedef struct DedlocARParams {
+  int P;                 /* group size */
+  int me;                /* my index in the group */
+  int mode;              /* DEDLOC_AR_* */
+  int codec;             /* Codec enum of csrc/codec.cuh */
+  int phases;            /* bit0 = phase A, bit1 = phase B (3 in production) */
+  int xgpu_barriers;     /* 1 in production; 0 for single-GPU emulated ranks */
+  uint32_t tag;          /* unique per round (low 2 bits ignored) */
+  int T;                 /* number of tensors in the flat layout */
+  unsigned long long timeout_ns;
+  int replicate_state;   /* push optimizer moments to every member */
+  int max_blocks;        /* 0 = as many as are co-resident */
+  float lr, beta1, beta2, eps, bias_correction, clamp_value, momentum, trust;
+  float w[DEDLOC_MAX_PEERS];                 /* normalised weights, sum = 1 */
+  int slot[DEDLOC_MAX_PEERS];                /* flag slot of every member */
+  long long cbeg[DEDLOC_MAX_PEERS];          /* owned chunk range of every member */
+  long long cend[DEDLOC_MAX_PEERS];
+  const uint8_t* send[DEDLOC_MAX_PEERS];     /* encoded payload of every member */
+  const float* aux[DEDLOC_MAX_PEERS];
+  float* out32[DEDLOC_MAX_PEERS];            /* MEAN: result; LAMB/LARS: fp32 master parameters */
+  uint16_t* out16[DEDLOC_MAX_PEERS];         /* optional bf16 mirror */
+  float* m[DEDLOC_MAX_PEERS];                /* exp_avg / momentum buffer */
+  float* v[DEDLOC_MAX_PEERS];                /* exp_avg_sq */
+  float* table[DEDLOC_MAX_PEERS];            /* [DEDLOC_MAX_PEERS][T+1][2] per-tensor partial sums */
+  uint32_t* flags[DEDLOC_MAX_PEERS];         /* [4][DEDLOC_MAX_PEERS] signal pad */
+  float* gavg;                               /* local scratch: averaged gradient of my shard */
+  float* chunk_stats;                        /* local scratch: [my chunks][2] */
+  const int* chunk_tid;                      /* tensor id of every chunk */
+  const long long* tensor_cbeg;              /* [T+1] first chunk of every tensor */
+  const float* t_wd;                         /* per-tensor weight decay */
+  const float* t_lr_scale;                   /* per-tensor lr multiplier */
+  const int* t_flags;                        /* DEDLOC_TF_* */
+  uint32_t* status;                          /* local: [0] ARStatus, [2] non-finite chunks, [5..7] verdicts */
+} DedlocARParams;
+
+int dedloc_fused_allreduce(const DedlocARParams* params, void* stream);
+int dedloc_ar_params_size(void);
+
+/* ---- tcgen05/TMEM/TMA GEMM with fused epilogues (cuBLAS calls under HF AlbertForPreTraining built at
+ *      albert/run_trainer.py:64-68 and the VISSL swav_head, swav_prototypes_head.py:64-110) ----------- */
+enum {
+  DEDLOC_EPI_BIAS = 1,       /* + bias[n] */
+  DEDLOC_EPI_BIAS_F32 = 2,   /* bias is fp32 (else same 16-bit type as A/B... bf16) */
+  DEDLOC_EPI_GELU = 4,       /* gelu_new(x) */
+  DEDLOC_EPI_DGELU = 8,      /* x * gelu_new'(aux_in[m,n]) */
+  DEDLOC_EPI_RESIDUAL = 16,  /* + residual[m,n] (bf16) */
+  DEDLOC_EPI_SAVE_PRE = 32   /* also store the pre-activation (after bias) to pre_out as bf16 */
+};
+
+typedef struct DedlocGemmArgs {
+  const void* A;      /* K-major: [M,K] row-major; MN-major: [K,M] row-major */
+  const void* B;      /* K-major: [N,K] row-major; MN-major: [K,N] row-major */
+  void* C;            /* [M,N] row-major */
+  int M, N, K;
+  long long lda, ldb, ldc;   /* row strides in elements */
+  int a_mn_major, b_mn_major;
+  int is_fp16;        /* inputs fp16 instead of bf16 */
+  int epilogue;       /* DEDLOC_EPI_* */
+  int out_kind;       /* 0 = bf16 store, 1 = fp32 store, 2 = fp32 atomic add (C += A B^T) */
+  float alpha;
+  const void* bias;
+  const void* residual;
+  long long ld_residual;
+  const void* aux_in;
+  long long ld_aux;
+  void* pre_out;
+  long long ld_pre;
+  int split_k;        /* >1 only with out_kind == 2 */
+  int block_n;        /* 0 = auto, 128 or 256 */
+  int max_ctas;       /* 0 = one per SM */
+} DedlocGemmArgs;
+
+int dedloc_gemm(const DedlocGemmArgs* args, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* DEDLOC_B200_H_ */

@@ -1,0 +1,137 @@
+"""tcgen05 GEMM numerics against an fp32 PyTorch reference: every operand layout, epilogue and tail case."""
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+
+
+def _rand(shape, seed, scale=1.0, dtype=torch.bfloat16):
+    g = torch.Generator().manual_seed(seed)
+    return (torch.randn(shape, generator=g) * scale).to(dtype).cuda()
+
+
+def _check(out, ref, what, rtol=2e-2, atol=2e-2):
+    out, ref = out.float(), ref.float()
+    err = (out - ref).abs().max().item()
+    denom = ref.abs().max().item() + 1e-6
+    assert torch.allclose(out, ref, rtol=rtol, atol=atol * denom), f"{what}: max err {err:.4g} (ref max {denom:.4g})"
+
+
+@pytest.mark.parametrize("a_mn,b_mn", [(False, False), (False, True), (True, False), (True, True)])
+@pytest.mark.parametrize("M,N,K", [(256, 256, 128), (384, 512, 320), (128, 128, 64), (200, 264, 192), (1024, 3072, 1024)])
+def test_gemm_layouts(native, a_mn, b_mn, M, N, K):
+    from dedloc_b200.ops.gemm import gemm
+
+    if a_mn and M % 8:
+        pytest.skip("MN-major A needs M % 8 == 0")
+    a = _rand((K, M) if a_mn else (M, K), 1, 0.5)
+    b = _rand((K, N) if b_mn else (N, K), 2, 0.5)
+    a_log = a.float().t() if a_mn else a.float()
+    b_log = b.float().t() if b_mn else b.float()
+    ref = a_log @ b_log.t()
+    out = torch.empty(M, N, dtype=torch.bfloat16, device="cuda")
+    gemm(a, b, out, a_mn_major=a_mn, b_mn_major=b_mn)
+    torch.cuda.synchronize()
+    _check(out, ref, f"layout a_mn={a_mn} b_mn={b_mn} {M}x{N}x{K}")
+    out32 = torch.empty(M, N, dtype=torch.float32, device="cuda")
+    gemm(a, b, out32, a_mn_major=a_mn, b_mn_major=b_mn)
+    _check(out32, ref, "fp32 out", rtol=1e-3, atol=1e-3)
+
+
+def test_gemm_block_n_128_and_fp16(native):
+    from dedloc_b200.ops.gemm import gemm
+
+    M, N, K = 512, 128, 1024
+    a, b = _rand((M, K), 3, 0.3), _rand((N, K), 4, 0.3)
+    out = torch.empty(M, N, dtype=torch.bfloat16, device="cuda")
+    gemm(a, b, out)
+    _check(out, a.float() @ b.float().t(), "bn128")
+    out = torch.empty(M, 512, dtype=torch.bfloat16, device="cuda")
+    b2 = _rand((512, K), 5, 0.3)
+    gemm(a, b2, out, block_n=128)
+    _check(out, a.float() @ b2.float().t(), "bn128 forced")
+    ah, bh = a.to(torch.float16), b2.to(torch.float16)
+    out32 = torch.empty(M, 512, dtype=torch.float32, device="cuda")
+    gemm(ah, bh, out32)
+    _check(out32, ah.float() @ bh.float().t(), "fp16 inputs", rtol=1e-3, atol=1e-3)
+
+
+def test_gemm_epilogues(native):
+    from dedloc_b200.ops.elementwise import gelu_new, gelu_new_grad
+    from dedloc_b200.ops.gemm import gemm
+
+    M, N, K = 640, 1024, 256
+    a, b = _rand((M, K), 6, 0.3), _rand((N, K), 7, 0.3)
+    bias = _rand((N,), 8, 0.5)
+    res = _rand((M, N), 9, 1.0)
+    base = a.float() @ b.float().t()
+    out = torch.empty(M, N, dtype=torch.bfloat16, device="cuda")
+
+    gemm(a, b, out, bias=bias)
+    _check(out, base + bias.float(), "bias bf16")
+    gemm(a, b, out, bias=bias.float())
+    _check(out, base + bias.float(), "bias fp32")
+    pre = torch.empty_like(out)
+    gemm(a, b, out, bias=bias, gelu=True, pre_out=pre)
+    _check(pre, base + bias.float(), "saved pre-activation")
+    _check(out, gelu_new(base + bias.float()), "gelu")
+    gemm(a, b, out, bias=bias, residual=res)
+    _check(out, base + bias.float() + res.float(), "bias+residual")
+    aux = _rand((M, N), 10, 1.0)
+    gemm(a, b, out, dgelu_aux=aux)
+    _check(out, base * gelu_new_grad(aux.float()), "dgelu")
+    gemm(a, b, out, alpha=0.125)
+    _check(out, base * 0.125, "alpha")
+
+
+def test_gemm_wgrad_splitk_accumulate(native):
+    from dedloc_b200.ops.gemm import gemm
+
+    tokens, N, K = 4096, 512, 256
+    dy, x = _rand((tokens, N), 11, 0.1), _rand((tokens, K), 12, 0.1)
+    wg = torch.ones(N, K, dtype=torch.float32, device="cuda")
+    ref = 1.0 + dy.float().t() @ x.float()
+    gemm(dy, x, wg, a_mn_major=True, b_mn_major=True, accumulate=True, split_k=8)
+    _check(wg, ref, "wgrad split-k", rtol=1e-3, atol=1e-3)
+    gemm(dy, x, wg, a_mn_major=True, b_mn_major=True, accumulate=True, split_k=1)
+    _check(wg, ref + dy.float().t() @ x.float(), "wgrad accumulate twice", rtol=1e-3, atol=1e-3)
+
+
+def test_fused_linear_autograd(native):
+    from dedloc_b200.ops.elementwise import gelu_new
+    from dedloc_b200.ops.gemm import linear
+
+    B, S, K, N = 4, 128, 256, 512
+    x = _rand((B, S, K), 13, 0.5).requires_grad_(True)
+    w, bias = _rand((N, K), 14, 0.05), _rand((N,), 15, 0.1)
+    res = _rand((B, S, N), 16, 0.5).requires_grad_(True)
+    dy = _rand((B, S, N), 17, 0.1)
+    for act in ("none", "gelu"):
+        wg = torch.zeros(N, K, device="cuda")
+        bg = torch.zeros(N, device="cuda")
+        x.grad = None
+        res.grad = None
+        y = linear(x, w, bias, act=act, residual=res, wgrad_out=wg, bgrad_out=bg)
+        y.backward(dy)
+        xr = x.detach().float().requires_grad_(True)
+        wr = w.float().requires_grad_(True)
+        br = bias.float().requires_grad_(True)
+        rr = res.detach().float().requires_grad_(True)
+        pre = xr @ wr.t() + br
+        yr = (gelu_new(pre) if act == "gelu" else pre) + rr
+        yr.backward(dy.float())
+        _check(y, yr, f"fwd {act}")
+        _check(x.grad, xr.grad, f"dx {act}", rtol=3e-2, atol=3e-2)
+        _check(wg, wr.grad, f"dw {act}", rtol=3e-2, atol=3e-2)
+        _check(bg, br.grad, f"db {act}", rtol=3e-2, atol=3e-2)
+        _check(res.grad, rr.grad, f"dres {act}")
+
+
+def test_gemm_rejects_bad_arguments(native):
+    from dedloc_b200.lib import NativeError
+    from dedloc_b200.ops.gemm import gemm
+
+    a, b = _rand((128, 72), 1), _rand((128, 72), 2)
+    out = torch.empty(128, 128, dtype=torch.bfloat16, device="cuda")
+    with pytest.raises(NativeError):
+        gemm(a, b, out)  # K not a multiple of 64
