@@ -131,7 +131,7 @@ __global__ void __launch_bounds__(256) encode_chunk_kernel(const float* __restri
     p[1] = make_uint4(__float_as_uint(x[4]), __float_as_uint(x[5]), __float_as_uint(x[6]), __float_as_uint(x[7]));
   } else if constexpr (CODEC == CODEC_FLOAT16) {
 #pragma unroll
-    for (int i = 0; i < 8; ++i) x[i] = fminf(fmaxf(x[i], -65504.f), 65504.f);  // NaN stays NaN
+    for (int i = 0; i < 8; ++i) x[i] = x[i] > 65504.f ? 65504.f : (x[i] < -65504.f ? -65504.f : x[i]);  // NaN stays NaN
     *reinterpret_cast<uint4*>(payload + e * 2) =
         make_uint4(pack_f16x2(x[0], x[1]), pack_f16x2(x[2], x[3]), pack_f16x2(x[4], x[5]), pack_f16x2(x[6], x[7]));
   } else if constexpr (CODEC == CODEC_BFLOAT16) {

@@ -371,6 +371,16 @@ static int launch_gemm(const DedlocGemmArgs& g, cudaStream_t st) {
   kp.kb_per_split = kb_per;
   DEDLOC_REQUIRE(splits == 1 || g.out_kind == 2, "gemm: split-K needs the fp32 atomic-add output");
 
+  // cuTensorMapEncodeTiled is a driver call: it needs a context bound to THIS thread (autograd's backward
+  // threads have none until a runtime call binds the primary context).
+  static thread_local bool ctx_bound = false;
+  if (!ctx_bound) {
+    int dev = 0;
+    DEDLOC_CUDA_CHECK(cudaGetDevice(&dev));
+    DEDLOC_CUDA_CHECK(cudaSetDevice(dev));
+    DEDLOC_CUDA_CHECK(cudaFree(0));
+    ctx_bound = true;
+  }
   CUtensorMap ta, tb;
   int rc;
   if (!g.a_mn_major) rc = make_tmap_2d_16bit(&ta, g.A, g.M, g.K, g.lda, BK, BM, !g.is_fp16);
