@@ -1,0 +1,623 @@
+"""CollaborativeOptimizer -- collaborative large-batch SGD (the product of the reference).
+
+Every peer accumulates gradients locally and reports progress to the DHT; when the COLLABORATION has
+accumulated `target_batch_size` samples the peers form a group (collab/matchmaking.py), run one weighted
+butterfly all-reduce of the accumulated gradients and all apply the same optimizer step. Constructor and
+attribute surface follow the `hivemind.CollaborativeOptimizer` call sites of the reference
+(albert/run_trainer.py:251-264, run_first_peer.py:97-108, run_aux.py:243-258, sgd_collaborative.py:145-157):
+`.step() .step_aux() .zero_grad() .load_state_from_peers() .opt .scheduler .prefix .local_step
+.local_samples_accumulated .performance_ema .collaboration_state .is_synchronized .param_groups .state_dict()`.
+
+Two data paths:
+  * fused (GPU, `opt` is a FusedLamb / FusedLARS): ONE sm_100a kernel reduce-scatters the encoded gradients
+    over NVLink peer memory, applies the sample-count weights, runs LAMB/LARS on the owned shard and all-gathers
+    the new parameters (parallel/fused_allreduce.py). No NCCL on this path.
+  * generic (any torch optimizer; CPU peers): weighted mean of the gradients through the socket butterfly
+    (parallel/cpu_backend.py) or the MEAN mode of the kernel, then `opt.step()` locally.
+Averaging failures are logged and swallowed: the peer proceeds with its local gradients (H3 step 6).
+"""
+from __future__ import annotations
+
+import asyncio
+import logging
+import threading
+import time
+from typing import Any, Dict, List, Optional
+
+import torch
+
+from ..dht import DHT, get_dht_time
+from ..dht.protocol import RPCClient, RPCServer
+from ..optim.fused import FusedOptimizerBase
+from ..utils.compression import CHUNK, CompressionType
+from .matchmaking import AllreduceException, GroupInfo, Matchmaking
+from .progress import CollaborationState, PerformanceEMA, ProgressTracker
+
+logger = logging.getLogger(__name__)
+
+MODE_NODE, MODE_CLIENT, MODE_AUX = 0, 1, 2
+
+
+class CollaborativeOptimizer:
+    def __init__(self, opt: torch.optim.Optimizer, *, dht: DHT, prefix: str, target_batch_size: int,
+                 batch_size_per_step: Optional[int] = None, scheduler=None, min_refresh_period: float = 0.5,
+                 max_refresh_period: float = 30, default_refresh_period: float = 3,
+                 expected_drift_peers: float = 3, expected_drift_rate: float = 0.2,
+                 performance_ema_alpha: float = 0.1, metadata_expiration: float = 30.0,
+                 averaging_timeout: Optional[float] = 30.0, averaging_expiration: float = 5.0,
+                 target_group_size: int = 256, step_tolerance: int = 1, client_mode: bool = False,
+                 auxiliary: bool = False, allow_state_sharing: bool = True, verbose: bool = False,
+                 compression_type: Any = CompressionType.FLOAT16, compression: Any = None,
+                 throughput: Optional[float] = None, bandwidth: Optional[float] = None,
+                 listen_on: str = "127.0.0.1:*", start: bool = True, max_grad_norm: Optional[float] = None,
+                 peer_key: Optional[bytes] = None, expected_group_size_from_tracker: bool = True,
+                 replicate_state: bool = True, **unused_kwargs):
+        if compression is not None:  # sgd_collaborative.py:150 spells the kwarg `compression=`
+            compression_type = compression
+        if isinstance(compression_type, str):
+            compression_type = CompressionType.Value(compression_type)
+        self.opt, self.dht, self.prefix, self.scheduler = opt, dht, prefix, scheduler
+        self.target_batch_size, self.batch_size_per_step = target_batch_size, batch_size_per_step
+        self.averaging_timeout = averaging_timeout if averaging_timeout is not None else 30.0
+        self.averaging_expiration, self.target_group_size = averaging_expiration, target_group_size
+        self.step_tolerance, self.client_mode, self.auxiliary = step_tolerance, client_mode, auxiliary
+        self.allow_state_sharing = allow_state_sharing and not auxiliary
+        self.verbose, self.compression_type = verbose, CompressionType(compression_type)
+        self.throughput = throughput if throughput is not None else bandwidth
+        self.max_grad_norm = max_grad_norm
+        self.expected_group_size_from_tracker = expected_group_size_from_tracker
+        self.replicate_state = replicate_state
+        self.unused_kwargs = unused_kwargs
+        assert not (client_mode and auxiliary), "an auxiliary peer must accept inbound connections"
+
+        self.local_step = 0
+        self.local_samples_accumulated = 0
+        self.local_steps_accumulated = 0
+        self.last_step_time: Optional[float] = None
+        self.state_lock = threading.RLock()
+        self.round_counter = 0
+        self.stats = {"rounds": 0, "failed_rounds": 0, "solo_rounds": 0, "state_downloads": 0,
+                      "matchmaking_s": 0.0, "averaging_host_s": 0.0}
+        self.is_fused = isinstance(opt, FusedOptimizerBase)
+        self._params = [p for g in opt.param_groups for p in g["params"]]
+        self.on_gpu = bool(self._params) and self._params[0].device.type == "cuda"
+        self._cpu_acc: Optional[List[torch.Tensor]] = None
+        self._server: Optional[RPCServer] = None
+        self._client = RPCClient()
+        self._matchmaking: Optional[Matchmaking] = None
+        self._cpu_averager = None
+        self.endpoint: Optional[str] = None
+        self.peer_key = peer_key
+        self.tracker: Optional[ProgressTracker] = None
+        self._tracker_kwargs = dict(
+            metadata_expiration=metadata_expiration, min_refresh_period=min_refresh_period,
+            max_refresh_period=max_refresh_period, default_refresh_period=default_refresh_period,
+            expected_drift_peers=expected_drift_peers, expected_drift_rate=expected_drift_rate,
+            performance_ema_alpha=performance_ema_alpha)
+        self.metadata_expiration = metadata_expiration
+        self.listen_on = listen_on
+        self._started = False
+        if start:
+            self.start()
+
+    # ------------------------------------------------------------------------------ lifecycle
+    def start(self) -> None:
+        if self._started:
+            return
+        if self.is_fused and self.on_gpu:
+            self.opt.materialize()
+        loop = self.dht.loop
+
+        async def _start_server():
+            if self.client_mode:
+                return None, None
+            server = RPCServer({})
+            host, _, port = self.listen_on.rpartition(":")
+            bind = host.strip("[]")
+            if bind in ("", "*", "::"):
+                bind = "0.0.0.0"
+            p = await server.start(bind, 0 if port in ("", "*") else int(port))
+            return server, p
+
+        self._server, port = asyncio.run_coroutine_threadsafe(_start_server(), loop).result()
+        visible_host = self.dht.get_visible_address().rpartition(":")[0]
+        import os
+        import uuid
+        self.endpoint = f"{visible_host}:{port}" if port else f"client-{os.getpid()}-{uuid.uuid4().hex[:8]}"
+        if self.peer_key is None:
+            self.peer_key = self.endpoint.encode()
+        from ..parallel.cpu_backend import CPUAverager
+
+        self._matchmaking = Matchmaking(self.dht, self._server, self._client, endpoint=self.endpoint,
+                                        prefix=self.prefix, target_group_size=self.target_group_size,
+                                        averaging_expiration=self.averaging_expiration,
+                                        client_mode=self.client_mode)
+        self._cpu_averager = CPUAverager(self._server, self._client, self.compression_type,
+                                         timeout=self.averaging_timeout)
+        if self._server is not None:
+            self._server.handlers["download_state"] = self._rpc_download_state
+        self.tracker = ProgressTracker(self.dht, self.prefix, self.peer_key, self.target_batch_size,
+                                       endpoint=self.endpoint, client_mode=self.client_mode,
+                                       auxiliary=self.auxiliary, **self._tracker_kwargs)
+        self._started = True
+        self._publish_state_sharing()
+        self.tracker.report(self.local_step, 0)
+
+    def shutdown(self) -> None:
+        if not self._started:
+            return
+        self._started = False
+        try:
+            self.tracker.shutdown()
+        except Exception:
+            pass
+
+        async def _stop():
+            if self._server is not None:
+                await self._server.shutdown()
+            await self._client.shutdown()
+
+        try:
+            asyncio.run_coroutine_threadsafe(_stop(), self.dht.loop).result(timeout=5)
+        except Exception:
+            pass
+
+    def __del__(self):
+        try:
+            self.shutdown()
+        except Exception:
+            pass
+
+    # ------------------------------------------------------------------------------ torch.optim duck typing
+    @property
+    def param_groups(self):
+        return self.opt.param_groups
+
+    @property
+    def state(self):
+        return self.opt.state
+
+    @property
+    def defaults(self):
+        return self.opt.defaults
+
+    def add_param_group(self, group):
+        raise ValueError("CollaborativeOptimizer does not support adding parameter groups after creation")
+
+    def state_dict(self) -> dict:
+        sd = self.opt.state_dict()
+        sd["state"] = dict(sd["state"])
+        sd["state"]["local_step"] = self.local_step
+        return sd
+
+    def load_state_dict(self, sd: dict) -> None:
+        sd = dict(sd)
+        state = dict(sd.get("state", {}))
+        if "local_step" in state:
+            self.local_step = int(state.pop("local_step"))
+        sd["state"] = state
+        self.opt.load_state_dict(sd)
+        self._sync_scheduler()
+
+    def zero_grad(self, *args, **kwargs):
+        if self.is_fused and self.on_gpu:
+            return self.opt.zero_grad()
+        kwargs.setdefault("set_to_none", False)
+        return self.opt.zero_grad(*args, **kwargs)
+
+    # ------------------------------------------------------------------------------ reference attributes
+    @property
+    def performance_ema(self) -> PerformanceEMA:
+        return self.tracker.performance_ema
+
+    @property
+    def collaboration_state(self) -> CollaborationState:
+        return self.tracker.collaboration_state
+
+    @property
+    def is_synchronized(self) -> bool:
+        return self.local_step >= self.collaboration_state.optimizer_step - self.step_tolerance
+
+    def is_alive(self) -> bool:
+        return self._started and self.dht.is_alive()
+
+    # ------------------------------------------------------------------------------ the step
+    def step(self, batch_size: Optional[int] = None, **kwargs) -> Optional[bool]:
+        """Accumulate the current gradients; run a collaborative optimizer step when the collaboration is ready.
+        Returns True when a global step happened."""
+        if self.auxiliary:
+            raise RuntimeError("auxiliary peers call step_aux()")
+        if self.batch_size_per_step is None:
+            if batch_size is None:
+                raise ValueError("pass batch_size to step() or batch_size_per_step to the constructor")
+            self.batch_size_per_step = batch_size
+        batch_size = batch_size if batch_size is not None else self.batch_size_per_step
+
+        if not self.is_synchronized:
+            logger.warning("%s is behind the collaboration (local step %d, global %d): downloading state",
+                           self.endpoint, self.local_step, self.collaboration_state.optimizer_step)
+            self.load_state_from_peers()
+            self.zero_grad()
+            return False
+        if self.last_step_time is not None and get_dht_time() - self.last_step_time > self.metadata_expiration:
+            logger.warning("training step took longer than metadata_expiration; peers may not see this one")
+
+        with self.state_lock:
+            self._accumulate_local_gradients()
+            self.local_samples_accumulated += batch_size
+            self.local_steps_accumulated += 1
+        self.tracker.report(self.local_step, self.local_samples_accumulated, update_ema_with=batch_size)
+        self.last_step_time = get_dht_time()
+        self._maybe_republish_state_sharing()
+
+        if not self.collaboration_state.ready_for_step:
+            return False
+        state = self.tracker.refresh_now()  # H3 step 4: somebody may already have stepped
+        if state.optimizer_step > self.local_step:
+            # the collaboration moved on without us: our accumulated samples belong to a finished step
+            if not self.is_synchronized:
+                return False
+        elif not state.ready_for_step:
+            return False
+        self._global_step(state)
+        return True
+
+    def step_aux(self, **kwargs) -> bool:
+        """Auxiliary peers donate bandwidth: they join the averaging round with weight 0 (run_aux.py:260-262)."""
+        if not self.auxiliary:
+            raise RuntimeError("step_aux() is for auxiliary peers")
+        if not self.is_synchronized and self.is_fused and self.on_gpu:
+            self.load_state_from_peers()
+        state = self.tracker.refresh_now()
+        if not state.ready_for_step or state.num_peers - state.num_aux < 1:
+            return False
+        self.local_step = max(self.local_step, state.optimizer_step)
+        self._global_step(state)
+        return True
+
+    # ------------------------------------------------------------------------------ gradient accumulation
+    @torch.no_grad()
+    def _accumulate_local_gradients(self) -> None:
+        if self.is_fused and self.on_gpu:
+            opt = self.opt
+            views = opt.layout.views(opt.grad_flat)
+            for p, v in zip(opt.flat_params, views):  # somebody may have reset .grad (set_to_none / new tensor)
+                if p.grad is None:
+                    p.grad = v
+                elif p.grad.data_ptr() != v.data_ptr():
+                    v.add_(p.grad)
+                    p.grad = v
+            opt.fold_gradients(self.max_grad_norm)
+            return
+        if self._cpu_acc is None:
+            self._cpu_acc = [torch.zeros_like(p, dtype=torch.float32) for p in self._params]
+        grads = [p.grad if p.grad is not None else torch.zeros_like(p) for p in self._params]
+        coef = 1.0
+        if self.max_grad_norm is not None and self.max_grad_norm > 0:
+            total = torch.sqrt(sum((g.float() ** 2).sum() for g in grads))
+            coef = float(min(1.0, self.max_grad_norm / (float(total) + 1e-6)))
+        for a, g in zip(self._cpu_acc, grads):
+            a.add_(g.float(), alpha=coef)
+
+    # ------------------------------------------------------------------------------ global step
+    def _my_blob(self) -> dict:
+        mode = MODE_AUX if self.auxiliary else (MODE_CLIENT if self.client_mode else MODE_NODE)
+        blob = {"weight": 0.0 if self.auxiliary else float(self.local_samples_accumulated), "mode": mode,
+                "throughput": None if self.client_mode else float(self.throughput or 1.0),
+                "step": self.local_step, "handle": None, "total": None, "device": None}
+        if self.is_fused and self.on_gpu:
+            blob.update(handle=self.opt.buffers.handle, total=self.opt.layout.total,
+                        device=self.opt.buffers.device)
+        return blob
+
+    def _global_step(self, state: CollaborationState) -> None:
+        t0 = time.perf_counter()
+        with self.performance_ema.pause(), self.state_lock:
+            group: Optional[GroupInfo] = None
+            if state.num_peers > 1:  # num_peers counts this peer's own progress record too
+                expected = state.num_peers if self.expected_group_size_from_tracker else None
+                try:
+                    group = self.dht.run_coroutine(
+                        lambda dht, node: self._matchmaking.look_for_group(
+                            self._my_blob(), timeout=self.averaging_timeout, expected_size=expected))
+                except Exception as e:
+                    logger.warning("matchmaking failed: %r", e)
+            t1 = time.perf_counter()
+            self.stats["matchmaking_s"] += t1 - t0
+            self.stats["rounds"] += 1
+            averaged = False
+            if group is not None and group.group_size > 1:
+                try:
+                    self._run_group_round(group)
+                    averaged = True
+                except AllreduceException as e:
+                    self.stats["failed_rounds"] += 1
+                    logger.warning("Skipped averaging: averaging round failed with %r", e)
+            if not averaged and not self.auxiliary:
+                self.stats["solo_rounds"] += 1
+                self._run_solo_round()
+            self._finish_global_step()
+            self.stats["averaging_host_s"] += time.perf_counter() - t1
+
+    def _finish_global_step(self) -> None:
+        if self.is_fused and self.on_gpu:
+            self.opt.buffers.acc.zero_()
+        elif self._cpu_acc is not None:
+            for a in self._cpu_acc:
+                a.zero_()
+        self.local_step += 1
+        self.local_samples_accumulated = 0
+        self.local_steps_accumulated = 0
+        self._sync_scheduler()
+        self.tracker.collaboration_state = self.tracker.collaboration_state.register_step(self.local_step)
+        self.tracker.report(self.local_step, 0)
+        self.tracker.should_refresh.set()
+        self._publish_state_sharing()
+        if self.verbose:
+            logger.info("%s: collaborative step %d done", self.endpoint, self.local_step)
+
+    def _sync_scheduler(self) -> None:
+        if self.scheduler is not None:
+            while getattr(self.scheduler, "_step_count", 0) <= self.local_step:
+                self.scheduler.step()
+
+    # ---- fused (GPU) rounds --------------------------------------------------------------------------
+    def _next_tag(self, group_id: Optional[bytes] = None) -> int:
+        self.round_counter += 1
+        if group_id is not None:
+            tag = int.from_bytes(group_id[:4], "little") & 0x3FFFFFFF
+        else:
+            tag = (0x20000000 | (self.round_counter & 0x1FFFFFFF))
+        return tag or 1
+
+    def _encode_local(self, codec: CompressionType) -> None:
+        from ..ops import flat_ops
+
+        buf = self.opt.buffers
+        scale = 1.0 / max(self.local_steps_accumulated, 1)
+        flat_ops.encode(codec, buf.acc, scale, buf.send, buf.aux)
+
+    def _launch_fused(self, group_spec, codec) -> dict:
+        from ..parallel.fused_allreduce import fused_allreduce
+
+        opt = self.opt
+        opt.opt_step += 1
+        hyper = opt.hyper()
+        hyper.replicate_state = self.replicate_state
+        fused_allreduce(opt.buffers, group_spec, codec, hyper, xgpu_barriers=len(group_spec.bases) > 1)
+        status = opt.buffers.read_status()
+        if status["code"] in (1, 2):
+            opt.opt_step -= 1
+        return status
+
+    def _run_solo_round(self) -> None:
+        if self.is_fused and self.on_gpu:
+            from ..parallel.fused_allreduce import GroupSpec
+
+            buf = self.opt.buffers
+            self._encode_local(CompressionType.NONE)
+            spec = GroupSpec(bases=[buf.symm.ptr], me=0, weights=[1.0], shards=[(0, self.opt.layout.n_chunks)],
+                             slots=[0], tag=self._next_tag())
+            status = self._launch_fused(spec, CompressionType.NONE)
+            if status["code"] == 4:
+                logger.warning("non-finite gradients: optimizer update skipped at step %d", self.local_step)
+            return
+        steps = max(self.local_steps_accumulated, 1)
+        with torch.no_grad():
+            for p, a in zip(self._params, self._cpu_acc or []):
+                p.grad = (a / steps).to(p.dtype)
+        self._generic_opt_step()
+
+    def _generic_opt_step(self) -> None:
+        finite = all(torch.isfinite(p.grad).all() for p in self._params if p.grad is not None)
+        if finite:
+            self.opt.step()
+        else:
+            logger.warning("non-finite gradients: optimizer update skipped at step %d", self.local_step)
+
+    def _run_group_round(self, group: GroupInfo) -> None:
+        blobs = list(group.gathered)
+        all_gpu = all(b.get("handle") for b in blobs) and len({b.get("total") for b in blobs}) == 1
+        if self.is_fused and self.on_gpu and all_gpu:
+            return self._run_fused_group_round(group, blobs)
+        return self._run_socket_group_round(group, blobs)
+
+    def _run_fused_group_round(self, group: GroupInfo, blobs: List[dict]) -> None:
+        from ..parallel.fused_allreduce import GroupSpec
+
+        opt, buf = self.opt, self.opt.buffers
+        if blobs[0]["total"] != opt.layout.total:
+            raise AllreduceException("peers disagree on the flat layout size")
+        try:
+            bases = [buf.peer_base(bytes(b["handle"])) for b in blobs]
+        except Exception as e:
+            raise AllreduceException(f"cannot map peer memory: {e!r}")
+        shares = [0.0 if b["mode"] == MODE_CLIENT else 1.0 for b in blobs]
+        weights = [float(b["weight"]) for b in blobs]
+        if sum(weights) <= 0:
+            raise AllreduceException("group has no gradient contributors")
+        self._encode_local(self.compression_type)
+        spec = GroupSpec(bases=bases, me=group.my_index, weights=weights,
+                         shards=opt.layout.shard_ranges(shares), slots=list(range(len(blobs))),
+                         tag=self._next_tag(group.group_id), timeout_s=self.averaging_timeout)
+        status = self._launch_fused(spec, self.compression_type)
+        code = status["code"]
+        if code == 0:
+            return
+        if code == 4:
+            logger.warning("non-finite averaged gradients: update skipped by the whole group")
+            return
+        if code == 3:
+            # pushes may be torn: force a resync on the next step()
+            self.local_step = -10 ** 6
+            raise AllreduceException("peer vanished during the all-gather; state will be re-downloaded")
+        raise AllreduceException(f"fused all-reduce aborted: {status['name']}")
+
+    def _run_socket_group_round(self, group: GroupInfo, blobs: List[dict]) -> None:
+        """Socket butterfly (CPU peers, or a mixed group): average the gradients, then step locally."""
+        from ..parallel.flat import FlatLayout
+
+        steps = max(self.local_steps_accumulated, 1)
+        if self.is_fused and self.on_gpu:
+            layout = self.opt.layout
+            flat = (self.opt.buffers.acc / steps).cpu()
+        else:
+            layout = FlatLayout([p.shape for p in self._params])
+            acc = self._cpu_acc or [torch.zeros_like(p, dtype=torch.float32) for p in self._params]
+            flat = layout.pack([a / steps for a in acc], dtype=torch.float32, device="cpu")
+        weights = [float(b["weight"]) for b in blobs]
+        throughputs = [b["throughput"] if b["mode"] != MODE_CLIENT else None for b in blobs]
+        if sum(weights) <= 0:
+            raise AllreduceException("group has no gradient contributors")
+        try:
+            averaged = self.dht.run_coroutine(
+                lambda dht, node: self._cpu_averager.allreduce(group, flat, weights, throughputs))
+        except AllreduceException:
+            raise
+        except Exception as e:
+            raise AllreduceException(repr(e))
+        if self.auxiliary:
+            return
+        if self.is_fused and self.on_gpu:
+            from ..parallel.fused_allreduce import GroupSpec
+
+            buf = self.opt.buffers
+            buf.acc.copy_(averaged.to(buf.acc.device))
+            self.local_steps_accumulated = 1
+            self._encode_local(CompressionType.NONE)
+            spec = GroupSpec(bases=[buf.symm.ptr], me=0, weights=[1.0], shards=[(0, layout.n_chunks)],
+                             slots=[0], tag=self._next_tag())
+            self._launch_fused(spec, CompressionType.NONE)
+            return
+        with torch.no_grad():
+            for p, g in zip(self._params, layout.views(averaged)):
+                p.grad = g.to(device=p.device, dtype=p.dtype).clone()
+        self._generic_opt_step()
+
+    # ------------------------------------------------------------------------------ state sharing (X2, H4)
+    @property
+    def _state_sharing_key(self) -> str:
+        return f"{self.prefix}_averaging.all_averagers"
+
+    def _publish_state_sharing(self) -> None:
+        self._last_state_publish = get_dht_time()
+        if not self.allow_state_sharing or self.client_mode or self._server is None:
+            return
+        self.dht.store(self._state_sharing_key, {"step": self.local_step}, get_dht_time() + self.metadata_expiration,
+                       subkey=self.endpoint, return_future=True)
+
+    def _maybe_republish_state_sharing(self) -> None:
+        if get_dht_time() - getattr(self, "_last_state_publish", 0.0) > self.metadata_expiration / 2:
+            self._publish_state_sharing()
+
+    def _scheduler_state(self):
+        try:
+            return None if self.scheduler is None else {k: v for k, v in self.scheduler.state_dict().items()
+                                                        if isinstance(v, (int, float, list, str, bool))}
+        except Exception:
+            return None
+
+    async def _rpc_download_state(self, peer_host: str, payload) -> dict:
+        """Donor side. `meta_only` answers are used by the requester as a seqlock around its NVLink copy."""
+        if not self.allow_state_sharing:
+            raise RuntimeError("this peer does not share its state")
+        meta = {"local_step": self.local_step, "fused": bool(self.is_fused and self.on_gpu), "handle": None,
+                "total": None, "opt_step": getattr(self.opt, "opt_step", None)}
+        if meta["fused"]:
+            meta.update(handle=self.opt.buffers.handle, total=self.opt.layout.total)
+        if payload.get("meta_only") or (meta["fused"] and payload.get("can_map")):
+            return meta
+        # host path: serialise parameters + optimizer state under the state lock (consistent snapshot)
+        import io
+
+        def snapshot() -> bytes:
+            with self.state_lock:
+                blob = {"params": [p.detach().float().cpu() for p in self._params],
+                        "opt": self.opt.state_dict()}
+                bio = io.BytesIO()
+                torch.save(blob, bio)
+                return bio.getvalue()
+
+        meta["blob"] = await asyncio.get_event_loop().run_in_executor(None, snapshot)
+        return meta
+
+    def load_state_from_peers(self, **kwargs) -> bool:
+        """Download parameters + optimizer statistics + step from the most advanced peer that shares state
+        (albert/run_trainer.py:124-128; run_first_peer.py:119-121). Returns False when nobody could serve us."""
+        found = self.dht.get(self._state_sharing_key, latest=True)
+        donors = []
+        if found is not None and isinstance(found.value, dict):
+            for ep, entry in found.value.items():
+                if ep != self.endpoint and isinstance(entry.value, dict):
+                    donors.append((int(entry.value.get("step", 0)), ep))
+        donors.sort(reverse=True)
+        can_map = bool(self.is_fused and self.on_gpu)
+        for _, ep in donors:
+            try:
+                ok = self._download_from(ep, can_map)
+            except Exception as e:
+                logger.warning("state download from %s failed: %r", ep, e)
+                ok = False
+            if ok:
+                self.stats["state_downloads"] += 1
+                self._sync_scheduler()
+                self.tracker.local_step = self.local_step
+                self.tracker.report(self.local_step, self.local_samples_accumulated)
+                return True
+        if donors:
+            logger.warning("could not load state from any of %d peers", len(donors))
+        else:
+            logger.info("no peers share state yet; keeping the local state")
+        # nobody to learn from: adopt the collaboration's step so that we are not "behind" forever
+        self.local_step = max(self.local_step, self.collaboration_state.optimizer_step)
+        return False
+
+    def _call(self, endpoint: str, method: str, payload: dict, timeout: float):
+        return asyncio.run_coroutine_threadsafe(self._client.call(endpoint, method, payload, timeout),
+                                                self.dht.loop).result()
+
+    def _download_from(self, endpoint: str, can_map: bool) -> bool:
+        meta = self._call(endpoint, "download_state", {"can_map": can_map}, self.averaging_timeout)
+        if meta.get("fused") and can_map and meta.get("handle") and meta["total"] == self.opt.layout.total:
+            # NVLink path: map the donor's symmetric buffer and copy master params, bf16 mirror and moments
+            buf = self.opt.buffers
+            r = buf.regions
+            for _attempt in range(5):
+                base = buf.peer_base(bytes(meta["handle"]))
+                from .. import lib as native
+
+                stream = torch.cuda.current_stream(buf.device)
+                with torch.cuda.device(buf.device):
+                    native.check(native.lib().dedloc_memcpy_async(buf.symm.ptr + r.p32, base + r.p32,
+                                                                  r.total - r.p32, stream.cuda_stream),
+                                 "state copy")
+                stream.synchronize()
+                after = self._call(endpoint, "download_state", {"meta_only": True}, self.averaging_timeout)
+                if after["local_step"] == meta["local_step"]:   # donor did not step while we were copying
+                    self.local_step = int(meta["local_step"])
+                    if meta.get("opt_step") is not None:
+                        self.opt.opt_step = int(meta["opt_step"])
+                    return True
+                meta = after
+            return False
+        if "blob" not in meta:
+            meta = self._call(endpoint, "download_state", {"can_map": False}, self.averaging_timeout * 4)
+        import io
+
+        blob = torch.load(io.BytesIO(meta["blob"]), map_location="cpu", weights_only=False)
+        with self.state_lock, torch.no_grad():
+            if self.is_fused and self.on_gpu:
+                views32 = self.opt.layout.views(self.opt.buffers.p32)
+                views16 = self.opt.layout.views(self.opt.buffers.p16)
+                for v32, v16, src in zip(views32, views16, blob["params"]):
+                    v32.copy_(src)
+                    v16.copy_(src)
+            else:
+                for p, src in zip(self._params, blob["params"]):
+                    p.copy_(src.to(p.dtype))
+            try:
+                self.opt.load_state_dict(blob["opt"])
+            except Exception as e:  # e.g. the donor has not created optimizer state yet
+                logger.debug("optimizer state not loaded: %r", e)
+            self.local_step = int(meta["local_step"])
+        return True

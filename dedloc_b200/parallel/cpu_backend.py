@@ -1,0 +1,147 @@
+"""CPU / socket backend of the averaging round: load-balanced butterfly all-reduce with wire compression
+(BASELINE.json config 1 "2 local peers on CPU").
+
+Every member splits the flat vector into per-owner parts (share proportional to the declared bandwidth, 0 for
+client-mode members), sends part j -- compressed -- to member j, the owner accumulates sum(w_i x_i) / sum(w_i)
+in fp32 and answers each sender with the compressed DELTA (average - what that sender sent, after decode); the
+sender adds the delta to its own decoded... local value. One hop each way: 2 (P-1)/P N bytes per peer. Any
+failure aborts the round for the group (AllreduceException -> the optimizer steps on local gradients).
+This is the path for CPU-only peers (auxiliary peers, tests); GPU peers use parallel/fused_allreduce.py.
+"""
+from __future__ import annotations
+
+import asyncio
+import logging
+from typing import Dict, List, Optional, Sequence, Tuple
+
+import numpy as np
+import torch
+
+from ..collab.matchmaking import AllreduceException, GroupInfo
+from ..dht.protocol import RPCClient, RPCServer
+from ..utils import compression as comp
+from ..utils.compression import CHUNK, CompressionType
+
+logger = logging.getLogger(__name__)
+
+
+def load_balance_peers(n_chunks: int, throughputs: Sequence[Optional[float]], min_chunks: int = 0) -> List[int]:
+    """How many chunks each member reduces. The reference solves an LP (scipy linprog) so that the slowest link
+    finishes earliest; its optimum for a star of independent links is the proportional split computed here in
+    closed form. `None` throughput = client mode = 0 chunks. On the uniform NVSwitch fabric this is an equal
+    split among non-client members."""
+    tp = np.array([0.0 if t is None else max(float(t), 0.0) for t in throughputs], dtype=np.float64)
+    if tp.sum() <= 0:
+        raise ValueError("at least one member must be able to reduce (non-client with positive throughput)")
+    ideal = tp / tp.sum() * n_chunks
+    if min_chunks > 0:  # members whose share would be tiny are not worth a round trip
+        small = (ideal < min_chunks) & (tp > 0)
+        if small.any() and (~small & (tp > 0)).any():
+            tp = np.where(small, 0.0, tp)
+            ideal = tp / tp.sum() * n_chunks
+    counts = np.floor(ideal).astype(np.int64)
+    remainder = int(n_chunks - counts.sum())
+    order = np.argsort(-(ideal - counts), kind="stable")
+    for i in order[:remainder]:
+        counts[i] += 1
+    return counts.tolist()
+
+
+def parts_from_counts(counts: Sequence[int]) -> List[Tuple[int, int]]:
+    out, start = [], 0
+    for c in counts:
+        out.append((start, start + c))
+        start += c
+    return out
+
+
+class _RoundState:
+    def __init__(self, group: GroupInfo, weights: List[float], my_part: torch.Tensor, my_weight: float):
+        self.group = group
+        self.weights = weights
+        self.acc = my_part.clone() * my_weight
+        self.total_weight = my_weight
+        self.received: Dict[int, torch.Tensor] = {}
+        self.remaining = set(range(group.group_size)) - {group.my_index}
+        self.done = asyncio.get_event_loop().create_future()
+
+    def add(self, sender: int, decoded: torch.Tensor, weight: float) -> None:
+        if sender not in self.remaining:
+            raise AllreduceException(f"unexpected part from member {sender}")
+        self.remaining.discard(sender)
+        self.received[sender] = decoded
+        self.acc += decoded * weight
+        self.total_weight += weight
+        if not self.remaining and not self.done.done():
+            self.done.set_result(self.acc / max(self.total_weight, 1e-30))
+
+
+class CPUAverager:
+    """Serves `allreduce_part` on the peer's RPC server and runs rounds on the DHT loop."""
+
+    def __init__(self, server: Optional[RPCServer], client: RPCClient, compression: CompressionType,
+                 timeout: float = 30.0):
+        self.client, self.compression, self.timeout = client, CompressionType(compression), timeout
+        self.rounds: Dict[bytes, _RoundState] = {}
+        self.early: Dict[bytes, List[tuple]] = {}
+        if server is not None:
+            server.handlers["allreduce_part"] = self.rpc_allreduce_part
+
+    async def rpc_allreduce_part(self, peer_host: str, payload) -> bytes:
+        gid, sender = bytes(payload["group_id"]), payload["sender"]
+        enc = comp.from_bytes(payload["data"])
+        decoded = comp.decode(enc)
+        deadline = asyncio.get_event_loop().time() + self.timeout
+        while gid not in self.rounds:  # the owner may enter the round slightly later than the sender
+            if asyncio.get_event_loop().time() > deadline:
+                raise AllreduceException("owner never joined the round")
+            await asyncio.sleep(0.002)
+        state = self.rounds[gid]
+        state.add(sender, decoded, state.weights[sender])
+        average = await asyncio.wait_for(asyncio.shield(state.done), self.timeout)
+        delta = average - decoded
+        return comp.to_bytes(comp.encode(delta, self._delta_codec()))
+
+    def _delta_codec(self) -> CompressionType:
+        return self.compression
+
+    async def allreduce(self, group: GroupInfo, flat: torch.Tensor, weights: List[float],
+                        throughputs: List[Optional[float]]) -> torch.Tensor:
+        """flat: padded fp32 vector (multiple of CHUNK). Returns the weighted average (same shape)."""
+        assert flat.dtype == torch.float32 and flat.numel() % CHUNK == 0
+        P, me = group.group_size, group.my_index
+        counts = load_balance_peers(flat.numel() // CHUNK, throughputs)
+        parts = [(b * CHUNK, e * CHUNK) for b, e in parts_from_counts(counts)]
+        gid = group.group_id
+        mb, me_ = parts[me]
+        state = _RoundState(group, weights, flat[mb:me_], weights[me])
+        if not state.remaining and not state.done.done():
+            state.done.set_result(state.acc / max(state.total_weight, 1e-30))
+        self.rounds[gid] = state
+        out = flat.clone()
+        try:
+            async def send_part(j: int):
+                b, e = parts[j]
+                if e == b:
+                    return
+                enc = comp.encode(flat[b:e], self.compression)
+                sent = comp.decode(enc)  # what the owner will see from us
+                raw = await self.client.call(group.endpoints[j], "allreduce_part",
+                                             {"group_id": gid, "sender": me, "data": comp.to_bytes(enc)},
+                                             timeout=self.timeout)
+                delta = comp.decode(comp.from_bytes(raw))
+                out[b:e] = sent + delta
+
+            sends = [send_part(j) for j in range(P) if j != me]
+            results = await asyncio.gather(*sends, return_exceptions=True)
+            for r in results:
+                if isinstance(r, Exception):
+                    raise AllreduceException(f"averaging round failed: {r!r}")
+            if me_ > mb:
+                out[mb:me_] = await asyncio.wait_for(asyncio.shield(state.done), self.timeout)
+            return out
+        except asyncio.TimeoutError as e:
+            raise AllreduceException("averaging round timed out") from e
+        finally:
+            # keep the round alive briefly so that late senders still get their delta
+            asyncio.get_event_loop().call_later(self.timeout, self.rounds.pop, gid, None)

@@ -1,0 +1,168 @@
+"""BASELINE.json config 1: ALBERT-tiny collaborative MLM, local peers on CPU, synthetic tokens, small target batch.
+
+Checks the plumbing end to end (DHT -> progress tracker -> matchmaking -> socket butterfly -> LAMB):
+  * after every collaborative step all peers hold identical parameters;
+  * the trajectory equals single-process large-batch training on the union of the contributed micro-batches;
+  * a late joiner downloads the state with load_state_from_peers and joins the next rounds;
+  * an auxiliary peer (weight 0) and a client-mode peer (owns no shard) take part without changing the result;
+  * a peer that dies does not stall the others.
+"""
+import threading
+import time
+
+import pytest
+import torch
+
+from dedloc_b200.collab.optimizer import CollaborativeOptimizer
+from dedloc_b200.dht import DHT
+from dedloc_b200.models.albert import AlbertConfig, AlbertForPreTraining
+from dedloc_b200.optim import Lamb
+from dedloc_b200.utils.compression import CompressionType
+
+CFG = dict(vocab_size=128, embedding_size=16, hidden_size=32, num_hidden_layers=2, num_attention_heads=2,
+           intermediate_size=64, max_position_embeddings=16, classifier_dropout_prob=0.0)
+S, BS = 16, 2
+
+
+def make_model(seed=0):
+    torch.manual_seed(seed)
+    return AlbertForPreTraining(AlbertConfig(**CFG))
+
+
+def make_batch(peer: int, k: int):
+    g = torch.Generator().manual_seed(1000 * peer + k)
+    ids = torch.randint(5, CFG["vocab_size"], (BS, S), generator=g)
+    labels = torch.full((BS, S), -100)
+    m = torch.rand(BS, S, generator=g) < 0.3
+    m[:, 1] = True
+    labels[m] = ids[m]
+    sop = torch.randint(0, 2, (BS,), generator=g)
+    return dict(input_ids=ids, labels=labels, sentence_order_label=sop)
+
+
+def make_opt(model, lr=1e-2):
+    no_decay = ["bias", "LayerNorm.weight"]
+    named = [(n, p) for n, p in model.named_parameters()]
+    groups = [{"params": [p for n, p in named if not any(nd in n for nd in no_decay)], "weight_decay": 0.01},
+              {"params": [p for n, p in named if any(nd in n for nd in no_decay)], "weight_decay": 0.0}]
+    return Lamb(groups, lr=lr, betas=(0.9, 0.999), eps=1e-6, weight_decay=0.01, clamp_value=10000.0, debias=True)
+
+
+def make_peer(first_dht, prefix, target, seed=0, **kw):
+    dht = DHT(start=True, initial_peers=[f"127.0.0.1:{first_dht.port}"] if first_dht else [])
+    model = make_model(seed)
+    opt = make_opt(model)
+    defaults = dict(dht=dht, prefix=prefix, target_batch_size=target, batch_size_per_step=BS,
+                    compression_type=CompressionType.NONE, averaging_expiration=2.0, averaging_timeout=10.0,
+                    min_refresh_period=0.05, default_refresh_period=0.1, max_refresh_period=0.5,
+                    target_group_size=16, metadata_expiration=10.0)
+    defaults.update(kw)
+    copt = CollaborativeOptimizer(opt, **defaults)
+    return dht, model, copt
+
+
+def run_trainer(peer_id, model, copt, n_rounds, log, stop=None, max_batches=400):
+    k = 0
+    while copt.local_step < n_rounds and k < max_batches and not (stop is not None and stop.is_set()):
+        batch = make_batch(peer_id, k)
+        round_idx = copt.local_step
+        model.zero_grad()
+        model(**batch).loss.backward()
+        log.append((round_idx, peer_id, k))
+        copt.step()
+        k += 1
+        time.sleep(0.01)
+
+
+def oracle(log, n_rounds, seed=0):
+    model = make_model(seed)
+    opt = make_opt(model)
+    for r in range(n_rounds):
+        items = [(p, k) for (rr, p, k) in log if rr == r]
+        assert items, f"no contributions for round {r}"
+        model.zero_grad()
+        for p, k in items:
+            (model(**make_batch(p, k)).loss / len(items)).backward()
+        opt.step()
+    return model
+
+
+def assert_same_params(a, b, tol=2e-5):
+    for (n, x), (_, y) in zip(a.named_parameters(), b.named_parameters()):
+        assert torch.allclose(x, y, atol=tol, rtol=1e-4), n
+
+
+def test_two_peers_match_large_batch_training():
+    first, m0, c0 = make_peer(None, "cfg1", target=16)
+    d1, m1, c1 = make_peer(first, "cfg1", target=16)
+    log, n_rounds = [], 3
+    threads = [threading.Thread(target=run_trainer, args=(i, m, c, n_rounds, log))
+               for i, (m, c) in enumerate([(m0, c0), (m1, c1)])]
+    try:
+        [t.start() for t in threads]
+        [t.join(timeout=120) for t in threads]
+        assert c0.local_step == n_rounds and c1.local_step == n_rounds
+        assert c0.stats["solo_rounds"] == 0 and c1.stats["solo_rounds"] == 0, (c0.stats, c1.stats)
+        assert_same_params(m0, m1, tol=1e-6)
+        assert_same_params(m0, oracle(log, n_rounds))
+    finally:
+        for c, d in ((c0, first), (c1, d1)):
+            c.shutdown()
+            d.shutdown()
+
+
+def test_late_joiner_aux_and_client_mode():
+    first, m0, c0 = make_peer(None, "cfg1b", target=12)
+    d1, m1, c1 = make_peer(first, "cfg1b", target=12, client_mode=True)
+    daux, maux, caux = make_peer(first, "cfg1b", target=12, auxiliary=True, allow_state_sharing=False)
+    log, stop = [], threading.Event()
+
+    def aux_loop():
+        while not stop.is_set():
+            caux.step_aux()
+            time.sleep(0.05)
+
+    ta = threading.Thread(target=aux_loop, daemon=True)
+    threads = [threading.Thread(target=run_trainer, args=(i, m, c, 2, log)) for i, (m, c) in enumerate([(m0, c0), (m1, c1)])]
+    try:
+        ta.start()
+        [t.start() for t in threads]
+        [t.join(timeout=120) for t in threads]
+        assert c0.local_step == 2 and c1.local_step == 2
+        assert_same_params(m0, m1, tol=1e-6)
+        assert_same_params(m0, oracle(log, 2))
+        # a newcomer with a DIFFERENT init adopts the collaboration's state
+        d2, m2, c2 = make_peer(first, "cfg1b", target=12, seed=123)
+        assert c2.load_state_from_peers()
+        assert c2.local_step == 2
+        assert_same_params(m2, m0, tol=1e-7)
+        st2, st0 = c2.opt.state_dict()["state"], c0.opt.state_dict()["state"]
+        assert torch.allclose(st2[0]["exp_avg"], st0[0]["exp_avg"])
+        c2.shutdown()
+        d2.shutdown()
+    finally:
+        stop.set()
+        for c, d in ((c0, first), (c1, d1), (caux, daux)):
+            c.shutdown()
+            d.shutdown()
+
+
+def test_dead_peer_does_not_stall_the_other():
+    first, m0, c0 = make_peer(None, "cfg1c", target=8, metadata_expiration=1.0, averaging_expiration=0.5)
+    d1, m1, c1 = make_peer(first, "cfg1c", target=8, metadata_expiration=1.0, averaging_expiration=0.5)
+    log = []
+    try:
+        run_trainer(1, m1, c1, 0, log, max_batches=0)
+        # peer 1 reports once, then "dies" (its record expires after metadata_expiration)
+        model_out = m1(**make_batch(1, 0)).loss
+        model_out.backward()
+        c1.step()
+        c1.shutdown()
+        d1.shutdown()
+        t = threading.Thread(target=run_trainer, args=(0, m0, c0, 2, log))
+        t.start()
+        t.join(timeout=60)
+        assert c0.local_step == 2, "the surviving peer must keep stepping on its own gradients"
+    finally:
+        c0.shutdown()
+        first.shutdown()
