@@ -246,12 +246,16 @@ class CollaborativeOptimizer:
             self._accumulate_local_gradients()
             self.local_samples_accumulated += batch_size
             self.local_steps_accumulated += 1
-        self.tracker.report(self.local_step, self.local_samples_accumulated, update_ema_with=batch_size)
+        report = self.tracker.report(self.local_step, self.local_samples_accumulated, update_ema_with=batch_size)
         self.last_step_time = get_dht_time()
         self._maybe_republish_state_sharing()
 
-        if not self.collaboration_state.ready_for_step:
+        if not self.tracker.locally_ready():
             return False
+        try:
+            report.result(timeout=5.0)  # our own latest sample count must be visible to the re-fetch below
+        except Exception:
+            pass
         state = self.tracker.refresh_now()  # H3 step 4: somebody may already have stepped
         if state.optimizer_step > self.local_step:
             # the collaboration moved on without us: our accumulated samples belong to a finished step

@@ -154,6 +154,15 @@ class ProgressTracker:
             fut.result()
         return fut
 
+    def locally_ready(self) -> bool:
+        """`ready_for_step` of the cached collaboration state, corrected by the samples this peer accumulated
+        since that state was fetched (so a fast peer does not wait for the next DHT refresh to notice)."""
+        st = self.collaboration_state
+        if st.ready_for_step:
+            return True
+        own_delta = self.local_samples_accumulated - getattr(self, "_own_samples_in_state", 0)
+        return st.optimizer_step <= self.local_step and st.samples_accumulated + max(own_delta, 0) >= st.target_batch_size
+
     # ---------------------------------------------------------------- fetching
     def _updater(self) -> None:
         while not self.shutdown_flag.is_set():
@@ -192,6 +201,8 @@ class ProgressTracker:
                 valid[key] = TrainingState.model_validate(entry.value)
             except Exception:
                 logger.debug("ignoring malformed progress record from %r", key)
+        mine = valid.get(self.peer_key)
+        self._own_samples_in_state = mine.samples_accumulated if (mine is not None and mine.step >= self.local_step) else 0
         num_peers = len(valid)
         num_clients = sum(s.client_mode for s in valid.values())
         num_aux = sum(s.auxiliary for s in valid.values())

@@ -1,0 +1,167 @@
+"""Building blocks shared by the ALBERT / sahajBERT trainers and bench.py: one collaborative peer on one GPU.
+
+`build_albert_peer()` wires model -> FusedLamb (two weight-decay groups, albert/run_trainer.py:73-100) -> linear
+warm-up schedule -> CollaborativeOptimizer; `PeerTrainer.micro_step()` is one forward/backward + `opt.step()`
+(= one HF-Trainer inner-loop iteration of the reference), and `SyntheticMLMBatches` produces
+WikiText-shaped synthetic batches (15 % masked tokens, 50 % swapped sentence order) in pinned host memory.
+"""
+from __future__ import annotations
+
+import math
+from dataclasses import dataclass
+from typing import Dict, Iterator, List, Optional
+
+import torch
+
+from ..collab.optimizer import CollaborativeOptimizer
+from ..dht import DHT
+from ..models.albert import AlbertConfig, AlbertForPreTraining
+from ..optim import Lamb
+from ..optim.fused import FusedLamb
+from ..optim.schedules import get_linear_schedule_with_warmup
+from ..utils.compression import CompressionType
+
+
+def albert_param_groups(model: torch.nn.Module, weight_decay: float) -> List[dict]:
+    no_decay = ["bias", "LayerNorm.weight", "layer_norm.weight"]
+    named = list(model.named_parameters())
+    for n, p in named:
+        p._dedloc_name = n
+    return [
+        {"params": [p for n, p in named if not any(nd in n for nd in no_decay)], "weight_decay": weight_decay},
+        {"params": [p for n, p in named if any(nd in n for nd in no_decay)], "weight_decay": 0.0},
+    ]
+
+
+class SyntheticMLMBatches:
+    """Random token batches with the shape and label statistics of tokenised WikiText-103 instances
+    (tokenize_wikitext103.py: [CLS] A [SEP] B [SEP], max 512 tokens, SOP label; DataCollatorForLanguageModeling:
+    15 % of the positions masked -> 80 % [MASK] / 10 % random / 10 % kept)."""
+
+    def __init__(self, vocab_size: int, seq_len: int, batch_size: int, seed: int = 0, mlm_probability: float = 0.15,
+                 pin: bool = True, pool: int = 8, mask_token_id: int = 4, cls_id: int = 2, sep_id: int = 3):
+        g = torch.Generator().manual_seed(seed)
+        self.batches: List[Dict[str, torch.Tensor]] = []
+        for _ in range(pool):
+            ids = torch.randint(5, vocab_size, (batch_size, seq_len), generator=g)
+            ids[:, 0] = cls_id
+            split = torch.randint(seq_len // 4, 3 * seq_len // 4, (batch_size,), generator=g)
+            pos = torch.arange(seq_len)[None]
+            ids[pos == split[:, None]] = sep_id
+            ids[:, -1] = sep_id
+            token_type = (pos > split[:, None]).long()
+            special = (ids == cls_id) | (ids == sep_id)
+            masked = (torch.rand(batch_size, seq_len, generator=g) < mlm_probability) & ~special
+            labels = torch.where(masked, ids, torch.full_like(ids, -100))
+            r = torch.rand(batch_size, seq_len, generator=g)
+            ids = torch.where(masked & (r < 0.8), torch.full_like(ids, mask_token_id), ids)
+            rnd = torch.randint(5, vocab_size, (batch_size, seq_len), generator=g)
+            ids = torch.where(masked & (r >= 0.8) & (r < 0.9), rnd, ids)
+            batch = {"input_ids": ids, "token_type_ids": token_type, "labels": labels,
+                     "attention_mask": torch.ones_like(ids),
+                     "sentence_order_label": torch.randint(0, 2, (batch_size,), generator=g)}
+            if pin and torch.cuda.is_available():
+                batch = {k: v.pin_memory() for k, v in batch.items()}
+            self.batches.append(batch)
+        self.i = 0
+        self.bytes_per_batch = sum(v.numel() * v.element_size() for v in self.batches[0].values())
+
+    def next_host(self) -> Dict[str, torch.Tensor]:
+        b = self.batches[self.i % len(self.batches)]
+        self.i += 1
+        return b
+
+    def to_device(self, batch: Dict[str, torch.Tensor], device) -> Dict[str, torch.Tensor]:
+        return {k: v.to(device, non_blocking=True) for k, v in batch.items()}
+
+
+@dataclass
+class PeerConfig:
+    prefix: str = "albert"
+    target_batch_size: int = 4096
+    micro_batch: int = 32
+    gradient_accumulation_steps: int = 1
+    seq_len: int = 512
+    learning_rate: float = 0.00176
+    warmup_steps: int = 5000
+    max_steps: int = 125_000
+    adam_epsilon: float = 1e-6
+    weight_decay: float = 0.01
+    max_grad_norm: float = 1.0
+    clamp_value: float = 10000.0
+    compression: str = "FLOAT16"
+    target_group_size: int = 256
+    averaging_expiration: float = 5.0
+    averaging_timeout: float = 30.0
+    metadata_expiration: float = 30.0
+    min_refresh_period: float = 0.05
+    max_refresh_period: float = 1.0
+    default_refresh_period: float = 0.2
+    client_mode: bool = False
+    impl: str = "native"
+
+
+class PeerTrainer:
+    def __init__(self, model, opt, scheduler, collab: CollaborativeOptimizer, cfg: PeerConfig, device):
+        self.model, self.opt, self.scheduler, self.collab, self.cfg, self.device = model, opt, scheduler, collab, cfg, device
+        self.loss_sum = torch.zeros((), device=device, dtype=torch.float32)
+        self.mini_steps = 0
+        self.samples_processed = 0
+
+    def micro_step(self, batch: Dict[str, torch.Tensor]) -> bool:
+        """One local step: forward/backward over `gradient_accumulation_steps` x micro_batch samples, then
+        CollaborativeOptimizer.step(). Returns True when a collaborative (global) step happened."""
+        cfg = self.cfg
+        n = batch["input_ids"].shape[0]
+        chunks = cfg.gradient_accumulation_steps
+        for c in range(chunks):
+            sub = {k: v[c * n // chunks:(c + 1) * n // chunks] for k, v in batch.items()} if chunks > 1 else batch
+            out = self.model(**sub)
+            (out.loss / chunks).backward()
+            self.loss_sum += out.loss.detach().float() / chunks
+        if hasattr(self.model, "flush_fused_grads"):
+            self.model.flush_fused_grads()
+        self.mini_steps += 1
+        self.samples_processed += n
+        return bool(self.collab.step(batch_size=n))
+
+    def pop_mean_loss(self) -> float:
+        """Device->host read of the mean loss since the last call (the per-step result of the e2e timing)."""
+        val = float(self.loss_sum.item()) / max(self.mini_steps, 1)
+        self.loss_sum.zero_()
+        self.mini_steps = 0
+        return val
+
+
+def build_albert_peer(dht: DHT, cfg: PeerConfig, model_cfg: Optional[AlbertConfig] = None, device=None,
+                      seed: int = 0, peer_key: Optional[bytes] = None, **collab_kwargs) -> PeerTrainer:
+    device = torch.device(device if device is not None else ("cuda" if torch.cuda.is_available() else "cpu"))
+    model_cfg = model_cfg or AlbertConfig.albert_large_v2()
+    torch.manual_seed(seed)
+    on_gpu = device.type == "cuda"
+    model = AlbertForPreTraining(model_cfg, impl=cfg.impl if on_gpu else "torch")
+    if on_gpu:
+        # fp32 initial values become the master copy; the module itself computes in bf16
+        for p in model.parameters():
+            p._dedloc_master = p.detach().clone().to(device)
+        model = model.to(device=device, dtype=torch.bfloat16)
+        for p in model.parameters():
+            pass
+    groups = albert_param_groups(model, cfg.weight_decay)
+    if on_gpu:
+        opt = FusedLamb(groups, lr=cfg.learning_rate, betas=(0.9, 0.999), eps=cfg.adam_epsilon,
+                        weight_decay=cfg.weight_decay, clamp_value=cfg.clamp_value, debias=True)
+    else:
+        opt = Lamb(groups, lr=cfg.learning_rate, betas=(0.9, 0.999), eps=cfg.adam_epsilon,
+                   weight_decay=cfg.weight_decay, clamp_value=cfg.clamp_value, debias=True)
+    scheduler = get_linear_schedule_with_warmup(opt, cfg.warmup_steps, cfg.max_steps)
+    collab = CollaborativeOptimizer(
+        opt, dht=dht, prefix=cfg.prefix, target_batch_size=cfg.target_batch_size,
+        batch_size_per_step=cfg.micro_batch, scheduler=scheduler,
+        compression_type=CompressionType.Value(cfg.compression), target_group_size=cfg.target_group_size,
+        averaging_expiration=cfg.averaging_expiration, averaging_timeout=cfg.averaging_timeout,
+        metadata_expiration=cfg.metadata_expiration, min_refresh_period=cfg.min_refresh_period,
+        max_refresh_period=cfg.max_refresh_period, default_refresh_period=cfg.default_refresh_period,
+        client_mode=cfg.client_mode, max_grad_norm=cfg.max_grad_norm, peer_key=peer_key, **collab_kwargs)
+    model.train()
+    return PeerTrainer(model, opt, scheduler, collab, cfg, device)
