@@ -98,6 +98,11 @@ def _declare(lib: C.CDLL) -> None:
     lib.dedloc_codec_payload_bytes_per_elem.argtypes = [i]
     lib.dedloc_fused_allreduce.argtypes = [C.POINTER(ARParams), vp]
     lib.dedloc_gemm.argtypes = [C.POINTER(GemmArgs), vp]
+    lib.dedloc_layernorm_fwd.argtypes = [vp, vp, vp, vp, vp, vp, i, i, f, vp]
+    lib.dedloc_layernorm_bwd.argtypes = [vp, vp, vp, vp, vp, vp, vp, vp, i, i, vp]
+    lib.dedloc_colsum_accumulate.argtypes = [vp, vp, i, i, ll, vp]
+    for name in ("dedloc_layernorm_fwd", "dedloc_layernorm_bwd", "dedloc_colsum_accumulate"):
+        getattr(lib, name).restype = i
     for name in ("dedloc_symm_alloc", "dedloc_symm_open", "dedloc_symm_close", "dedloc_symm_free",
                  "dedloc_enable_peer_access", "dedloc_memset_async", "dedloc_memcpy_async",
                  "dedloc_memcpy_peer_async", "dedloc_sumsq", "dedloc_accumulate_clip", "dedloc_encode",

@@ -115,6 +115,14 @@ def fused_linear(x, lin: _Linear, impl: str, act: str = "none", residual=None):
     return y
 
 
+def _ln(x, ln: nn.LayerNorm, impl: str):
+    if impl == "native" and x.is_cuda:
+        from ..ops.layernorm import layer_norm
+
+        return layer_norm(x, ln, impl)
+    return ln(x)
+
+
 class AlbertEmbeddings(nn.Module):
     def __init__(self, cfg: AlbertConfig):
         super().__init__()
@@ -158,7 +166,7 @@ class AlbertAttention(nn.Module):
             y = F.dropout(fused_linear(ctx, self.dense, impl), self.out_dropout_p, True) + x
         else:
             y = fused_linear(ctx, self.dense, impl, residual=x)          # residual fused in the epilogue
-        return self.LayerNorm(y)
+        return _ln(y, self.LayerNorm, impl)
 
 
 class AlbertLayer(nn.Module):
@@ -172,12 +180,17 @@ class AlbertLayer(nn.Module):
 
     def forward(self, x, attn_bias, impl: str, fused_qkv=None):
         a = self.attention(x, attn_bias, impl, fused_qkv)
+        if (impl == "native" and a.is_cuda and _main_grad(self.ffn.weight) is not None
+                and not (self.dropout_p > 0 and self.training)):
+            from ..ops.gemm import ffn as native_ffn
+
+            return _ln(native_ffn(a, self.ffn, self.ffn_output, residual=a), self.full_layer_layer_norm, impl)
         h = fused_linear(a, self.ffn, impl, act="gelu")                  # gelu_new fused in the epilogue
         if self.dropout_p > 0 and self.training:
             y = F.dropout(fused_linear(h, self.ffn_output, impl), self.dropout_p, True) + a
         else:
             y = fused_linear(h, self.ffn_output, impl, residual=a)
-        return self.full_layer_layer_norm(y)
+        return _ln(y, self.full_layer_layer_norm, impl)
 
 
 class AlbertLayerGroup(nn.Module):

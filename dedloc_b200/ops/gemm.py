@@ -135,8 +135,67 @@ class _LinearFn(torch.autograd.Function):
         sk = pick_split_k(N, K, M, _sms(x2.device))
         gemm(dy2, x2, wg, a_mn_major=True, b_mn_major=True, accumulate=True, split_k=sk)
         if ctx.has_bias:
-            ctx.bgrad_out.add_(dy2.sum(dim=0, dtype=torch.float32))
+            _bias_grad(dy2, ctx.bgrad_out)
         return dx.view(ctx.x_shape), None, None, None, dres, None, None
+
+
+def _bias_grad(dy2: torch.Tensor, out: torch.Tensor) -> None:
+    if dy2.dtype == torch.bfloat16 and dy2.shape[1] % 8 == 0:
+        from .layernorm import colsum_accumulate
+
+        colsum_accumulate(dy2, out)
+    else:
+        out.add_(dy2.sum(dim=0, dtype=torch.float32))
+
+
+class _FFNFn(torch.autograd.Function):
+    """y = gelu_new(x W1^T + b1) W2^T + b2 (+ residual): ALBERT's feed-forward block (SURVEY C5 + C6) as ONE
+    autograd node, so that gelu' is fused into the epilogue of the dgrad GEMM of the second linear
+    (dpre = (dy W2) * gelu'(pre)) instead of being a separate pass over the [tokens, 4096] activation."""
+
+    @staticmethod
+    def forward(ctx, x, w1, b1, w2, b2, residual, g_w1, g_b1, g_w2, g_b2):
+        x2 = x.reshape(-1, x.shape[-1])
+        if not x2.is_contiguous():
+            x2 = x2.contiguous()
+        M, K = x2.shape
+        I, N = w1.shape[0], w2.shape[0]
+        pre = torch.empty(M, I, dtype=x.dtype, device=x.device)
+        h = torch.empty(M, I, dtype=x.dtype, device=x.device)
+        gemm(x2, w1, h, bias=b1, gelu=True, pre_out=pre)
+        out = torch.empty(M, N, dtype=x.dtype, device=x.device)
+        res2 = residual.reshape(M, N) if residual is not None else None
+        gemm(h, w2, out, bias=b2, residual=res2)
+        ctx.save_for_backward(x2, w1, w2, pre, h)
+        ctx.grads = (g_w1, g_b1, g_w2, g_b2)
+        ctx.has_res, ctx.x_shape = residual is not None, x.shape
+        return out.view(*x.shape[:-1], N)
+
+    @staticmethod
+    def backward(ctx, dy):
+        x2, w1, w2, pre, h = ctx.saved_tensors
+        g_w1, g_b1, g_w2, g_b2 = ctx.grads
+        M, K = x2.shape
+        I, N = w1.shape[0], w2.shape[0]
+        dy2 = dy.reshape(M, N)
+        if not dy2.is_contiguous():
+            dy2 = dy2.contiguous()
+        sms = _sms(x2.device)
+        dpre = torch.empty(M, I, dtype=x2.dtype, device=x2.device)
+        gemm(dy2, w2, dpre, b_mn_major=True, dgelu_aux=pre)                      # (dy W2) * gelu'(pre)
+        gemm(dy2, h, g_w2, a_mn_major=True, b_mn_major=True, accumulate=True, split_k=pick_split_k(N, I, M, sms))
+        _bias_grad(dy2, g_b2)
+        dx = torch.empty(M, K, dtype=x2.dtype, device=x2.device)
+        gemm(dpre, w1, dx, b_mn_major=True)
+        gemm(dpre, x2, g_w1, a_mn_major=True, b_mn_major=True, accumulate=True, split_k=pick_split_k(I, K, M, sms))
+        _bias_grad(dpre, g_b1)
+        return dx.view(ctx.x_shape), None, None, None, None, (dy if ctx.has_res else None), None, None, None, None
+
+
+def ffn(x, lin1, lin2, residual=None):
+    """Fused feed-forward block; `lin1` / `lin2` carry `.weight/.bias` with fp32 `.main_grad` buffers."""
+    return _FFNFn.apply(x, lin1.weight, lin1.bias, lin2.weight, lin2.bias, residual, lin1.weight.main_grad,
+                        lin1.bias.main_grad, lin2.weight.main_grad, lin2.bias.main_grad)
 
 
 def linear(x, weight, bias=None, *, act: str = "none", residual=None, wgrad_out=None, bgrad_out=None):

@@ -125,6 +125,14 @@ typedef struct DedlocGemmArgs {
 
 int dedloc_gemm(const DedlocGemmArgs* args, void* stream);
 
+/* ---- row-wise kernels around the GEMMs (torch LayerNorm / bias-gradient reductions under HF ALBERT) ----- */
+int dedloc_layernorm_fwd(const void* x, const void* gamma, const void* beta, void* y, float* mean, float* rstd,
+                         int M, int H, float eps, void* stream);
+/* dgamma / dbeta are fp32 and ACCUMULATED (weight sharing: 24 uses per step) */
+int dedloc_layernorm_bwd(const void* dy, const void* x, const void* gamma, const float* mean, const float* rstd,
+                         void* dx, float* dgamma, float* dbeta, int M, int H, void* stream);
+int dedloc_colsum_accumulate(const void* dy, float* out, int M, int N, long long ld, void* stream);
+
 #ifdef __cplusplus
 }
 #endif
