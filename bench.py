@@ -195,6 +195,15 @@ def main_ours(args):
         e2e = timed_region(args.steps, e2e=True)
 
     collab = trainer.collab
+    # all peers must hold bit-identical master parameters after the same sequence of collaborative steps
+    torch.cuda.synchronize()
+    p32 = trainer.opt.buffers.p32
+    digest = torch.stack([p32.double().sum(), p32.double().abs().sum(), (p32.double() ** 2).sum()])
+    in_sync = True
+    if world > 1:
+        gathered = [torch.zeros_like(digest) for _ in range(world)]
+        dist.all_gather(gathered, digest)
+        in_sync = all(bool(torch.equal(g, gathered[0])) for g in gathered)
     if rank == 0:
         value = dev["samples"] / (dev["dev_ms"] / 1e3)
         out = {
@@ -209,7 +218,8 @@ def main_ours(args):
                        "l2": "inputs larger than L2 (activations of one micro-batch >> 126 MB)",
                        "step": "one collaborative optimizer step (accumulate to target_batch_size, fused "
                                "all-reduce + LAMB)"},
-            "clocks": clocks, "gpu_launches": dev["launches"],
+            "clocks": clocks, "gpu_launches": dev["launches"], "params_in_sync": in_sync,
+            "local_step": collab.local_step,
             "collab": {"rounds": collab.stats["rounds"], "solo_rounds": collab.stats["solo_rounds"],
                        "failed_rounds": collab.stats["failed_rounds"],
                        "matchmaking_ms_per_round": round(1e3 * collab.stats["matchmaking_s"] / max(collab.stats["rounds"], 1), 2),

@@ -108,6 +108,8 @@ def test_albert_native_matches_torch_path(native):
     ref_grads = dict(ref.named_parameters())
     worst = 0.0
     for name, p in nat.named_parameters():
+        if name.endswith("key.bias"):
+            continue  # softmax is invariant to the key bias: its exact gradient is 0, both paths only hold noise
         total = p.grad.float() + p.main_grad
         g_ref = ref_grads[name].grad.float()
         denom = g_ref.norm().item() + 1e-6
