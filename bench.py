@@ -35,7 +35,7 @@ def parse_args():
     ap.add_argument("--seq-len", type=int, default=512)
     ap.add_argument("--target-batch-size", type=int, default=4096)
     ap.add_argument("--compression", default="FLOAT16")
-    ap.add_argument("--model", default="albert-large-v2", choices=["albert-large-v2", "albert-tiny"])
+    ap.add_argument("--model", default="albert-large-v2", choices=["albert-large-v2", "albert-small", "albert-tiny"])
     ap.add_argument("--ops", default="native", choices=["native", "torch"], help="linear layers: tcgen05 or torch")
     ap.add_argument("--skip-e2e", action="store_true")
     return ap.parse_args()
@@ -130,7 +130,8 @@ def main_ours(args):
     if rank != 0:
         dht = DHT(start=True, initial_peers=[f"127.0.0.1:{port[0]}"])
 
-    model_cfg = AlbertConfig.albert_large_v2() if args.model == "albert-large-v2" else AlbertConfig.tiny()
+    model_cfg = {"albert-large-v2": AlbertConfig.albert_large_v2, "albert-small": AlbertConfig.small,
+                 "albert-tiny": AlbertConfig.tiny}[args.model]()
     seq = min(args.seq_len, model_cfg.max_position_embeddings)
     cfg = PeerConfig(prefix="bench", target_batch_size=args.target_batch_size, micro_batch=args.micro_batch,
                      seq_len=seq, compression=args.compression, target_group_size=max(world, 2),
@@ -223,6 +224,7 @@ def main_ours(args):
             "collab": {"rounds": collab.stats["rounds"], "solo_rounds": collab.stats["solo_rounds"],
                        "failed_rounds": collab.stats["failed_rounds"],
                        "matchmaking_ms_per_round": round(1e3 * collab.stats["matchmaking_s"] / max(collab.stats["rounds"], 1), 2),
+                       "exposed_averaging_device_ms_per_round": round(collab.stats.get("averaging_device_ms", 0.0) / max(collab.stats.get("fused_rounds", 0), 1), 3),
                        "averaging_host_ms_per_round": round(1e3 * collab.stats["averaging_host_s"] / max(collab.stats["rounds"], 1), 2)},
         }
         if e2e is not None:

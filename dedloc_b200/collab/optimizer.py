@@ -378,6 +378,10 @@ class CollaborativeOptimizer:
         from ..ops import flat_ops
 
         buf = self.opt.buffers
+        # device-side bracket of the averaging work (encode + fused kernel): the "exposed averaging time"
+        self._avg_ev0 = torch.cuda.Event(enable_timing=True)
+        self._avg_ev1 = torch.cuda.Event(enable_timing=True)
+        self._avg_ev0.record(torch.cuda.current_stream(buf.device))
         scale = 1.0 / max(self.local_steps_accumulated, 1)
         flat_ops.encode(codec, buf.acc, scale, buf.send, buf.aux)
 
@@ -389,7 +393,10 @@ class CollaborativeOptimizer:
         hyper = opt.hyper()
         hyper.replicate_state = self.replicate_state
         fused_allreduce(opt.buffers, group_spec, codec, hyper, xgpu_barriers=len(group_spec.bases) > 1)
+        self._avg_ev1.record(torch.cuda.current_stream(opt.buffers.device))
         status = opt.buffers.read_status()
+        self.stats["averaging_device_ms"] = self.stats.get("averaging_device_ms", 0.0) + self._avg_ev0.elapsed_time(self._avg_ev1)
+        self.stats["fused_rounds"] = self.stats.get("fused_rounds", 0) + 1
         if status["code"] in (1, 2):
             opt.opt_step -= 1
         return status

@@ -64,6 +64,14 @@ class AlbertConfig:
         return cls(**d)
 
     @classmethod
+    def small(cls, **kw) -> "AlbertConfig":
+        """Small but tcgen05-friendly dimensions (every width a multiple of 64) for GPU smoke tests."""
+        d = dict(vocab_size=2048, embedding_size=128, hidden_size=256, num_hidden_layers=4, num_attention_heads=4,
+                 intermediate_size=1024, max_position_embeddings=128)
+        d.update(kw)
+        return cls(**d)
+
+    @classmethod
     def from_dict(cls, d: Dict) -> "AlbertConfig":
         known = {f for f in cls.__dataclass_fields__}
         return cls(**{k: v for k, v in d.items() if k in known})
@@ -98,11 +106,18 @@ def _main_grad(p: torch.Tensor) -> Optional[torch.Tensor]:
     return getattr(p, "main_grad", None)
 
 
+def _native_ok(x, lin, impl: str) -> bool:
+    """The tcgen05 GEMM needs every reduction dimension (in_features for forward, out_features for dgrad, tokens for
+    wgrad) to be a multiple of its 64-element K block."""
+    return (impl == "native" and x.is_cuda and x.dtype == torch.bfloat16 and _main_grad(lin.weight) is not None
+            and lin.in_features % 64 == 0 and lin.out_features % 64 == 0
+            and (x.numel() // lin.in_features) % 64 == 0)
+
+
 def fused_linear(x, lin: _Linear, impl: str, act: str = "none", residual=None):
     """y = act(x W^T + b) (+ residual) through the tcgen05 GEMM when impl == 'native' and the parameters carry
     fp32 `main_grad` buffers; otherwise plain PyTorch."""
-    if impl == "native" and x.is_cuda and _main_grad(lin.weight) is not None and lin.in_features % 64 == 0 \
-            and lin.out_features % 8 == 0:
+    if _native_ok(x, lin, impl):
         from ..ops.gemm import linear as native_linear
 
         return native_linear(x, lin.weight, lin.bias, act=act, residual=residual,
@@ -180,8 +195,8 @@ class AlbertLayer(nn.Module):
 
     def forward(self, x, attn_bias, impl: str, fused_qkv=None):
         a = self.attention(x, attn_bias, impl, fused_qkv)
-        if (impl == "native" and a.is_cuda and _main_grad(self.ffn.weight) is not None
-                and not (self.dropout_p > 0 and self.training)):
+        if (_native_ok(a, self.ffn, impl) and self.ffn_output.out_features % 64 == 0
+                and _main_grad(self.ffn_output.weight) is not None and not (self.dropout_p > 0 and self.training)):
             from ..ops.gemm import ffn as native_ffn
 
             return _ln(native_ffn(a, self.ffn, self.ffn_output, residual=a), self.full_layer_layer_norm, impl)
@@ -253,7 +268,7 @@ class AlbertModel(nn.Module):
             group = self.encoder.albert_layer_groups[i // layers_per_group]
             for j, layer in enumerate(group.albert_layers):
                 fq = None
-                use_fused = impl == "native" and x.is_cuda and _main_grad(layer.attention.query.weight) is not None
+                use_fused = _native_ok(x, layer.attention.query, impl)
                 if use_fused:
                     key = id(layer)
                     if key not in fused:
@@ -369,7 +384,7 @@ class AlbertForPreTraining(nn.Module):
             # gather the masked positions first (static capacity: no host sync, CUDA-graph friendly)
             flat_labels = labels.reshape(-1)
             is_masked = flat_labels != -100
-            cap = min(B * S, max(8, int(math.ceil(B * S * self.max_predictions_ratio / 8.0)) * 8))
+            cap = min(B * S, max(64, int(math.ceil(B * S * self.max_predictions_ratio / 64.0)) * 64))
             order = torch.argsort(is_masked.to(torch.int8), descending=True, stable=True)[:cap]
             sel_labels = flat_labels[order]
             sel_valid = is_masked[order]

@@ -17,7 +17,7 @@ def test_two_gpu_collaborative_steps(compression):
     port = 29500 + (os.getpid() % 400)
     cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node=2", "--master-addr",
            "127.0.0.1", "--master-port", str(port), os.path.join(ROOT, "bench.py"), "--gpus", "2", "--steps", "2",
-           "--warmup", "2", "--model", "albert-tiny", "--micro-batch", "8", "--target-batch-size", "64",
+           "--warmup", "2", "--model", "albert-small", "--micro-batch", "8", "--target-batch-size", "64",
            "--seq-len", "128", "--compression", compression, "--skip-e2e"]
     res = subprocess.run(cmd, capture_output=True, text=True, timeout=600, cwd=ROOT)
     assert res.returncode == 0, res.stdout[-3000:] + res.stderr[-3000:]
