@@ -16,8 +16,7 @@
 //               scaling -> bf16 or fp32 stores, or fp32 red.add for split-K weight-gradient accumulation
 // so the epilogue of tile i overlaps the mainloop of tile i+1 (double-buffered accumulators).
 #include <cuda.h>
-#include "common.cuh"
-#include "../include/dedloc_b200.h"
+#include "gemm_common.cuh"
 
 namespace dedloc {
 
@@ -26,26 +25,6 @@ constexpr int BM = 128;
 constexpr int BK = 64;  // 64 x 2 bytes = 128 B = one SWIZZLE_128B row
 constexpr int kStagesBN256 = 4;
 constexpr int kStagesBN128 = 6;
-
-struct GemmKernelParams {
-  int M, N, K;
-  int a_mn, b_mn;       // operand majors
-  int splits;           // split-K factor (output must be an atomic-add epilogue when > 1)
-  int kb_per_split;
-  int epi;              // DEDLOC_EPI_* flags
-  int out_kind;         // 0 bf16 store, 1 fp32 store, 2 fp32 atomic add
-  int fmt;              // 1 = bf16 inputs, 0 = fp16 inputs
-  float alpha;
-  void* C;              // [M, ldc]
-  long long ldc;
-  const void* bias;     // [N], bf16 or fp32 (epi flag)
-  const void* residual; // [M, ld_res] bf16
-  long long ld_res;
-  const void* aux_in;   // [M, ld_aux] bf16: pre-activation for the gelu' epilogue
-  long long ld_aux;
-  void* pre_out;        // [M, ld_pre] bf16: pre-activation saved by the forward gelu epilogue
-  long long ld_pre;
-};
 
 template <int BN>
 struct GemmSmem {
@@ -177,12 +156,6 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_con
     const int quad = warp & 3;  // TMEM lane quadrant this warp may read
     int acc = 0;
     uint32_t acc_phase = 0;
-    const bool has_bias = (p.epi & DEDLOC_EPI_BIAS) != 0;
-    const bool bias_f32 = (p.epi & DEDLOC_EPI_BIAS_F32) != 0;
-    const bool do_gelu = (p.epi & DEDLOC_EPI_GELU) != 0;
-    const bool do_dgelu = (p.epi & DEDLOC_EPI_DGELU) != 0;
-    const bool has_res = (p.epi & DEDLOC_EPI_RESIDUAL) != 0;
-    const bool save_pre = (p.epi & DEDLOC_EPI_SAVE_PRE) != 0;
     for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
       const int rem = tile % (m_tiles * n_tiles);
       const int m0 = (rem % m_tiles) * BM;
@@ -199,100 +172,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_con
         tmem_ld_wait();
         const int col0 = n0 + cb;
         if (col0 >= p.N) continue;  // warp-uniform
-        float v[32];
-#pragma unroll
-        for (int i = 0; i < 32; ++i) v[i] = __uint_as_float(r[i]) * p.alpha;
-        const bool full_cols = (col0 + 32 <= p.N);
-        if (has_bias) {
-          if (bias_f32) {
-            const float* b = reinterpret_cast<const float*>(p.bias) + col0;
-#pragma unroll
-            for (int i = 0; i < 32; ++i) if (full_cols || col0 + i < p.N) v[i] += __ldg(b + i);
-          } else {
-            const __nv_bfloat16* b = reinterpret_cast<const __nv_bfloat16*>(p.bias) + col0;
-#pragma unroll
-            for (int i = 0; i < 32; ++i) if (full_cols || col0 + i < p.N) v[i] += __bfloat162float(b[i]);
-          }
-        }
-        if (row_ok) {
-          if (save_pre) {
-            __nv_bfloat16* po = reinterpret_cast<__nv_bfloat16*>(p.pre_out) + (size_t)row * p.ld_pre + col0;
-            if (full_cols) {
-#pragma unroll
-              for (int i = 0; i < 32; i += 8)
-                *reinterpret_cast<uint4*>(po + i) = make_uint4(pack_bf16x2(v[i], v[i + 1]), pack_bf16x2(v[i + 2], v[i + 3]),
-                                                               pack_bf16x2(v[i + 4], v[i + 5]), pack_bf16x2(v[i + 6], v[i + 7]));
-            } else {
-              for (int i = 0; i < 32 && col0 + i < p.N; ++i) po[i] = __float2bfloat16(v[i]);
-            }
-          }
-          if (do_gelu) {
-#pragma unroll
-            for (int i = 0; i < 32; ++i) v[i] = gelu_tanh(v[i]);
-          }
-          if (do_dgelu) {
-            const __nv_bfloat16* ai = reinterpret_cast<const __nv_bfloat16*>(p.aux_in) + (size_t)row * p.ld_aux + col0;
-            if (full_cols) {
-#pragma unroll
-              for (int i = 0; i < 32; i += 8) {
-                const uint4 u = *reinterpret_cast<const uint4*>(ai + i);
-                float2 t;
-                t = unpack_bf16x2(u.x); v[i] *= gelu_tanh_grad(t.x); v[i + 1] *= gelu_tanh_grad(t.y);
-                t = unpack_bf16x2(u.y); v[i + 2] *= gelu_tanh_grad(t.x); v[i + 3] *= gelu_tanh_grad(t.y);
-                t = unpack_bf16x2(u.z); v[i + 4] *= gelu_tanh_grad(t.x); v[i + 5] *= gelu_tanh_grad(t.y);
-                t = unpack_bf16x2(u.w); v[i + 6] *= gelu_tanh_grad(t.x); v[i + 7] *= gelu_tanh_grad(t.y);
-              }
-            } else {
-              for (int i = 0; i < 32 && col0 + i < p.N; ++i) v[i] *= gelu_tanh_grad(__bfloat162float(ai[i]));
-            }
-          }
-          if (has_res) {
-            const __nv_bfloat16* rs = reinterpret_cast<const __nv_bfloat16*>(p.residual) + (size_t)row * p.ld_res + col0;
-            if (full_cols) {
-#pragma unroll
-              for (int i = 0; i < 32; i += 8) {
-                const uint4 u = *reinterpret_cast<const uint4*>(rs + i);
-                float2 t;
-                t = unpack_bf16x2(u.x); v[i] += t.x; v[i + 1] += t.y;
-                t = unpack_bf16x2(u.y); v[i + 2] += t.x; v[i + 3] += t.y;
-                t = unpack_bf16x2(u.z); v[i + 4] += t.x; v[i + 5] += t.y;
-                t = unpack_bf16x2(u.w); v[i + 6] += t.x; v[i + 7] += t.y;
-              }
-            } else {
-              for (int i = 0; i < 32 && col0 + i < p.N; ++i) v[i] += __bfloat162float(rs[i]);
-            }
-          }
-          if (p.out_kind == 0) {
-            __nv_bfloat16* co = reinterpret_cast<__nv_bfloat16*>(p.C) + (size_t)row * p.ldc + col0;
-            if (full_cols) {
-#pragma unroll
-              for (int i = 0; i < 32; i += 8)
-                *reinterpret_cast<uint4*>(co + i) = make_uint4(pack_bf16x2(v[i], v[i + 1]), pack_bf16x2(v[i + 2], v[i + 3]),
-                                                               pack_bf16x2(v[i + 4], v[i + 5]), pack_bf16x2(v[i + 6], v[i + 7]));
-            } else {
-              for (int i = 0; i < 32 && col0 + i < p.N; ++i) co[i] = __float2bfloat16(v[i]);
-            }
-          } else if (p.out_kind == 1) {
-            float* co = reinterpret_cast<float*>(p.C) + (size_t)row * p.ldc + col0;
-            if (full_cols) {
-#pragma unroll
-              for (int i = 0; i < 32; i += 4) *reinterpret_cast<float4*>(co + i) = make_float4(v[i], v[i + 1], v[i + 2], v[i + 3]);
-            } else {
-              for (int i = 0; i < 32 && col0 + i < p.N; ++i) co[i] = v[i];
-            }
-          } else {
-            float* co = reinterpret_cast<float*>(p.C) + (size_t)row * p.ldc + col0;
-            if (full_cols) {
-#pragma unroll
-              for (int i = 0; i < 32; i += 4)
-                asm volatile("red.global.add.v4.f32 [%0], {%1,%2,%3,%4};" ::"l"(co + i), "f"(v[i]), "f"(v[i + 1]),
-                             "f"(v[i + 2]), "f"(v[i + 3])
-                             : "memory");
-            } else {
-              for (int i = 0; i < 32 && col0 + i < p.N; ++i) atomicAdd(co + i, v[i]);
-            }
-          }
-        }
+        gemm_epilogue_32cols(p, row, row_ok, col0, r);
       }
       tc_fence_before();
       __syncwarp();
@@ -352,6 +232,20 @@ int make_tmap_2d_16bit(CUtensorMap* map, const void* base, long long rows, long 
   return 0;
 }
 
+// cuTensorMapEncodeTiled is a driver call: it needs a context bound to THIS thread (autograd's backward threads
+// have none until a runtime call binds the primary context).
+int bind_context_for_driver_calls() {
+  static thread_local bool ctx_bound = false;
+  if (!ctx_bound) {
+    int dev = 0;
+    DEDLOC_CUDA_CHECK(cudaGetDevice(&dev));
+    DEDLOC_CUDA_CHECK(cudaSetDevice(dev));
+    DEDLOC_CUDA_CHECK(cudaFree(0));
+    ctx_bound = true;
+  }
+  return 0;
+}
+
 template <int BN>
 static int launch_gemm(const DedlocGemmArgs& g, cudaStream_t st) {
   GemmKernelParams kp;
@@ -371,16 +265,7 @@ static int launch_gemm(const DedlocGemmArgs& g, cudaStream_t st) {
   kp.kb_per_split = kb_per;
   DEDLOC_REQUIRE(splits == 1 || g.out_kind == 2, "gemm: split-K needs the fp32 atomic-add output");
 
-  // cuTensorMapEncodeTiled is a driver call: it needs a context bound to THIS thread (autograd's backward
-  // threads have none until a runtime call binds the primary context).
-  static thread_local bool ctx_bound = false;
-  if (!ctx_bound) {
-    int dev = 0;
-    DEDLOC_CUDA_CHECK(cudaGetDevice(&dev));
-    DEDLOC_CUDA_CHECK(cudaSetDevice(dev));
-    DEDLOC_CUDA_CHECK(cudaFree(0));
-    ctx_bound = true;
-  }
+  { int rc0 = bind_context_for_driver_calls(); if (rc0) return rc0; }
   CUtensorMap ta, tb;
   int rc;
   if (!g.a_mn_major) rc = make_tmap_2d_16bit(&ta, g.A, g.M, g.K, g.lda, BK, BM, !g.is_fp16);
@@ -412,6 +297,7 @@ static int launch_gemm(const DedlocGemmArgs& g, cudaStream_t st) {
 
 }  // namespace dedloc
 
+namespace dedloc { int launch_gemm_2cta(const DedlocGemmArgs& g, cudaStream_t st); }
 using namespace dedloc;
 
 extern "C" int dedloc_gemm(const DedlocGemmArgs* gp, void* stream) {
@@ -425,6 +311,13 @@ extern "C" int dedloc_gemm(const DedlocGemmArgs* gp, void* stream) {
   DEDLOC_REQUIRE(g.ldc % 8 == 0, "gemm: ldc must be a multiple of 8");
   if (g.a_mn_major) DEDLOC_REQUIRE(g.M % 8 == 0, "gemm: MN-major A needs M %% 8 == 0");
   cudaStream_t st = (cudaStream_t)stream;
+  // CTA pairs halve the L2->SMEM traffic of the B operand; worth it once the problem fills 74 pairs
+  const bool pair_ok = g.block_n != 128 && g.N > 128;
+  const long long tiles_2cta = (long long)((g.M + 255) / 256) * ((g.N + 255) / 256) * (g.split_k > 1 ? g.split_k : 1);
+  if (g.cta_pair == 2 || (g.cta_pair == 0 && pair_ok && tiles_2cta >= 64)) {
+    DEDLOC_REQUIRE(pair_ok, "gemm: the CTA-pair kernel needs N > 128 and block_n != 128");
+    return launch_gemm_2cta(g, st);
+  }
   const int bn = g.block_n ? g.block_n : (g.N <= 128 ? 128 : 256);
   if (bn == 128) return launch_gemm<128>(g, st);
   if (bn == 256) return launch_gemm<256>(g, st);

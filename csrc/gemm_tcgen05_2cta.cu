@@ -1,0 +1,281 @@
+// 2-CTA (cta_group::2) variant of the tcgen05 GEMM: a CTA pair on one TPC computes a 256 x 256 output tile.
+//
+// Why: with one CTA per 128 x 256 tile every CTA streams its own A (16 KB) and B (32 KB) per 64-wide k-block --
+// 85 FLOP per byte of L2->SMEM traffic, and the v1 kernel measured ~0.9-1.1 PFLOP/s, i.e. bound by the L2 fabric
+// (~6300 B/clk chip-wide), not by the tensor cores. Pairing two CTAs lets each one load ITS 128 rows of A and only
+// HALF of B (128 of the 256 columns); tcgen05.mma.cta_group::2 reads both halves across the pair: 128 FLOP/byte.
+//
+// Roles per CTA (256 threads): warp 0 TMA producer (both CTAs; transaction bytes of both land on the LEADER's
+// full barrier), warp 1 MMA issuer (leader CTA only; tcgen05.commit multicasts to both CTAs' barriers), warp 2
+// TMEM allocator (cta_group::2, both CTAs), warps 4..7 epilogue (each CTA drains its own 128 accumulator rows and
+// arrives on the leader's tmem_empty barrier). Same operand layouts / fused epilogues as gemm_tcgen05.cu.
+#include "gemm_common.cuh"
+
+namespace dedloc {
+
+constexpr int k2Threads = 256;
+constexpr int k2BM = 128;       // rows per CTA (256 per pair)
+constexpr int k2BN = 256;       // columns per pair; each CTA stages 128 of them
+constexpr int k2BK = 64;
+constexpr int k2Stages = 6;
+constexpr int k2ABytes = k2BM * k2BK * 2;          // 16 KB
+constexpr int k2BBytes = (k2BN / 2) * k2BK * 2;    // 16 KB
+constexpr int k2StageBytes = k2ABytes + k2BBytes;  // 32 KB per CTA per stage
+constexpr int k2SmemTotal = k2Stages * k2StageBytes + 256 + 1024;
+constexpr uint32_t kPeerBitMask = 0xFEFFFFFFu;     // clears the CTA-pair bit of a shared::cluster address
+
+__device__ __forceinline__ uint32_t cluster_ctarank() {
+  uint32_t r;
+  asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r));
+  return r;
+}
+__device__ __forceinline__ void cluster_sync_all() {
+  asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory");
+  asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory");
+}
+__device__ __forceinline__ void tma_load_2d_2sm(void* smem_dst, const void* tmap, uint64_t* leader_bar, int c0, int c1) {
+  const uint32_t bar = smem_u32(leader_bar) & kPeerBitMask;   // transaction bytes update CTA 0's barrier
+  asm volatile(
+      "cp.async.bulk.tensor.2d.cta_group::2.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];"
+      ::"r"(smem_u32(smem_dst)), "l"(tmap), "r"(bar), "r"(c0), "r"(c1)
+      : "memory");
+}
+__device__ __forceinline__ void umma_f16_ss_2cta(uint32_t tmem_d, uint64_t desc_a, uint64_t desc_b, uint32_t idesc,
+                                                 uint32_t accumulate) {
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "setp.ne.b32 p, %4, 0;\n\t"
+      "tcgen05.mma.cta_group::2.kind::f16 [%0], %1, %2, %3, p;\n\t}" ::"r"(tmem_d),
+      "l"(desc_a), "l"(desc_b), "r"(idesc), "r"(accumulate)
+      : "memory");
+}
+// arrive (once MMAs retire) on the barrier at this smem offset in BOTH CTAs of the pair
+__device__ __forceinline__ void umma_commit_2cta_mc(uint64_t* bar) {
+  const uint16_t mask = 0b11;
+  asm volatile("tcgen05.commit.cta_group::2.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;"
+               ::"r"(smem_u32(bar)), "h"(mask)
+               : "memory");
+}
+// arrive on the barrier at this smem offset in CTA 0 of the pair
+__device__ __forceinline__ void mbar_arrive_leader(uint64_t* bar) {
+  const uint32_t addr = smem_u32(bar) & kPeerBitMask;
+  asm volatile("mbarrier.arrive.shared::cluster.b64 _, [%0];" ::"r"(addr) : "memory");
+}
+__device__ __forceinline__ void tmem_alloc_2cta(uint32_t* smem_dst, uint32_t ncols) {
+  asm volatile("tcgen05.alloc.cta_group::2.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(smem_dst)), "r"(ncols)
+               : "memory");
+  asm volatile("tcgen05.relinquish_alloc_permit.cta_group::2.sync.aligned;" ::: "memory");
+}
+__device__ __forceinline__ void tmem_dealloc_2cta(uint32_t taddr, uint32_t ncols) {
+  asm volatile("tcgen05.dealloc.cta_group::2.sync.aligned.b32 %0, %1;" ::"r"(taddr), "r"(ncols) : "memory");
+}
+
+__global__ void __launch_bounds__(k2Threads, 1)
+gemm_tcgen05_2cta_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b,
+                         const __grid_constant__ GemmKernelParams p) {
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + k2Stages * k2StageBytes);
+  uint64_t* full_bar = bars;                        // [k2Stages]  (leader's copy is the live one)
+  uint64_t* empty_bar = bars + k2Stages;            // [k2Stages]  (live in both CTAs)
+  uint64_t* tmem_full = bars + 2 * k2Stages;        // [2]         (live in both CTAs)
+  uint64_t* tmem_empty = bars + 2 * k2Stages + 2;   // [2]         (leader's copy is the live one)
+  uint32_t* tmem_base_slot = reinterpret_cast<uint32_t*>(bars + 2 * k2Stages + 4);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const uint32_t cta_rank = cluster_ctarank();
+  const bool leader = cta_rank == 0;
+  const int cluster_id = blockIdx.x >> 1, num_clusters = gridDim.x >> 1;
+
+  const int m_tiles = (p.M + 2 * k2BM - 1) / (2 * k2BM);
+  const int n_tiles = (p.N + k2BN - 1) / k2BN;
+  const int kb_total = p.K / k2BK;
+  const int total_tiles = m_tiles * n_tiles * p.splits;
+
+  if (warp == 0 && lane == 0) {
+    tma_prefetch_desc(&tmap_a);
+    tma_prefetch_desc(&tmap_b);
+  }
+  if (warp == 1 && lane == 0) {
+    for (int s = 0; s < k2Stages; ++s) { mbar_init(&full_bar[s], 1); mbar_init(&empty_bar[s], 1); }
+    for (int s = 0; s < 2; ++s) { mbar_init(&tmem_full[s], 1); mbar_init(&tmem_empty[s], 8); }
+    mbar_fence_init();
+  }
+  if (warp == 2) tmem_alloc_2cta(tmem_base_slot, 2 * k2BN);
+  tc_fence_before();
+  __syncthreads();
+  cluster_sync_all();   // the peer's barriers are initialised before any remote arrive / complete_tx targets them
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_base_slot;
+
+  if (warp == 0) {
+    // ===================== TMA producer (both CTAs) =====================
+    if (lane == 0) {
+      int stage = 0;
+      uint32_t phase = 0;
+      for (int tile = cluster_id; tile < total_tiles; tile += num_clusters) {
+        const int split = tile / (m_tiles * n_tiles);
+        const int rem = tile - split * (m_tiles * n_tiles);
+        const int m0 = (rem % m_tiles) * (2 * k2BM) + (int)cta_rank * k2BM;
+        const int n0 = (rem / m_tiles) * k2BN + (int)cta_rank * (k2BN / 2);
+        const int kb0 = split * p.kb_per_split;
+        const int kb1 = min(kb_total, kb0 + p.kb_per_split);
+        for (int kb = kb0; kb < kb1; ++kb) {
+          mbar_wait(&empty_bar[stage], phase ^ 1);
+          uint8_t* sa = smem + stage * k2StageBytes;
+          uint8_t* sb = sa + k2ABytes;
+          if (leader) mbar_expect_tx(&full_bar[stage], 2 * k2StageBytes);
+          const int k0 = kb * k2BK;
+          if (!p.a_mn) {
+            tma_load_2d_2sm(sa, &tmap_a, &full_bar[stage], k0, m0);
+          } else {
+#pragma unroll
+            for (int i = 0; i < k2BM / 64; ++i)
+              tma_load_2d_2sm(sa + i * (k2BK * 128), &tmap_a, &full_bar[stage], m0 + 64 * i, k0);
+          }
+          if (!p.b_mn) {
+            tma_load_2d_2sm(sb, &tmap_b, &full_bar[stage], k0, n0);
+          } else {
+#pragma unroll
+            for (int i = 0; i < (k2BN / 2) / 64; ++i)
+              tma_load_2d_2sm(sb + i * (k2BK * 128), &tmap_b, &full_bar[stage], n0 + 64 * i, k0);
+          }
+          if (++stage == k2Stages) { stage = 0; phase ^= 1; }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ===================== MMA issuer (leader CTA only) =====================
+    if (leader) {
+      const uint32_t idesc = make_idesc_f16(2 * k2BM, k2BN, p.a_mn, p.b_mn, p.fmt);
+      int stage = 0;
+      uint32_t phase = 0;
+      int acc = 0;
+      uint32_t acc_phase = 0;
+      for (int tile = cluster_id; tile < total_tiles; tile += num_clusters) {
+        const int split = tile / (m_tiles * n_tiles);
+        const int kb0 = split * p.kb_per_split;
+        const int kb1 = min(kb_total, kb0 + p.kb_per_split);
+        mbar_wait(&tmem_empty[acc], acc_phase ^ 1);
+        tc_fence_after();
+        const uint32_t tmem_d = tmem_base + acc * k2BN;
+        for (int kb = kb0; kb < kb1; ++kb) {
+          mbar_wait(&full_bar[stage], phase);
+          tc_fence_after();
+          if (lane == 0) {
+            const uint32_t sa = smem_u32(smem + stage * k2StageBytes);
+            const uint32_t sb = sa + k2ABytes;
+#pragma unroll
+            for (int j = 0; j < k2BK / 16; ++j) {
+              const uint64_t da = p.a_mn ? make_smem_desc_sw128(sa + j * 2048, k2BK * 128, 1024)
+                                         : make_smem_desc_sw128(sa + j * 32, 16, 1024);
+              const uint64_t db = p.b_mn ? make_smem_desc_sw128(sb + j * 2048, k2BK * 128, 1024)
+                                         : make_smem_desc_sw128(sb + j * 32, 16, 1024);
+              umma_f16_ss_2cta(tmem_d, da, db, idesc, (kb > kb0 || j > 0) ? 1u : 0u);
+            }
+            umma_commit_2cta_mc(&empty_bar[stage]);                    // frees this stage in BOTH CTAs
+            if (kb == kb1 - 1) umma_commit_2cta_mc(&tmem_full[acc]);   // accumulators ready in BOTH CTAs
+          }
+          __syncwarp();
+          if (++stage == k2Stages) { stage = 0; phase ^= 1; }
+        }
+        if (++acc == 2) { acc = 0; acc_phase ^= 1; }
+      }
+    }
+  } else if (warp >= 4) {
+    // ===================== epilogue (both CTAs, own 128 rows) =====================
+    const int quad = warp & 3;
+    int acc = 0;
+    uint32_t acc_phase = 0;
+    for (int tile = cluster_id; tile < total_tiles; tile += num_clusters) {
+      const int rem = tile % (m_tiles * n_tiles);
+      const int m0 = (rem % m_tiles) * (2 * k2BM) + (int)cta_rank * k2BM;
+      const int n0 = (rem / m_tiles) * k2BN;
+      mbar_wait(&tmem_full[acc], acc_phase);
+      tc_fence_after();
+      const int row = m0 + quad * 32 + lane;
+      const bool row_ok = row < p.M;
+      const uint32_t taddr = tmem_base + ((uint32_t)(quad * 32) << 16) + acc * k2BN;
+#pragma unroll 1
+      for (int cb = 0; cb < k2BN; cb += 32) {
+        uint32_t r[32];
+        tmem_ld_32x32b_x32(taddr + cb, r);
+        tmem_ld_wait();
+        const int col0 = n0 + cb;
+        if (col0 >= p.N) continue;  // warp-uniform
+        gemm_epilogue_32cols(p, row, row_ok, col0, r);
+      }
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive_leader(&tmem_empty[acc]);
+      if (++acc == 2) { acc = 0; acc_phase ^= 1; }
+    }
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  cluster_sync_all();   // both CTAs are done with tensor memory and with each other's barriers
+  if (warp == 2) {
+    tc_fence_after();
+    tmem_dealloc_2cta(tmem_base, 2 * k2BN);
+  }
+}
+
+int launch_gemm_2cta(const DedlocGemmArgs& g, cudaStream_t st) {
+  GemmKernelParams kp;
+  kp.M = g.M; kp.N = g.N; kp.K = g.K;
+  kp.a_mn = g.a_mn_major; kp.b_mn = g.b_mn_major;
+  kp.epi = g.epilogue; kp.out_kind = g.out_kind; kp.fmt = g.is_fp16 ? 0 : 1;
+  kp.alpha = g.alpha;
+  kp.C = g.C; kp.ldc = g.ldc;
+  kp.bias = g.bias; kp.residual = g.residual; kp.ld_res = g.ld_residual;
+  kp.aux_in = g.aux_in; kp.ld_aux = g.ld_aux; kp.pre_out = g.pre_out; kp.ld_pre = g.ld_pre;
+  const int kb_total = g.K / k2BK;
+  int splits = g.split_k < 1 ? 1 : g.split_k;
+  if (splits > kb_total) splits = kb_total;
+  const int kb_per = (kb_total + splits - 1) / splits;
+  splits = (kb_total + kb_per - 1) / kb_per;
+  kp.splits = splits;
+  kp.kb_per_split = kb_per;
+  DEDLOC_REQUIRE(splits == 1 || g.out_kind == 2, "gemm: split-K needs the fp32 atomic-add output");
+  { int rc0 = bind_context_for_driver_calls(); if (rc0) return rc0; }
+
+  CUtensorMap ta, tb;
+  int rc;
+  if (!g.a_mn_major) rc = make_tmap_2d_16bit(&ta, g.A, g.M, g.K, g.lda, k2BK, k2BM, !g.is_fp16);
+  else rc = make_tmap_2d_16bit(&ta, g.A, g.K, g.M, g.lda, 64, k2BK, !g.is_fp16);
+  if (rc) return rc;
+  if (!g.b_mn_major) rc = make_tmap_2d_16bit(&tb, g.B, g.N, g.K, g.ldb, k2BK, k2BN / 2, !g.is_fp16);
+  else rc = make_tmap_2d_16bit(&tb, g.B, g.K, g.N, g.ldb, 64, k2BK, !g.is_fp16);
+  if (rc) return rc;
+
+  static int sms = 0;
+  if (sms == 0) {
+    int dev = 0;
+    DEDLOC_CUDA_CHECK(cudaGetDevice(&dev));
+    DEDLOC_CUDA_CHECK(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
+    DEDLOC_CUDA_CHECK(cudaFuncSetAttribute(gemm_tcgen05_2cta_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                           k2SmemTotal));
+  }
+  const int m_tiles = (g.M + 2 * k2BM - 1) / (2 * k2BM), n_tiles = (g.N + k2BN - 1) / k2BN;
+  const int total = m_tiles * n_tiles * splits;
+  int clusters = total < sms / 2 ? total : sms / 2;
+  if (g.max_ctas > 0 && g.max_ctas / 2 < clusters) clusters = g.max_ctas / 2 > 0 ? g.max_ctas / 2 : 1;
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3(2 * clusters);
+  cfg.blockDim = dim3(k2Threads);
+  cfg.dynamicSmemBytes = k2SmemTotal;
+  cfg.stream = st;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeClusterDimension;
+  attr[0].val.clusterDim.x = 2;
+  attr[0].val.clusterDim.y = 1;
+  attr[0].val.clusterDim.z = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = 1;
+  DEDLOC_CUDA_CHECK(cudaLaunchKernelEx(&cfg, gemm_tcgen05_2cta_kernel, ta, tb, kp));
+  count_launch();
+  return 0;
+}
+
+}  // namespace dedloc

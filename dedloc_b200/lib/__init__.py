@@ -64,7 +64,7 @@ class GemmArgs(C.Structure):
         ("bias", C.c_void_p), ("residual", C.c_void_p), ("ld_residual", C.c_longlong),
         ("aux_in", C.c_void_p), ("ld_aux", C.c_longlong),
         ("pre_out", C.c_void_p), ("ld_pre", C.c_longlong),
-        ("split_k", C.c_int), ("block_n", C.c_int), ("max_ctas", C.c_int),
+        ("split_k", C.c_int), ("block_n", C.c_int), ("max_ctas", C.c_int), ("cta_pair", C.c_int),
     ]
 
 

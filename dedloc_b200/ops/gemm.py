@@ -29,7 +29,7 @@ def gemm(a: torch.Tensor, b: torch.Tensor, out: torch.Tensor, *, a_mn_major: boo
          b_mn_major: bool = False, bias: Optional[torch.Tensor] = None, gelu: bool = False,
          dgelu_aux: Optional[torch.Tensor] = None, residual: Optional[torch.Tensor] = None,
          pre_out: Optional[torch.Tensor] = None, accumulate: bool = False, alpha: float = 1.0,
-         split_k: int = 1, block_n: int = 0, max_ctas: int = 0) -> torch.Tensor:
+         split_k: int = 1, block_n: int = 0, max_ctas: int = 0, cta_pair: int = 0) -> torch.Tensor:
     """out[M,N] = epilogue(A . B^T).
 
     a: [M,K] (K-major) or [K,M] (a_mn_major); b: [N,K] (K-major, nn.Linear weight) or [K,N] (b_mn_major).
@@ -75,7 +75,7 @@ def gemm(a: torch.Tensor, b: torch.Tensor, out: torch.Tensor, *, a_mn_major: boo
         assert out.dtype == torch.float32
         g.out_kind = native.OUT_F32_ATOMIC if accumulate else native.OUT_F32
     g.alpha = alpha
-    g.split_k, g.block_n, g.max_ctas = split_k, block_n, max_ctas
+    g.split_k, g.block_n, g.max_ctas, g.cta_pair = split_k, block_n, max_ctas, cta_pair
     with torch.cuda.device(a.device):
         native.check(native.lib().dedloc_gemm(C.byref(g), torch.cuda.current_stream(a.device).cuda_stream), "gemm")
     return out

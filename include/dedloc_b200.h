@@ -121,6 +121,7 @@ typedef struct DedlocGemmArgs {
   int split_k;        /* >1 only with out_kind == 2 */
   int block_n;        /* 0 = auto, 128 or 256 */
   int max_ctas;       /* 0 = one per SM */
+  int cta_pair;       /* 0 = auto, 1 = one CTA per 128x256 tile, 2 = CTA pair (cta_group::2) per 256x256 tile */
 } DedlocGemmArgs;
 
 int dedloc_gemm(const DedlocGemmArgs* args, void* stream);

@@ -46,6 +46,7 @@ def main():
         sk = pick_split_k(N, K, M, 148)
         res = {"name": name, "M": M, "N": N, "K": K}
         for tag, ours, ref in [
+            ("fwd_1cta", lambda: gemm(a, w, out, cta_pair=1), lambda: torch.matmul(a, w.t())),
             ("fwd", lambda: gemm(a, w, out), lambda: torch.matmul(a, w.t())),
             ("dgrad", lambda: gemm(dy, w, dx, b_mn_major=True), lambda: torch.matmul(dy, w)),
             ("wgrad", lambda: gemm(dy, a, wg, a_mn_major=True, b_mn_major=True, accumulate=True, split_k=sk),

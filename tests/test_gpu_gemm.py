@@ -38,6 +38,28 @@ def test_gemm_layouts(native, a_mn, b_mn, M, N, K):
     _check(out32, ref, "fp32 out", rtol=1e-3, atol=1e-3)
 
 
+@pytest.mark.parametrize("a_mn,b_mn", [(False, False), (False, True), (True, False), (True, True)])
+@pytest.mark.parametrize("M,N,K", [(512, 512, 128), (768, 1024, 320), (1000, 776, 192), (4096, 3072, 1024)])
+def test_gemm_cta_pair_layouts(native, a_mn, b_mn, M, N, K):
+    """cta_group::2 kernel (256 x 256 tile per CTA pair): every operand layout, M/N tails, bias+gelu epilogue."""
+    from dedloc_b200.ops.elementwise import gelu_new
+    from dedloc_b200.ops.gemm import gemm
+
+    a = _rand((K, M) if a_mn else (M, K), 21, 0.5)
+    b = _rand((K, N) if b_mn else (N, K), 22, 0.5)
+    bias = _rand((N,), 23, 0.5)
+    ref = (a.float().t() if a_mn else a.float()) @ (b.float() if b_mn else b.float().t())
+    out = torch.empty(M, N, dtype=torch.bfloat16, device="cuda")
+    gemm(a, b, out, a_mn_major=a_mn, b_mn_major=b_mn, cta_pair=2)
+    torch.cuda.synchronize()
+    _check(out, ref, f"2cta a_mn={a_mn} b_mn={b_mn} {M}x{N}x{K}")
+    gemm(a, b, out, a_mn_major=a_mn, b_mn_major=b_mn, cta_pair=2, bias=bias, gelu=True)
+    _check(out, gelu_new(ref + bias.float()), "2cta bias+gelu")
+    acc = torch.ones(M, N, dtype=torch.float32, device="cuda")
+    gemm(a, b, acc, a_mn_major=a_mn, b_mn_major=b_mn, cta_pair=2, accumulate=True, split_k=2 if K >= 128 else 1)
+    _check(acc, 1.0 + ref, "2cta split-k accumulate", rtol=1e-3, atol=1e-3)
+
+
 def test_gemm_block_n_128_and_fp16(native):
     from dedloc_b200.ops.gemm import gemm
 
