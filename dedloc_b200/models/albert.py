@@ -461,3 +461,53 @@ class AlbertForPreTraining(nn.Module):
 
     def num_parameters(self) -> int:
         return sum(p.numel() for p in self.parameters())
+
+
+class AlbertForTokenClassification(nn.Module):
+    """Encoder + per-token linear classifier (HF names: `albert.*`, `classifier.*`); used by train_ner.py."""
+
+    def __init__(self, cfg: AlbertConfig, num_labels: int, impl: str = "torch"):
+        super().__init__()
+        self.config, self.impl, self.num_labels = cfg, impl, num_labels
+        self.albert = AlbertModel(cfg)
+        self.dropout_p = cfg.classifier_dropout_prob
+        self.classifier = _Linear(cfg.hidden_size, num_labels)
+        self._pending_flush: list = []
+        self.apply(lambda m: AlbertForPreTraining._init_weights(self, m))
+
+    def forward(self, input_ids, attention_mask=None, token_type_ids=None, labels=None):
+        if token_type_ids is None:
+            token_type_ids = torch.zeros_like(input_ids)
+        seq, _ = self.albert(input_ids, attention_mask, token_type_ids, self.impl, self._pending_flush)
+        logits = F.linear(F.dropout(seq, self.dropout_p, self.training), self.classifier.weight, self.classifier.bias)
+        loss = None
+        if labels is not None:
+            loss = F.cross_entropy(logits.float().view(-1, self.num_labels), labels.view(-1), ignore_index=-100)
+        return AlbertPreTrainingOutput(loss=loss, prediction_logits=logits)
+
+    def load_encoder_from(self, pretrained: "AlbertForPreTraining") -> None:
+        self.albert.load_state_dict(pretrained.albert.state_dict())
+
+
+class AlbertForSequenceClassification(nn.Module):
+    """Encoder + pooled-output classifier (HF names: `albert.*`, `classifier.*`); used by train_ncc.py."""
+
+    def __init__(self, cfg: AlbertConfig, num_labels: int, impl: str = "torch"):
+        super().__init__()
+        self.config, self.impl, self.num_labels = cfg, impl, num_labels
+        self.albert = AlbertModel(cfg)
+        self.dropout_p = cfg.classifier_dropout_prob
+        self.classifier = _Linear(cfg.hidden_size, num_labels)
+        self._pending_flush: list = []
+        self.apply(lambda m: AlbertForPreTraining._init_weights(self, m))
+
+    def forward(self, input_ids, attention_mask=None, token_type_ids=None, labels=None):
+        if token_type_ids is None:
+            token_type_ids = torch.zeros_like(input_ids)
+        _, pooled = self.albert(input_ids, attention_mask, token_type_ids, self.impl, self._pending_flush)
+        logits = F.linear(F.dropout(pooled, self.dropout_p, self.training), self.classifier.weight, self.classifier.bias)
+        loss = F.cross_entropy(logits.float(), labels.view(-1)) if labels is not None else None
+        return AlbertPreTrainingOutput(loss=loss, prediction_logits=logits)
+
+    def load_encoder_from(self, pretrained: "AlbertForPreTraining") -> None:
+        self.albert.load_state_dict(pretrained.albert.state_dict())
