@@ -101,6 +101,10 @@ def _declare(lib: C.CDLL) -> None:
     lib.dedloc_layernorm_fwd.argtypes = [vp, vp, vp, vp, vp, vp, i, i, f, vp]
     lib.dedloc_layernorm_bwd.argtypes = [vp, vp, vp, vp, vp, vp, vp, vp, i, i, vp]
     lib.dedloc_colsum_accumulate.argtypes = [vp, vp, i, i, ll, vp]
+    lib.dedloc_sinkhorn_scratch_floats.argtypes = [i, i]
+    lib.dedloc_sinkhorn_scratch_floats.restype = ll
+    lib.dedloc_sinkhorn.argtypes = [vp, i, ll, i, i, i, f, i, f, vp, ll, vp, vp]
+    lib.dedloc_sinkhorn.restype = i
     for name in ("dedloc_layernorm_fwd", "dedloc_layernorm_bwd", "dedloc_colsum_accumulate"):
         getattr(lib, name).restype = i
     for name in ("dedloc_symm_alloc", "dedloc_symm_open", "dedloc_symm_close", "dedloc_symm_free",

@@ -1,0 +1,248 @@
+"""Hooks of the collaborative SwAV run (everything enabled by W4 through vissl/hooks/__init__.py:72-146):
+
+SwAVUpdateQueueScoresHook, NormalizePrototypesHook (swav_hooks.py:11-92), CheckNanLossHook, FreezeParametersHook
+(state_update_hooks.py:207-280), UpdateBatchesSeenHook / UpdateTrainIterationNumHook / UpdateTrainBatchTimeHook,
+LogLossLrEtaHook, LogPerfTimeMetricsHook, LogGpuStatsHook, LogGpuMemoryHook, LogLossMetricsCheckpointHook
+(log_hooks.py), SSLTensorboardHook. Hook points follow ClassyHook: on_start, on_forward, on_loss_and_meter,
+on_backward, on_update, on_step, on_phase_end, on_end."""
+from __future__ import annotations
+
+import json
+import logging
+import os
+import subprocess
+import time
+from typing import List
+
+import torch
+
+from ...models.swav import normalize_prototypes
+
+logger = logging.getLogger(__name__)
+
+
+class ClassyHook:
+    def on_start(self, task): pass
+    def on_phase_start(self, task): pass
+    def on_forward(self, task): pass
+    def on_loss_and_meter(self, task): pass
+    def on_backward(self, task): pass
+    def on_update(self, task): pass
+    def on_step(self, task): pass
+    def on_phase_end(self, task): pass
+    def on_end(self, task): pass
+
+
+class SwAVUpdateQueueScoresHook(ClassyHook):
+    """Before the loss: re-score the queued embeddings with the current prototypes when the queue is in use."""
+
+    def on_forward(self, task):
+        loss = task.loss
+        if loss.local_queue_length > 0 and loss.use_queue:
+            loss.compute_queue_scores(task.model.heads[0])
+
+
+class NormalizePrototypesHook(ClassyHook):
+    """After every parameter update: L2-normalise the prototypes. With the fused LARS kernel the normalisation
+    happens inside the optimizer update (tensor flag ROWNORM128) and this hook has nothing left to do."""
+
+    def on_start(self, task):
+        if not getattr(task, "prototypes_normalized_by_kernel", False):
+            normalize_prototypes(task.model)
+
+    def on_update(self, task):
+        if not getattr(task, "prototypes_normalized_by_kernel", False) and task.last_step_was_global:
+            normalize_prototypes(task.model)
+
+
+class FreezeParametersHook(ClassyHook):
+    """Zero the gradients of the parameters named in MODEL.TEMP_FROZEN_PARAMS_ITER_MAP while the LOCAL iteration is
+    below their threshold (prototypes frozen for the first 5005 iterations in the recipe)."""
+
+    def __init__(self, frozen_map):
+        self.map = {name.replace("module.", "", 1): int(it) for name, it in frozen_map}
+        self._params = None
+
+    def on_start(self, task):
+        named = dict(task.model.named_parameters())
+        self._params = {n: named[n] for n in self.map if n in named}
+        missing = set(self.map) - set(self._params)
+        if missing:
+            logger.warning("TEMP_FROZEN_PARAMS_ITER_MAP names not found in the model: %s", sorted(missing))
+        self._apply(task)
+
+    def _apply(self, task):
+        for name, p in self._params.items():
+            frozen = task.iteration < self.map[name]
+            task.set_param_frozen(p, frozen)
+
+    def on_backward(self, task):
+        for name, p in self._params.items():
+            if task.iteration < self.map[name]:
+                if p.grad is not None:
+                    p.grad.zero_()
+                mg = getattr(p, "main_grad", None)
+                if mg is not None:
+                    mg.zero_()
+        self._apply(task)
+
+
+class CheckNanLossHook(ClassyHook):
+    def on_loss_and_meter(self, task):
+        if task.check_nan_every > 0 and task.iteration % task.check_nan_every == 0:
+            if not torch.isfinite(task.last_loss).item():
+                raise FloatingPointError(f"Infinite Loss or NaN at iteration={task.iteration}")
+
+
+class UpdateTrainIterationNumHook(ClassyHook):
+    def on_forward(self, task):
+        task.iteration += 1
+
+
+class UpdateBatchesSeenHook(ClassyHook):
+    def on_forward(self, task):
+        task.batches += 1
+
+
+class UpdateTrainBatchTimeHook(ClassyHook):
+    def on_start(self, task):
+        task.batch_time, self._t = [], time.perf_counter()
+
+    def on_step(self, task):
+        now = time.perf_counter()
+        task.batch_time.append(now - self._t)
+        self._t = now
+
+
+class LogLossLrEtaHook(ClassyHook):
+    def __init__(self, log_frequency: int):
+        self.freq = max(int(log_frequency), 1)
+
+    def on_update(self, task):
+        if task.iteration % self.freq == 0 or task.iteration <= 5:
+            lr = task.optimizer.optimizer.param_groups[0]["lr"]
+            bt = sum(task.batch_time[-self.freq:]) / max(len(task.batch_time[-self.freq:]), 1) if task.batch_time else 0.0
+            mem = torch.cuda.max_memory_allocated() / 2 ** 20 if torch.cuda.is_available() else 0
+            collab = task.optimizer.optimizer
+            gstep = getattr(getattr(collab, "collaboration_state", None), "optimizer_step", None)
+            logger.info(f"Rank: 0; [it: {task.iteration}]; lr: {lr:.5g}; loss: {float(task.last_loss):.5f}; "
+                        f"btime(ms): {1e3 * bt:.1f}; global step: {gstep}; max_mem: {mem:.0f}M")
+
+
+class LogPerfTimeMetricsHook(ClassyHook):
+    def __init__(self, rolling_freq: int):
+        self.freq = rolling_freq
+
+    def on_update(self, task):
+        if task.perf_stats is not None and self.freq > 0 and task.iteration % self.freq == 0:
+            logger.info("Performance stats:\n" + task.perf_stats.report_str())
+
+    def on_phase_end(self, task):
+        if task.perf_stats is not None:
+            logger.info("Performance stats (phase):\n" + task.perf_stats.report_str())
+
+
+class LogGpuStatsHook(ClassyHook):
+    def on_start(self, task):
+        try:
+            out = subprocess.run(["nvidia-smi"], capture_output=True, text=True, timeout=10).stdout
+            logger.info("nvidia-smi:\n" + out)
+        except Exception:
+            pass
+
+
+class LogGpuMemoryHook(ClassyHook):
+    def __init__(self, iteration_num: int):
+        self.iteration_num = iteration_num
+
+    def on_step(self, task):
+        if torch.cuda.is_available() and task.iteration == self.iteration_num + 1:
+            logger.info(torch.cuda.memory_summary())
+
+
+class LogLossMetricsCheckpointHook(ClassyHook):
+    """VISSL-shaped checkpoints (log_hooks.py:268-417): `model_iteration{N}.torch` every CHECKPOINT_ITER_FREQUENCY
+    iterations, `model_phase{N}.torch` every CHECKPOINT_FREQUENCY phases, `model_final_checkpoint_phase{N}.torch`,
+    `checkpoint.torch` symlink to the newest, `metrics.json` lines. The `optimizer` entry is None for
+    sgd_collaborative; the SwAV queue rides in `loss`."""
+
+    def __init__(self, cfg):
+        self.dir = cfg.CHECKPOINT.DIR
+        self.iter_freq = cfg.CHECKPOINT.CHECKPOINT_ITER_FREQUENCY
+        self.phase_freq = cfg.CHECKPOINT.CHECKPOINT_FREQUENCY
+
+    def on_step(self, task):
+        if self.iter_freq > 0 and task.iteration > 0 and task.iteration % self.iter_freq == 0:
+            self._save(task, f"model_iteration{task.iteration}.torch")
+
+    def on_phase_end(self, task):
+        final = task.phase_idx + 1 >= task.num_phases
+        if final:
+            self._save(task, f"model_final_checkpoint_phase{task.phase_idx}.torch")
+        elif self.phase_freq > 0 and (task.phase_idx + 1) % self.phase_freq == 0:
+            self._save(task, f"model_phase{task.phase_idx}.torch")
+        with open(os.path.join(self.dir, "metrics.json"), "a") as f:
+            f.write(json.dumps({"iteration": task.iteration, "phase_idx": task.phase_idx,
+                                "loss": float(task.last_loss) if task.last_loss is not None else None}) + "\n")
+
+    def _save(self, task, name):
+        os.makedirs(self.dir, exist_ok=True)
+        state = {"phase_idx": task.phase_idx, "iteration": task.iteration, "iteration_num": task.iteration,
+                 "train_phase_idx": task.phase_idx,
+                 "loss": float(task.last_loss) if task.last_loss is not None else None,
+                 "classy_state_dict": task.get_classy_state()}
+        path = os.path.join(self.dir, name)
+        torch.save(state, path)
+        link = os.path.join(self.dir, "checkpoint.torch")
+        if os.path.islink(link) or os.path.exists(link):
+            os.remove(link)
+        os.symlink(name, link)
+        logger.info(f"Saved checkpoint: {path}")
+
+
+class SSLTensorboardHook(ClassyHook):
+    def __init__(self, cfg):
+        tb = cfg.HOOKS.TENSORBOARD_SETUP
+        self.writer = None
+        try:
+            from torch.utils.tensorboard import SummaryWriter
+
+            self.writer = SummaryWriter(log_dir=os.path.join(tb.LOG_DIR, tb.EXPERIMENT_LOG_DIR),
+                                        flush_secs=60 * tb.FLUSH_EVERY_N_MIN)
+        except Exception as e:
+            logger.warning("tensorboard unavailable: %r", e)
+        self.log_params, self.log_grads = tb.LOG_PARAMS, tb.LOG_PARAMS_GRADIENTS
+        self.every = tb.LOG_PARAMS_EVERY_N_ITERS
+
+    def on_update(self, task):
+        if self.writer is None:
+            return
+        it = task.iteration
+        self.writer.add_scalar("Training/Loss", float(task.last_loss), it)
+        self.writer.add_scalar("Training/Learning_rate", task.optimizer.optimizer.param_groups[0]["lr"], it)
+        if self.every > 0 and it % self.every == 0 and self.log_params:
+            for name, p in task.model.named_parameters():
+                self.writer.add_histogram(f"Parameters/{name}", p.detach().float().cpu(), it)
+
+    def on_end(self, task):
+        if self.writer is not None:
+            self.writer.close()
+
+
+def default_hook_generator(cfg) -> List[ClassyHook]:
+    hooks: List[ClassyHook] = []
+    if cfg.LOSS.name == "swav_loss":
+        hooks += [SwAVUpdateQueueScoresHook(), NormalizePrototypesHook()]
+    hooks += [CheckNanLossHook(), UpdateTrainIterationNumHook(), UpdateBatchesSeenHook(), UpdateTrainBatchTimeHook()]
+    if cfg.MODEL.TEMP_FROZEN_PARAMS_ITER_MAP:
+        hooks.append(FreezeParametersHook(cfg.MODEL.TEMP_FROZEN_PARAMS_ITER_MAP))
+    if cfg.HOOKS.PERF_STATS.MONITOR_PERF_STATS:
+        hooks.append(LogPerfTimeMetricsHook(cfg.HOOKS.PERF_STATS.ROLLING_BTIME_FREQ))
+    if cfg.HOOKS.LOG_GPU_STATS:
+        hooks.append(LogGpuStatsHook())
+    if cfg.HOOKS.MEMORY_SUMMARY.PRINT_MEMORY_SUMMARY:
+        hooks.append(LogGpuMemoryHook(cfg.HOOKS.MEMORY_SUMMARY.LOG_ITERATION_NUM))
+    if cfg.HOOKS.TENSORBOARD_SETUP.USE_TENSORBOARD:
+        hooks.append(SSLTensorboardHook(cfg))
+    hooks += [LogLossLrEtaHook(cfg.LOG_FREQUENCY), LogLossMetricsCheckpointHook(cfg)]
+    return hooks

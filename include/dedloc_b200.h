@@ -134,6 +134,13 @@ int dedloc_layernorm_bwd(const void* dy, const void* x, const void* gamma, const
                          void* dx, float* dgamma, float* dbeta, int M, int H, void* stream);
 int dedloc_colsum_accumulate(const void* dy, float* out, int M, int N, long long ld, void* stream);
 
+/* ---- SwAV Sinkhorn-Knopp assignments in one persistent kernel (vissl/losses/swav_loss.py:177-244) -------- */
+/* scores: [n, K] bf16 or fp32 (rows = samples: batch first, then the queue); out: [n_out, K] fp32 assignments of
+ * the first n_out rows; scratch: dedloc_sinkhorn_scratch_floats(K, iters) floats, clobbered. */
+long long dedloc_sinkhorn_scratch_floats(int K, int iters);
+int dedloc_sinkhorn(const void* scores, int is_bf16, long long ld, int n, int K, int n_out, float epsilon, int iters,
+                    float world_size, float* out, long long ld_out, float* scratch, void* stream);
+
 #ifdef __cplusplus
 }
 #endif
