@@ -38,6 +38,7 @@ def parse_args():
     ap.add_argument("--model", default="albert-large-v2", choices=["albert-large-v2", "albert-small", "albert-tiny"])
     ap.add_argument("--ops", default="native", choices=["native", "torch"], help="linear layers: tcgen05 or torch")
     ap.add_argument("--skip-e2e", action="store_true")
+    ap.add_argument("--no-cuda-graph", action="store_true", help="run the micro-step eagerly")
     return ap.parse_args()
 
 
@@ -139,6 +140,7 @@ def main_ours(args):
     trainer = build_albert_peer(dht, cfg, model_cfg, device=device, seed=0)
     data = SyntheticMLMBatches(model_cfg.vocab_size, seq, args.micro_batch, seed=1234 + rank)
     resident = [data.to_device(b, device) for b in data.batches]   # device-resident copies for the kernel-timed arm
+    graphed = False if args.no_cuda_graph else trainer.enable_cuda_graph(resident[0])
     barrier()
 
     def run_global_step(e2e: bool) -> int:
@@ -147,7 +149,8 @@ def main_ours(args):
         i = 0
         while True:
             if e2e:
-                batch = data.to_device(data.next_host(), device)   # H2D from pinned memory, every micro-batch
+                # H2D from pinned memory, every micro-batch (straight into the graph's static inputs when graphed)
+                batch = data.next_host() if graphed else data.to_device(data.next_host(), device)
             else:
                 batch = resident[i % len(resident)]
             i += 1
@@ -215,6 +218,7 @@ def main_ours(args):
             "config": {"model": args.model, "global_batch": args.target_batch_size, "seq_len": seq,
                        "parallelism": f"dedloc-dp{world}", "optimizer": "LAMB (fused in all-reduce kernel)",
                        "micro_batch": args.micro_batch, "compression": args.compression, "linear_ops": args.ops,
+                       "cuda_graph_micro_step": bool(graphed),
                        "samples_per_step_measured": round(dev["samples"] / args.steps, 1),
                        "l2": "inputs larger than L2 (activations of one micro-batch >> 126 MB)",
                        "step": "one collaborative optimizer step (accumulate to target_batch_size, fused "

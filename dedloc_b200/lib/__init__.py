@@ -81,6 +81,8 @@ def _declare(lib: C.CDLL) -> None:
     vp, ll, i, f = C.c_void_p, C.c_longlong, C.c_int, C.c_float
     lib.dedloc_last_error.restype = C.c_char_p
     lib.dedloc_launch_count.restype = ll
+    lib.dedloc_add_launch_count.argtypes = [ll]
+    lib.dedloc_add_launch_count.restype = None
     lib.dedloc_device_info.argtypes = [C.POINTER(i), C.POINTER(i), C.POINTER(i), C.POINTER(ll)]
     lib.dedloc_symm_alloc.argtypes = [ll, C.POINTER(vp), C.c_char_p]
     lib.dedloc_symm_open.argtypes = [C.c_char_p, C.POINTER(vp)]

@@ -107,13 +107,14 @@ class PeerTrainer:
         self.loss_sum = torch.zeros((), device=device, dtype=torch.float32)
         self.mini_steps = 0
         self.samples_processed = 0
+        self._graph = None
+        self._static_batch: Optional[Dict[str, torch.Tensor]] = None
+        self._graph_launches = 0
 
-    def micro_step(self, batch: Dict[str, torch.Tensor]) -> bool:
-        """One local step: forward/backward over `gradient_accumulation_steps` x micro_batch samples, then
-        CollaborativeOptimizer.step(). Returns True when a collaborative (global) step happened."""
-        cfg = self.cfg
+    # ---------------------------------------------------------------- CUDA-graph capture of the micro-step
+    def _forward_backward(self, batch: Dict[str, torch.Tensor]) -> None:
+        chunks = self.cfg.gradient_accumulation_steps
         n = batch["input_ids"].shape[0]
-        chunks = cfg.gradient_accumulation_steps
         for c in range(chunks):
             sub = {k: v[c * n // chunks:(c + 1) * n // chunks] for k, v in batch.items()} if chunks > 1 else batch
             out = self.model(**sub)
@@ -121,6 +122,56 @@ class PeerTrainer:
             self.loss_sum += out.loss.detach().float() / chunks
         if hasattr(self.model, "flush_fused_grads"):
             self.model.flush_fused_grads()
+
+    def enable_cuda_graph(self, example_batch: Dict[str, torch.Tensor], warmup: int = 3) -> bool:
+        """Capture forward + backward (+ fused-gradient flush) of one micro-batch into a CUDA graph: the launch-bound
+        inner loop (~600 kernels) then costs one graph launch per micro-batch. Returns False (and stays eager) when
+        the capture is not possible."""
+        if self.device.type != "cuda" or self._graph is not None:
+            return self._graph is not None
+        from .. import lib as native
+
+        try:
+            self._static_batch = {k: v.to(self.device).clone() for k, v in example_batch.items()}
+            side = torch.cuda.Stream(self.device)
+            side.wait_stream(torch.cuda.current_stream(self.device))
+            with torch.cuda.stream(side):
+                for _ in range(warmup):
+                    self._forward_backward(self._static_batch)
+            torch.cuda.current_stream(self.device).wait_stream(side)
+            torch.cuda.synchronize(self.device)
+            self.collab.zero_grad()          # the warm-up gradients are not part of training
+            self.loss_sum.zero_()
+            graph = torch.cuda.CUDAGraph()
+            before = native.launch_count()
+            with torch.cuda.graph(graph):
+                self._forward_backward(self._static_batch)
+            self._graph_launches = native.launch_count() - before
+            self.collab.zero_grad()          # capture does not execute, but keep the buffers clean regardless
+            self.loss_sum.zero_()
+            self._graph = graph
+            return True
+        except Exception as e:  # pragma: no cover
+            import logging
+
+            logging.getLogger(__name__).warning("CUDA-graph capture failed, staying eager: %r", e)
+            self._graph, self._static_batch = None, None
+            torch.cuda.synchronize(self.device)
+            return False
+
+    def micro_step(self, batch: Dict[str, torch.Tensor]) -> bool:
+        """One local step: forward/backward over `gradient_accumulation_steps` x micro_batch samples, then
+        CollaborativeOptimizer.step(). Returns True when a collaborative (global) step happened."""
+        n = batch["input_ids"].shape[0]
+        if self._graph is not None:
+            from .. import lib as native
+
+            for k, v in batch.items():       # host (pinned) or device source -> static graph inputs
+                self._static_batch[k].copy_(v, non_blocking=True)
+            self._graph.replay()
+            native.lib().dedloc_add_launch_count(self._graph_launches)
+        else:
+            self._forward_backward(batch)
         self.mini_steps += 1
         self.samples_processed += n
         return bool(self.collab.step(batch_size=n))

@@ -21,6 +21,7 @@ extern "C" {
 /* ---- library ---------------------------------------------------------------------------------- */
 const char* dedloc_last_error(void);
 long long dedloc_launch_count(void);          /* kernels launched by this library since load */
+void dedloc_add_launch_count(long long n);    /* account for kernels replayed from a captured CUDA graph */
 int dedloc_device_info(int* sm_count, int* cc_major, int* cc_minor, long long* total_mem);
 
 /* ---- symmetric peer memory over CUDA IPC (SURVEY 5.8 data plane; replaces hivemind's gRPC tensors) */
