@@ -107,6 +107,12 @@ def _declare(lib: C.CDLL) -> None:
     lib.dedloc_sinkhorn_scratch_floats.restype = ll
     lib.dedloc_sinkhorn.argtypes = [vp, i, ll, i, i, i, f, i, f, vp, ll, vp, vp]
     lib.dedloc_sinkhorn.restype = i
+    lib.dedloc_attention_fwd.argtypes = [vp, vp, vp, vp, i, i, i, i, f, vp]
+    lib.dedloc_attention_fwd.restype = i
+    lib.dedloc_attention_bwd_scratch_floats.argtypes = [i]
+    lib.dedloc_attention_bwd_scratch_floats.restype = ll
+    lib.dedloc_attention_bwd.argtypes = [vp, vp, vp, vp, vp, vp, vp, i, i, i, i, f, vp]
+    lib.dedloc_attention_bwd.restype = i
     for name in ("dedloc_layernorm_fwd", "dedloc_layernorm_bwd", "dedloc_colsum_accumulate"):
         getattr(lib, name).restype = i
     for name in ("dedloc_symm_alloc", "dedloc_symm_open", "dedloc_symm_close", "dedloc_symm_free",

@@ -142,6 +142,17 @@ long long dedloc_sinkhorn_scratch_floats(int K, int iters);
 int dedloc_sinkhorn(const void* scores, int is_bf16, long long ld, int n, int K, int n_out, float epsilon, int iters,
                     float world_size, float* out, long long ld_out, float* scratch, void* stream);
 
+/* ---- shared-layer attention on the packed QKV layout (HF AlbertAttention: bmm + softmax + bmm) ----------- */
+/* qkv: [B, S, 3, H, 64] bf16 (output of the fused QKV GEMM); mask: [B, S] bytes (1 = attend) or NULL;
+ * out: [B, S, H*64] bf16; lse: [B, H, S] fp32 (log-sum-exp of the scaled scores, for backward) or NULL. */
+int dedloc_attention_fwd(const void* qkv, const unsigned char* mask, void* out, float* lse, int B, int S, int H, int D,
+                         float scale, void* stream);
+/* backward: dqkv [B, S, 3, H, 64] bf16 from out / dout [B, S, H*64] and lse; scratch holds
+ * dedloc_attention_bwd_scratch_floats(S) floats (per-CTA fp32 dQ accumulators), contents are clobbered. */
+long long dedloc_attention_bwd_scratch_floats(int S);
+int dedloc_attention_bwd(const void* qkv, const void* out, const void* dout, const float* lse, const unsigned char* mask,
+                         void* dqkv, float* scratch, int B, int S, int H, int D, float scale, void* stream);
+
 #ifdef __cplusplus
 }
 #endif
