@@ -165,10 +165,21 @@ class AlbertAttention(nn.Module):
         self.LayerNorm = nn.LayerNorm(H, eps=cfg.layer_norm_eps)
         self.attn_dropout_p, self.out_dropout_p = cfg.attention_probs_dropout_prob, cfg.hidden_dropout_prob
 
-    def forward(self, x, attn_bias, impl: str, fused_qkv=None):
+    def forward(self, x, attn_bias, impl: str, fused_qkv=None, key_mask=None):
         B, S, H = x.shape
         if fused_qkv is not None:
             qkv = fused_linear(x, fused_qkv, impl)                        # [B,S,3H] in one GEMM
+            if impl == "native" and self.head_dim == 64 and not (self.attn_dropout_p > 0 and self.training):
+                from ..ops import attention as native_attention
+
+                if native_attention.supported(qkv, self.num_heads):
+                    # tcgen05 attention straight on the packed projection: no head transposes / unpack copies
+                    ctx = native_attention.packed_attention(qkv, self.num_heads, key_mask)
+                    if self.out_dropout_p > 0 and self.training:
+                        y = F.dropout(fused_linear(ctx, self.dense, impl), self.out_dropout_p, True) + x
+                    else:
+                        y = fused_linear(ctx, self.dense, impl, residual=x)
+                    return _ln(y, self.LayerNorm, impl)
             q, k, v = qkv.view(B, S, 3, self.num_heads, self.head_dim).permute(2, 0, 3, 1, 4)
         else:
             q = fused_linear(x, self.query, impl).view(B, S, self.num_heads, self.head_dim).transpose(1, 2)
@@ -193,8 +204,8 @@ class AlbertLayer(nn.Module):
         self.ffn_output = _Linear(cfg.intermediate_size, cfg.hidden_size)
         self.dropout_p = cfg.hidden_dropout_prob
 
-    def forward(self, x, attn_bias, impl: str, fused_qkv=None):
-        a = self.attention(x, attn_bias, impl, fused_qkv)
+    def forward(self, x, attn_bias, impl: str, fused_qkv=None, key_mask=None):
+        a = self.attention(x, attn_bias, impl, fused_qkv, key_mask)
         if (_native_ok(a, self.ffn, impl) and self.ffn_output.out_features % 64 == 0
                 and _main_grad(self.ffn_output.weight) is not None and not (self.dropout_p > 0 and self.training)):
             from ..ops.gemm import ffn as native_ffn
@@ -276,7 +287,7 @@ class AlbertModel(nn.Module):
                         if torch.is_grad_enabled():
                             pending_flush.append(fused[key])
                     fq = fused[key]
-                x = layer(x, attn_bias, impl, fq)
+                x = layer(x, attn_bias, impl, fq, attention_mask)
         pooled = torch.tanh(fused_linear(x[:, 0], self.pooler, "torch"))
         return x, pooled
 
