@@ -29,109 +29,138 @@ struct GemmKernelParams {
 };
 
 
-// r[32]: raw fp32 accumulator bits of columns [col0, col0 + 32) of output row `row`.
+__device__ __forceinline__ void unpack8_bf16(const uint4& u, float (&o)[8]) {
+  float2 t;
+  t = unpack_bf16x2(u.x); o[0] = t.x; o[1] = t.y;
+  t = unpack_bf16x2(u.y); o[2] = t.x; o[3] = t.y;
+  t = unpack_bf16x2(u.z); o[4] = t.x; o[5] = t.y;
+  t = unpack_bf16x2(u.w); o[6] = t.x; o[7] = t.y;
+}
+
+// Epilogue math on 32 accumulator columns [col0, col0+32) of output row `row`:
+//   v = acc * alpha (+ bias) ; pre = v ; (gelu_new | * gelu'(aux)) ; (+ residual)
+// `pre` (the pre-activation, only meaningful with SAVE_PRE) is returned separately so that the caller decides how
+// to store it. Loads of row-indexed operands are skipped for rows beyond M.
+__device__ __forceinline__ void gemm_epilogue_math(const GemmKernelParams& p, int row, bool row_ok, int col0,
+                                                   const uint32_t (&r)[32], float (&v)[32], float (&pre)[32]) {
+  const bool full_cols = (col0 + 32 <= p.N);
+#pragma unroll
+  for (int i = 0; i < 32; ++i) v[i] = __uint_as_float(r[i]) * p.alpha;
+  if (p.epi & DEDLOC_EPI_BIAS) {
+    if (p.epi & DEDLOC_EPI_BIAS_F32) {
+      const float* b = reinterpret_cast<const float*>(p.bias) + col0;
+      if (full_cols) {
+#pragma unroll
+        for (int i = 0; i < 32; i += 4) {
+          const float4 t = __ldg(reinterpret_cast<const float4*>(b + i));   // same address in every lane: broadcast
+          v[i] += t.x; v[i + 1] += t.y; v[i + 2] += t.z; v[i + 3] += t.w;
+        }
+      } else {
+        for (int i = 0; i < 32 && col0 + i < p.N; ++i) v[i] += __ldg(b + i);
+      }
+    } else {
+      const __nv_bfloat16* b = reinterpret_cast<const __nv_bfloat16*>(p.bias) + col0;
+      if (full_cols) {
+#pragma unroll
+        for (int i = 0; i < 32; i += 8) {
+          float t[8];
+          unpack8_bf16(__ldg(reinterpret_cast<const uint4*>(b + i)), t);
+#pragma unroll
+          for (int k = 0; k < 8; ++k) v[i + k] += t[k];
+        }
+      } else {
+        for (int i = 0; i < 32 && col0 + i < p.N; ++i) v[i] += __bfloat162float(b[i]);
+      }
+    }
+  }
+  if (p.epi & DEDLOC_EPI_SAVE_PRE) {
+#pragma unroll
+    for (int i = 0; i < 32; ++i) pre[i] = v[i];
+  }
+  if (p.epi & DEDLOC_EPI_GELU) {
+#pragma unroll
+    for (int i = 0; i < 32; ++i) v[i] = gelu_tanh(v[i]);
+  }
+  if ((p.epi & DEDLOC_EPI_DGELU) && row_ok) {
+    const __nv_bfloat16* ai = reinterpret_cast<const __nv_bfloat16*>(p.aux_in) + (size_t)row * p.ld_aux + col0;
+    if (full_cols) {
+#pragma unroll
+      for (int i = 0; i < 32; i += 8) {
+        float t[8];
+        unpack8_bf16(*reinterpret_cast<const uint4*>(ai + i), t);
+#pragma unroll
+        for (int k = 0; k < 8; ++k) v[i + k] *= gelu_tanh_grad(t[k]);
+      }
+    } else {
+      for (int i = 0; i < 32 && col0 + i < p.N; ++i) v[i] *= gelu_tanh_grad(__bfloat162float(ai[i]));
+    }
+  }
+  if ((p.epi & DEDLOC_EPI_RESIDUAL) && row_ok) {
+    const __nv_bfloat16* rs = reinterpret_cast<const __nv_bfloat16*>(p.residual) + (size_t)row * p.ld_res + col0;
+    if (full_cols) {
+#pragma unroll
+      for (int i = 0; i < 32; i += 8) {
+        float t[8];
+        unpack8_bf16(*reinterpret_cast<const uint4*>(rs + i), t);
+#pragma unroll
+        for (int k = 0; k < 8; ++k) v[i + k] += t[k];
+      }
+    } else {
+      for (int i = 0; i < 32 && col0 + i < p.N; ++i) v[i] += __bfloat162float(rs[i]);
+    }
+  }
+}
+
+// bf16 row-segment store (32 columns) straight to global memory.
+__device__ __forceinline__ void store_bf16_32(__nv_bfloat16* dst, const float (&v)[32], bool full_cols, int valid) {
+  if (full_cols) {
+#pragma unroll
+    for (int i = 0; i < 32; i += 8)
+      *reinterpret_cast<uint4*>(dst + i) = make_uint4(pack_bf16x2(v[i], v[i + 1]), pack_bf16x2(v[i + 2], v[i + 3]),
+                                                      pack_bf16x2(v[i + 4], v[i + 5]), pack_bf16x2(v[i + 6], v[i + 7]));
+  } else {
+    for (int i = 0; i < 32 && i < valid; ++i) dst[i] = __float2bfloat16(v[i]);
+  }
+}
+
+// Direct (register -> global) store of the epilogue result for every output kind.
+__device__ __forceinline__ void gemm_epilogue_store(const GemmKernelParams& p, int row, int col0, const float (&v)[32]) {
+  const bool full_cols = (col0 + 32 <= p.N);
+  const int valid = p.N - col0;
+  if (p.out_kind == 0) {
+    store_bf16_32(reinterpret_cast<__nv_bfloat16*>(p.C) + (size_t)row * p.ldc + col0, v, full_cols, valid);
+  } else if (p.out_kind == 1) {
+    float* co = reinterpret_cast<float*>(p.C) + (size_t)row * p.ldc + col0;
+    if (full_cols) {
+#pragma unroll
+      for (int i = 0; i < 32; i += 4) *reinterpret_cast<float4*>(co + i) = make_float4(v[i], v[i + 1], v[i + 2], v[i + 3]);
+    } else {
+      for (int i = 0; i < 32 && i < valid; ++i) co[i] = v[i];
+    }
+  } else {
+    float* co = reinterpret_cast<float*>(p.C) + (size_t)row * p.ldc + col0;
+    if (full_cols) {
+#pragma unroll
+      for (int i = 0; i < 32; i += 4)
+        asm volatile("red.global.add.v4.f32 [%0], {%1,%2,%3,%4};" ::"l"(co + i), "f"(v[i]), "f"(v[i + 1]),
+                     "f"(v[i + 2]), "f"(v[i + 3])
+                     : "memory");
+    } else {
+      for (int i = 0; i < 32 && i < valid; ++i) atomicAdd(co + i, v[i]);
+    }
+  }
+}
+
+// r[32]: raw fp32 accumulator bits of columns [col0, col0 + 32) of output row `row`; everything stored directly.
 __device__ __forceinline__ void gemm_epilogue_32cols(const GemmKernelParams& p, int row, bool row_ok, int col0,
                                                      const uint32_t (&r)[32]) {
-    const bool has_bias = (p.epi & DEDLOC_EPI_BIAS) != 0;
-    const bool bias_f32 = (p.epi & DEDLOC_EPI_BIAS_F32) != 0;
-    const bool do_gelu = (p.epi & DEDLOC_EPI_GELU) != 0;
-    const bool do_dgelu = (p.epi & DEDLOC_EPI_DGELU) != 0;
-    const bool has_res = (p.epi & DEDLOC_EPI_RESIDUAL) != 0;
-    const bool save_pre = (p.epi & DEDLOC_EPI_SAVE_PRE) != 0;
-    float v[32];
-#pragma unroll
-    for (int i = 0; i < 32; ++i) v[i] = __uint_as_float(r[i]) * p.alpha;
-    const bool full_cols = (col0 + 32 <= p.N);
-    if (has_bias) {
-      if (bias_f32) {
-        const float* b = reinterpret_cast<const float*>(p.bias) + col0;
-#pragma unroll
-        for (int i = 0; i < 32; ++i) if (full_cols || col0 + i < p.N) v[i] += __ldg(b + i);
-      } else {
-        const __nv_bfloat16* b = reinterpret_cast<const __nv_bfloat16*>(p.bias) + col0;
-#pragma unroll
-        for (int i = 0; i < 32; ++i) if (full_cols || col0 + i < p.N) v[i] += __bfloat162float(b[i]);
-      }
-    }
-    if (row_ok) {
-      if (save_pre) {
-        __nv_bfloat16* po = reinterpret_cast<__nv_bfloat16*>(p.pre_out) + (size_t)row * p.ld_pre + col0;
-        if (full_cols) {
-#pragma unroll
-          for (int i = 0; i < 32; i += 8)
-            *reinterpret_cast<uint4*>(po + i) = make_uint4(pack_bf16x2(v[i], v[i + 1]), pack_bf16x2(v[i + 2], v[i + 3]),
-                                                           pack_bf16x2(v[i + 4], v[i + 5]), pack_bf16x2(v[i + 6], v[i + 7]));
-        } else {
-          for (int i = 0; i < 32 && col0 + i < p.N; ++i) po[i] = __float2bfloat16(v[i]);
-        }
-      }
-      if (do_gelu) {
-#pragma unroll
-        for (int i = 0; i < 32; ++i) v[i] = gelu_tanh(v[i]);
-      }
-      if (do_dgelu) {
-        const __nv_bfloat16* ai = reinterpret_cast<const __nv_bfloat16*>(p.aux_in) + (size_t)row * p.ld_aux + col0;
-        if (full_cols) {
-#pragma unroll
-          for (int i = 0; i < 32; i += 8) {
-            const uint4 u = *reinterpret_cast<const uint4*>(ai + i);
-            float2 t;
-            t = unpack_bf16x2(u.x); v[i] *= gelu_tanh_grad(t.x); v[i + 1] *= gelu_tanh_grad(t.y);
-            t = unpack_bf16x2(u.y); v[i + 2] *= gelu_tanh_grad(t.x); v[i + 3] *= gelu_tanh_grad(t.y);
-            t = unpack_bf16x2(u.z); v[i + 4] *= gelu_tanh_grad(t.x); v[i + 5] *= gelu_tanh_grad(t.y);
-            t = unpack_bf16x2(u.w); v[i + 6] *= gelu_tanh_grad(t.x); v[i + 7] *= gelu_tanh_grad(t.y);
-          }
-        } else {
-          for (int i = 0; i < 32 && col0 + i < p.N; ++i) v[i] *= gelu_tanh_grad(__bfloat162float(ai[i]));
-        }
-      }
-      if (has_res) {
-        const __nv_bfloat16* rs = reinterpret_cast<const __nv_bfloat16*>(p.residual) + (size_t)row * p.ld_res + col0;
-        if (full_cols) {
-#pragma unroll
-          for (int i = 0; i < 32; i += 8) {
-            const uint4 u = *reinterpret_cast<const uint4*>(rs + i);
-            float2 t;
-            t = unpack_bf16x2(u.x); v[i] += t.x; v[i + 1] += t.y;
-            t = unpack_bf16x2(u.y); v[i + 2] += t.x; v[i + 3] += t.y;
-            t = unpack_bf16x2(u.z); v[i + 4] += t.x; v[i + 5] += t.y;
-            t = unpack_bf16x2(u.w); v[i + 6] += t.x; v[i + 7] += t.y;
-          }
-        } else {
-          for (int i = 0; i < 32 && col0 + i < p.N; ++i) v[i] += __bfloat162float(rs[i]);
-        }
-      }
-      if (p.out_kind == 0) {
-        __nv_bfloat16* co = reinterpret_cast<__nv_bfloat16*>(p.C) + (size_t)row * p.ldc + col0;
-        if (full_cols) {
-#pragma unroll
-          for (int i = 0; i < 32; i += 8)
-            *reinterpret_cast<uint4*>(co + i) = make_uint4(pack_bf16x2(v[i], v[i + 1]), pack_bf16x2(v[i + 2], v[i + 3]),
-                                                           pack_bf16x2(v[i + 4], v[i + 5]), pack_bf16x2(v[i + 6], v[i + 7]));
-        } else {
-          for (int i = 0; i < 32 && col0 + i < p.N; ++i) co[i] = __float2bfloat16(v[i]);
-        }
-      } else if (p.out_kind == 1) {
-        float* co = reinterpret_cast<float*>(p.C) + (size_t)row * p.ldc + col0;
-        if (full_cols) {
-#pragma unroll
-          for (int i = 0; i < 32; i += 4) *reinterpret_cast<float4*>(co + i) = make_float4(v[i], v[i + 1], v[i + 2], v[i + 3]);
-        } else {
-          for (int i = 0; i < 32 && col0 + i < p.N; ++i) co[i] = v[i];
-        }
-      } else {
-        float* co = reinterpret_cast<float*>(p.C) + (size_t)row * p.ldc + col0;
-        if (full_cols) {
-#pragma unroll
-          for (int i = 0; i < 32; i += 4)
-            asm volatile("red.global.add.v4.f32 [%0], {%1,%2,%3,%4};" ::"l"(co + i), "f"(v[i]), "f"(v[i + 1]),
-                         "f"(v[i + 2]), "f"(v[i + 3])
-                         : "memory");
-        } else {
-          for (int i = 0; i < 32 && col0 + i < p.N; ++i) atomicAdd(co + i, v[i]);
-        }
-      }
-    }
+  float v[32], pre[32];
+  gemm_epilogue_math(p, row, row_ok, col0, r, v, pre);
+  if (!row_ok) return;
+  if (p.epi & DEDLOC_EPI_SAVE_PRE)
+    store_bf16_32(reinterpret_cast<__nv_bfloat16*>(p.pre_out) + (size_t)row * p.ld_pre + col0, pre, col0 + 32 <= p.N,
+                  p.N - col0);
+  gemm_epilogue_store(p, row, col0, v);
 }
 
 // Host helper shared by both kernels (defined in gemm_tcgen05.cu).

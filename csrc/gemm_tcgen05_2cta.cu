@@ -21,7 +21,8 @@ constexpr int k2Stages = 6;
 constexpr int k2ABytes = k2BM * k2BK * 2;          // 16 KB
 constexpr int k2BBytes = (k2BN / 2) * k2BK * 2;    // 16 KB
 constexpr int k2StageBytes = k2ABytes + k2BBytes;  // 32 KB per CTA per stage
-constexpr int k2SmemTotal = k2Stages * k2StageBytes + 256 + 1024;
+constexpr int k2StagingBytes = 4 * 2 * 4096;           // per epilogue warp: two 32-row x 128-byte TMA-store buffers
+constexpr int k2SmemTotal = k2Stages * k2StageBytes + k2StagingBytes + 256 + 1024;
 constexpr uint32_t kPeerBitMask = 0xFEFFFFFFu;     // clears the CTA-pair bit of a shared::cluster address
 
 __device__ __forceinline__ uint32_t cluster_ctarank() {
@@ -72,10 +73,12 @@ __device__ __forceinline__ void tmem_dealloc_2cta(uint32_t taddr, uint32_t ncols
 
 __global__ void __launch_bounds__(k2Threads, 1)
 gemm_tcgen05_2cta_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b,
+                         const __grid_constant__ CUtensorMap tmap_c, const __grid_constant__ CUtensorMap tmap_pre,
                          const __grid_constant__ GemmKernelParams p) {
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
-  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + k2Stages * k2StageBytes);
+  uint8_t* staging = smem + k2Stages * k2StageBytes;
+  uint64_t* bars = reinterpret_cast<uint64_t*>(staging + k2StagingBytes);
   uint64_t* full_bar = bars;                        // [k2Stages]  (leader's copy is the live one)
   uint64_t* empty_bar = bars + k2Stages;            // [k2Stages]  (live in both CTAs)
   uint64_t* tmem_full = bars + 2 * k2Stages;        // [2]         (live in both CTAs)
@@ -95,6 +98,7 @@ gemm_tcgen05_2cta_kernel(const __grid_constant__ CUtensorMap tmap_a, const __gri
   if (warp == 0 && lane == 0) {
     tma_prefetch_desc(&tmap_a);
     tma_prefetch_desc(&tmap_b);
+    if (p.out_kind == 0) tma_prefetch_desc(&tmap_c);
   }
   if (warp == 1 && lane == 0) {
     for (int s = 0; s < k2Stages; ++s) { mbar_init(&full_bar[s], 1); mbar_init(&empty_bar[s], 1); }
@@ -187,6 +191,12 @@ gemm_tcgen05_2cta_kernel(const __grid_constant__ CUtensorMap tmap_a, const __gri
     const int quad = warp & 3;
     int acc = 0;
     uint32_t acc_phase = 0;
+    // bf16 outputs leave through swizzled smem + TMA stores (coalesced 128-byte rows, tails clipped by the tensor
+    // map); fp32 / atomic outputs use direct register stores.
+    const bool tma_c = (p.out_kind == 0);
+    const bool tma_pre = tma_c && (p.epi & DEDLOC_EPI_SAVE_PRE);
+    uint8_t* stg = staging + quad * 8192;
+    int sbuf = 0;
     for (int tile = cluster_id; tile < total_tiles; tile += num_clusters) {
       const int rem = tile % (m_tiles * n_tiles);
       const int m0 = (rem % m_tiles) * (2 * k2BM) + (int)cta_rank * k2BM;
@@ -196,20 +206,61 @@ gemm_tcgen05_2cta_kernel(const __grid_constant__ CUtensorMap tmap_a, const __gri
       const int row = m0 + quad * 32 + lane;
       const bool row_ok = row < p.M;
       const uint32_t taddr = tmem_base + ((uint32_t)(quad * 32) << 16) + acc * k2BN;
+      if (!tma_c) {
 #pragma unroll 1
-      for (int cb = 0; cb < k2BN; cb += 32) {
-        uint32_t r[32];
-        tmem_ld_32x32b_x32(taddr + cb, r);
-        tmem_ld_wait();
-        const int col0 = n0 + cb;
-        if (col0 >= p.N) continue;  // warp-uniform
-        gemm_epilogue_32cols(p, row, row_ok, col0, r);
+        for (int cb = 0; cb < k2BN; cb += 32) {
+          uint32_t r[32];
+          tmem_ld_32x32b_x32(taddr + cb, r);
+          tmem_ld_wait();
+          const int col0 = n0 + cb;
+          if (col0 >= p.N) continue;  // warp-uniform
+          gemm_epilogue_32cols(p, row, row_ok, col0, r);
+        }
+      } else {
+#pragma unroll 1
+        for (int cb = 0; cb < k2BN; cb += 64) {
+          const int col0 = n0 + cb;
+          if (col0 >= p.N) break;  // warp-uniform
+          uint8_t* buf_out = stg + sbuf * 4096;
+          uint8_t* buf_pre = stg + (sbuf ^ 1) * 4096;
+          // the buffer(s) written below must have been fully read by their previous TMA store
+          if (lane == 0) { if (tma_pre) tma_store_wait_read<0>(); else tma_store_wait_read<1>(); }
+          __syncwarp();
+#pragma unroll
+          for (int half = 0; half < 2; ++half) {
+            uint32_t r[32];
+            tmem_ld_32x32b_x32(taddr + cb + half * 32, r);
+            tmem_ld_wait();
+            float v[32], pre[32];
+            gemm_epilogue_math(p, row, row_ok, col0 + half * 32, r, v, pre);
+#pragma unroll
+            for (int ch = 0; ch < 4; ++ch) {
+              const uint32_t off = (uint32_t)lane * 128 + (((uint32_t)(half * 4 + ch) ^ ((uint32_t)lane & 7)) << 4);
+              *reinterpret_cast<uint4*>(buf_out + off) =
+                  make_uint4(pack_bf16x2(v[8 * ch], v[8 * ch + 1]), pack_bf16x2(v[8 * ch + 2], v[8 * ch + 3]),
+                             pack_bf16x2(v[8 * ch + 4], v[8 * ch + 5]), pack_bf16x2(v[8 * ch + 6], v[8 * ch + 7]));
+              if (tma_pre)
+                *reinterpret_cast<uint4*>(buf_pre + off) =
+                    make_uint4(pack_bf16x2(pre[8 * ch], pre[8 * ch + 1]), pack_bf16x2(pre[8 * ch + 2], pre[8 * ch + 3]),
+                               pack_bf16x2(pre[8 * ch + 4], pre[8 * ch + 5]), pack_bf16x2(pre[8 * ch + 6], pre[8 * ch + 7]));
+            }
+          }
+          fence_proxy_async_smem();
+          __syncwarp();
+          if (lane == 0) {
+            if (tma_pre) { tma_store_2d(&tmap_pre, buf_pre, col0, m0 + quad * 32); tma_store_commit(); }
+            tma_store_2d(&tmap_c, buf_out, col0, m0 + quad * 32);
+            tma_store_commit();
+          }
+          if (!tma_pre) sbuf ^= 1;
+        }
       }
       tc_fence_before();
       __syncwarp();
       if (lane == 0) mbar_arrive_leader(&tmem_empty[acc]);
       if (++acc == 2) { acc = 0; acc_phase ^= 1; }
     }
+    if (tma_c && lane == 0) tma_store_wait<0>();   // staging smem must outlive the last bulk store
   }
 
   tc_fence_before();
@@ -249,6 +300,15 @@ int launch_gemm_2cta(const DedlocGemmArgs& g, cudaStream_t st) {
   else rc = make_tmap_2d_16bit(&tb, g.B, g.K, g.N, g.ldb, 64, k2BK, !g.is_fp16);
   if (rc) return rc;
 
+  CUtensorMap tc = ta, tp = ta;   // placeholders unless the bf16 TMA-store epilogue is used
+  if (g.out_kind == 0) {
+    rc = make_tmap_2d_16bit(&tc, g.C, g.M, g.N, g.ldc, 64, 32, 1);
+    if (rc) return rc;
+    if (g.epilogue & DEDLOC_EPI_SAVE_PRE) {
+      rc = make_tmap_2d_16bit(&tp, g.pre_out, g.M, g.N, g.ld_pre, 64, 32, 1);
+      if (rc) return rc;
+    }
+  }
   static int sms = 0;
   if (sms == 0) {
     int dev = 0;
@@ -273,7 +333,7 @@ int launch_gemm_2cta(const DedlocGemmArgs& g, cudaStream_t st) {
   attr[0].val.clusterDim.z = 1;
   cfg.attrs = attr;
   cfg.numAttrs = 1;
-  DEDLOC_CUDA_CHECK(cudaLaunchKernelEx(&cfg, gemm_tcgen05_2cta_kernel, ta, tb, kp));
+  DEDLOC_CUDA_CHECK(cudaLaunchKernelEx(&cfg, gemm_tcgen05_2cta_kernel, ta, tb, tc, tp, kp));
   count_launch();
   return 0;
 }
