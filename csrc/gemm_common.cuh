@@ -29,6 +29,20 @@ struct GemmKernelParams {
 };
 
 
+// Grouped tile order: consecutive tile ids walk kGroupM row-tiles before moving to the next column-tile, so the
+// CTAs resident at the same time share both A row-panels and B column-panels out of L2 (instead of streaming a
+// different A panel per CTA against one B panel).
+constexpr int kGroupM = 8;
+__device__ __forceinline__ void tile_coords(int rem, int m_tiles, int n_tiles, int& mt, int& nt) {
+  const int per_group = kGroupM * n_tiles;
+  const int group = rem / per_group;
+  const int first_m = group * kGroupM;
+  const int gm = min(m_tiles - first_m, kGroupM);
+  const int in_group = rem - group * per_group;
+  mt = first_m + in_group % gm;
+  nt = in_group / gm;
+}
+
 __device__ __forceinline__ void unpack8_bf16(const uint4& u, float (&o)[8]) {
   float2 t;
   t = unpack_bf16x2(u.x); o[0] = t.x; o[1] = t.y;

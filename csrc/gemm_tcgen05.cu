@@ -85,8 +85,10 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_con
       for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
         const int split = tile / (m_tiles * n_tiles);
         const int rem = tile - split * (m_tiles * n_tiles);
-        const int m0 = (rem % m_tiles) * BM;
-        const int n0 = (rem / m_tiles) * BN;
+        int mt, nt;
+        tile_coords(rem, m_tiles, n_tiles, mt, nt);
+        const int m0 = mt * BM;
+        const int n0 = nt * BN;
         const int kb0 = split * p.kb_per_split;
         const int kb1 = min(kb_total, kb0 + p.kb_per_split);
         for (int kb = kb0; kb < kb1; ++kb) {
@@ -158,8 +160,10 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_con
     uint32_t acc_phase = 0;
     for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
       const int rem = tile % (m_tiles * n_tiles);
-      const int m0 = (rem % m_tiles) * BM;
-      const int n0 = (rem / m_tiles) * BN;
+      int mt, nt;
+      tile_coords(rem, m_tiles, n_tiles, mt, nt);
+      const int m0 = mt * BM;
+      const int n0 = nt * BN;
       mbar_wait(&tmem_full[acc], acc_phase);
       tc_fence_after();
       const int row = m0 + quad * 32 + lane;

@@ -120,8 +120,10 @@ gemm_tcgen05_2cta_kernel(const __grid_constant__ CUtensorMap tmap_a, const __gri
       for (int tile = cluster_id; tile < total_tiles; tile += num_clusters) {
         const int split = tile / (m_tiles * n_tiles);
         const int rem = tile - split * (m_tiles * n_tiles);
-        const int m0 = (rem % m_tiles) * (2 * k2BM) + (int)cta_rank * k2BM;
-        const int n0 = (rem / m_tiles) * k2BN + (int)cta_rank * (k2BN / 2);
+        int mt, nt;
+        tile_coords(rem, m_tiles, n_tiles, mt, nt);
+        const int m0 = mt * (2 * k2BM) + (int)cta_rank * k2BM;
+        const int n0 = nt * k2BN + (int)cta_rank * (k2BN / 2);
         const int kb0 = split * p.kb_per_split;
         const int kb1 = min(kb_total, kb0 + p.kb_per_split);
         for (int kb = kb0; kb < kb1; ++kb) {
@@ -199,8 +201,10 @@ gemm_tcgen05_2cta_kernel(const __grid_constant__ CUtensorMap tmap_a, const __gri
     int sbuf = 0;
     for (int tile = cluster_id; tile < total_tiles; tile += num_clusters) {
       const int rem = tile % (m_tiles * n_tiles);
-      const int m0 = (rem % m_tiles) * (2 * k2BM) + (int)cta_rank * k2BM;
-      const int n0 = (rem / m_tiles) * k2BN;
+      int mt, nt;
+      tile_coords(rem, m_tiles, n_tiles, mt, nt);
+      const int m0 = mt * (2 * k2BM) + (int)cta_rank * k2BM;
+      const int n0 = nt * k2BN;
       mbar_wait(&tmem_full[acc], acc_phase);
       tc_fence_after();
       const int row = m0 + quad * 32 + lane;
