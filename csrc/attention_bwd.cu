@@ -216,12 +216,19 @@ attention_bwd_kernel(const __grid_constant__ CUtensorMap tmap_qkv, const __grid_
           mbar_wait(s_full, step_phase);
           tc_fence_after();
           // ---- P^T and dS^T for key `row` against the 128 queries of block i ----
-#pragma unroll 1
-          for (int c = 0; c < kAbBlk; c += 32) {
-            uint32_t rs[32], rp[32];
-            tmem_ld_32x32b_x32(t_S + lane_off + c, rs);
-            tmem_ld_32x32b_x32(t_dP + lane_off + c, rp);
+          uint32_t rsA[32], rpA[32], rsB[32], rpB[32];
+          tmem_ld_32x32b_x32(t_S + lane_off, rsA);
+          tmem_ld_32x32b_x32(t_dP + lane_off, rpA);
+#pragma unroll
+          for (int cidx4 = 0; cidx4 < 4; ++cidx4) {
+            const int c = cidx4 * 32;
             tmem_ld_wait();
+            uint32_t (&rs)[32] = (cidx4 & 1) ? rsB : rsA;
+            uint32_t (&rp)[32] = (cidx4 & 1) ? rpB : rpA;
+            if (cidx4 < 3) {   // next chunk in flight while this one is processed
+              tmem_ld_32x32b_x32(t_S + lane_off + c + 32, (cidx4 & 1) ? rsA : rsB);
+              tmem_ld_32x32b_x32(t_dP + lane_off + c + 32, (cidx4 & 1) ? rpA : rpB);
+            }
             uint32_t pk[16], dk[16];
 #pragma unroll
             for (int q = 0; q < 32; q += 2) {
@@ -248,37 +255,40 @@ attention_bwd_kernel(const __grid_constant__ CUtensorMap tmap_qkv, const __grid_
           __syncwarp();
           if (lane == 0) mbar_arrive(pds_full);
           // ---- dQ partial of query `row` of block i ----
-          mbar_wait(dq_full, step_phase);
-          tc_fence_after();
           {
             float* acc = dq_acc + (size_t)(i * kAbBlk + row) * kAbD;
             __nv_bfloat16* dst = p.dqkv + (((size_t)(b * S + i * kAbBlk + row) * 3 + 0) * H + h) * kAbD;
+            // the running fp32 sum of this row (L2-resident scratch) is fetched while MMA3-5 are still running
+            float4 prev[16];
+            if (j > 0) {
 #pragma unroll
-            for (int c = 0; c < kAbD; c += 32) {
-              uint32_t r[32];
-              tmem_ld_32x32b_x32(t_dQ + lane_off + c, r);
-              tmem_ld_wait();
-              float v[32];
+              for (int q = 0; q < 16; ++q) prev[q] = *reinterpret_cast<const float4*>(acc + 4 * q);
+            }
+            mbar_wait(dq_full, step_phase);
+            tc_fence_after();
+            uint32_t r0[32], r1[32];
+            tmem_ld_32x32b_x32(t_dQ + lane_off, r0);
+            tmem_ld_32x32b_x32(t_dQ + lane_off + 32, r1);
+            tmem_ld_wait();
+            float v[64];
 #pragma unroll
-              for (int q = 0; q < 32; ++q) v[q] = __uint_as_float(r[q]);
-              if (j > 0) {
+            for (int q = 0; q < 32; ++q) { v[q] = __uint_as_float(r0[q]); v[32 + q] = __uint_as_float(r1[q]); }
+            if (j > 0) {
 #pragma unroll
-                for (int q = 0; q < 32; q += 4) {
-                  const float4 o = *reinterpret_cast<const float4*>(acc + c + q);
-                  v[q] += o.x; v[q + 1] += o.y; v[q + 2] += o.z; v[q + 3] += o.w;
-                }
+              for (int q = 0; q < 16; ++q) {
+                v[4 * q] += prev[q].x; v[4 * q + 1] += prev[q].y; v[4 * q + 2] += prev[q].z; v[4 * q + 3] += prev[q].w;
               }
-              if (j < nblk - 1) {
+            }
+            if (j < nblk - 1) {
 #pragma unroll
-                for (int q = 0; q < 32; q += 4)
-                  *reinterpret_cast<float4*>(acc + c + q) = make_float4(v[q], v[q + 1], v[q + 2], v[q + 3]);
-              } else {
+              for (int q = 0; q < 64; q += 4)
+                *reinterpret_cast<float4*>(acc + q) = make_float4(v[q], v[q + 1], v[q + 2], v[q + 3]);
+            } else {
 #pragma unroll
-                for (int q = 0; q < 32; q += 8)
-                  *reinterpret_cast<uint4*>(dst + c + q) =
-                      make_uint4(pack_bf16x2(v[q], v[q + 1]), pack_bf16x2(v[q + 2], v[q + 3]),
-                                 pack_bf16x2(v[q + 4], v[q + 5]), pack_bf16x2(v[q + 6], v[q + 7]));
-              }
+              for (int q = 0; q < 64; q += 8)
+                *reinterpret_cast<uint4*>(dst + q) =
+                    make_uint4(pack_bf16x2(v[q], v[q + 1]), pack_bf16x2(v[q + 2], v[q + 3]),
+                               pack_bf16x2(v[q + 4], v[q + 5]), pack_bf16x2(v[q + 6], v[q + 7]));
             }
           }
           tc_fence_before();

@@ -182,40 +182,64 @@ attention_fwd_kernel(const __grid_constant__ CUtensorMap tmap_qkv, const __grid_
       }
       mbar_wait(s_full, unit_phase);
       tc_fence_after();
+      // Both passes are software-pipelined: the tcgen05.ld of chunk c+1 is in flight while chunk c is processed
+      // (tcgen05.wait::ld waits for every outstanding load, so the next load is issued right after the wait).
       // pass 1: row maximum
       float m = -INFINITY;
-      for (int c = 0; c < S; c += 32) {
-        uint32_t r[32];
-        tmem_ld_32x32b_x32(t_row + c, r);
-        tmem_ld_wait();
+      {
+        uint32_t ra[32], rb[32];
+        tmem_ld_32x32b_x32(t_row, ra);
+        for (int c = 0; c < S; c += 64) {
+          tmem_ld_wait();
+          tmem_ld_32x32b_x32(t_row + c + 32, rb);
 #pragma unroll
-        for (int i = 0; i < 32; ++i) {
-          float v = __uint_as_float(r[i]);
-          if (has_mask) v += sBias[c + i];
-          m = fmaxf(m, v);
+          for (int i = 0; i < 32; ++i) {
+            float v = __uint_as_float(ra[i]);
+            if (has_mask) v += sBias[c + i];
+            m = fmaxf(m, v);
+          }
+          tmem_ld_wait();
+          if (c + 64 < S) tmem_ld_32x32b_x32(t_row + c + 64, ra);
+#pragma unroll
+          for (int i = 0; i < 32; ++i) {
+            float v = __uint_as_float(rb[i]);
+            if (has_mask) v += sBias[c + 32 + i];
+            m = fmaxf(m, v);
+          }
         }
       }
       const float m_scaled = (m == -INFINITY) ? 0.f : m * p.scale_log2;
       // pass 2: p = exp2(s * scale_log2 - m_scaled); packed bf16 pairs overwrite the scores in place
       float sum = 0.f;
-      for (int c = 0; c < S; c += 32) {
-        uint32_t r[32];
-        tmem_ld_32x32b_x32(t_row + c, r);
-        tmem_ld_wait();
-        uint32_t pk[16];
+      {
+        uint32_t ra[32], rb[32];
+        tmem_ld_32x32b_x32(t_row, ra);
+        for (int c = 0; c < S; c += 64) {
 #pragma unroll
-        for (int i = 0; i < 32; i += 2) {
-          float v0 = __uint_as_float(r[i]), v1 = __uint_as_float(r[i + 1]);
-          if (has_mask) { v0 += sBias[c + i]; v1 += sBias[c + i + 1]; }
-          const float e0 = ex2f(fmaf(v0, p.scale_log2, -m_scaled));
-          const float e1 = ex2f(fmaf(v1, p.scale_log2, -m_scaled));
-          // the row sum uses the bf16-rounded probabilities that the P V product will actually see
-          const uint32_t packed = pack_bf16x2(e0, e1);
-          const float2 back = unpack_bf16x2(packed);
-          sum += back.x + back.y;
-          pk[i >> 1] = packed;
+          for (int half = 0; half < 2; ++half) {
+            tmem_ld_wait();
+            uint32_t (&cur)[32] = half == 0 ? ra : rb;
+            const int cc = c + half * 32;
+            if (half == 0) tmem_ld_32x32b_x32(t_row + c + 32, rb);
+            else if (c + 64 < S) tmem_ld_32x32b_x32(t_row + c + 64, ra);
+            uint32_t pk[16];
+#pragma unroll
+            for (int i = 0; i < 32; i += 2) {
+              float v0 = __uint_as_float(cur[i]), v1 = __uint_as_float(cur[i + 1]);
+              if (has_mask) { v0 += sBias[cc + i]; v1 += sBias[cc + i + 1]; }
+              const float e0 = ex2f(fmaf(v0, p.scale_log2, -m_scaled));
+              const float e1 = ex2f(fmaf(v1, p.scale_log2, -m_scaled));
+              // the row sum uses the bf16-rounded probabilities that the P V product will actually see
+              const uint32_t packed = pack_bf16x2(e0, e1);
+              const float2 back = unpack_bf16x2(packed);
+              sum += back.x + back.y;
+              pk[i >> 1] = packed;
+            }
+            // in-place: columns [cc/2, cc/2 + 16) were read two or more chunks ago; the load in flight reads
+            // columns >= cc + 32
+            tmem_st_32x32b_x16(t_row + (cc >> 1), pk);
+          }
         }
-        tmem_st_32x32b_x16(t_row + (c >> 1), pk);
       }
       tmem_st_wait();
       tc_fence_before();

@@ -82,12 +82,19 @@ def gemm(a: torch.Tensor, b: torch.Tensor, out: torch.Tensor, *, a_mn_major: boo
 
 
 def pick_split_k(m_out: int, n_out: int, k_red: int, sms: int, block_n: int = 256) -> int:
-    """Split the reduction so that (tiles x splits) fills the machine (wgrad has few output tiles)."""
-    tiles = ((m_out + 127) // 128) * ((n_out + block_n - 1) // block_n)
+    """Split the reduction so that (output tiles x splits) fills whole waves of CTA pairs: weight gradients have few
+    output tiles (e.g. 3072 x 1024 = 48 tiles of 256 x 256 for 74 pairs). The smallest split within 2 % of the best
+    wave efficiency wins (every extra split is another fp32 red.add pass over the output)."""
+    pairs = max(sms // 2, 1)
+    tiles = ((m_out + 255) // 256) * ((n_out + 255) // 256)
     kb = max(k_red // 64, 1)
-    if tiles >= sms:
-        return 1
-    return max(1, min(kb, sms // tiles))
+    best_s, best_eff = 1, 0.0
+    for s in range(1, min(kb, 16) + 1):
+        work = tiles * s
+        eff = work / (((work + pairs - 1) // pairs) * pairs)
+        if eff > best_eff + 0.02:
+            best_s, best_eff = s, eff
+    return best_s
 
 
 class _LinearFn(torch.autograd.Function):
