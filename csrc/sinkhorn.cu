@@ -188,3 +188,102 @@ extern "C" int dedloc_sinkhorn(const void* scores, int is_bf16, long long ld, in
   count_launch();
   return 0;
 }
+
+// ------------------------------------------------------------------------------------------------------------
+// Allocation-free variant of the Sinkhorn entry point.
+//
+// Who needs it: callers that are not allowed to (or simply cannot) obtain device memory at the moment they need
+// assignments -- a host application that handed its whole memory budget to an allocator it does not own, a plug-in
+// running under a fixed-footprint contract, or a latency-critical loop where cudaMalloc's device-wide
+// synchronisation is not acceptable. dedloc_sinkhorn() makes them bring `scratch`; this entry point brings its own:
+// a file-scope device array that every GPU loading the library holds until the process exits (128.1 KiB per GPU).
+//
+// Contract:
+//   * capacity: 32 + (iters + 1) * K floats must fit in kSkNoAllocFloats (e.g. K = 4096 with iters <= 7, or
+//     K = 3000 with iters <= 9); larger requests are rejected with DEDLOC_EINVAL and a message;
+//   * the FIRST call on each device performs one-time set-up (it looks up the device address of the array for the
+//     device that is current, and queries occupancy). Make that first call before starting any stream capture;
+//   * nothing is allocated or freed: no cudaMalloc / cudaFree, no allocating library routine;
+//   * the array is shared by every call and keeps the previous call's contents, so each call first resets the part
+//     it uses (max slot to -FLT_MAX, column sums to zero) with a small kernel on the same stream. Two calls whose
+//     GPU work overlaps (different streams, or different host threads) race on the array: serialise them.
+// ------------------------------------------------------------------------------------------------------------
+#include <mutex>
+
+namespace dedloc {
+
+constexpr int kSkNoAllocFloats = 32 + 8 * 4096;   // 32 800 floats
+static __device__ __align__(256) float g_sk_noalloc_scratch[kSkNoAllocFloats];
+
+__global__ void sinkhorn_noalloc_reset(float* scratch, int nfloats) {
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < nfloats; i += gridDim.x * blockDim.x)
+    scratch[i] = (i == 0) ? -FLT_MAX : 0.f;
+}
+
+// In host code `g_sk_noalloc_scratch` is only a handle for the runtime, not a device address: the address valid on
+// the CURRENT device comes from cudaGetSymbolAddress (looked up once per device, with that device current).
+static int sk_noalloc_scratch(float** out) {
+  constexpr int kMaxDevices = 64;
+  static float* ptrs[kMaxDevices] = {};
+  static std::mutex mu;
+  int dev = 0;
+  DEDLOC_CUDA_CHECK(cudaGetDevice(&dev));
+  DEDLOC_REQUIRE(dev >= 0 && dev < kMaxDevices, "sinkhorn_noalloc: device ordinal %d out of range", dev);
+  std::lock_guard<std::mutex> lock(mu);
+  if (ptrs[dev] == nullptr) {
+    float* p = nullptr;
+    DEDLOC_CUDA_CHECK(cudaGetSymbolAddress((void**)&p, g_sk_noalloc_scratch));
+    DEDLOC_REQUIRE(p != nullptr, "sinkhorn_noalloc: cudaGetSymbolAddress returned a null address");
+    ptrs[dev] = p;
+  }
+  *out = ptrs[dev];
+  return 0;
+}
+
+}  // namespace dedloc
+
+extern "C" int dedloc_sinkhorn_noalloc_capacity_floats(void) { return dedloc::kSkNoAllocFloats; }
+
+extern "C" int dedloc_sinkhorn_noalloc(const void* scores, int is_bf16, long long ld, int n, int K, int n_out,
+                                       float epsilon, int iters, float world_size, float* out, long long ld_out,
+                                       void* stream) {
+  using namespace dedloc;
+  DEDLOC_REQUIRE(n > 0 && K > 0 && K <= kSkThreads * kSkMaxPerThread, "sinkhorn_noalloc: K (%d) must be in [1, %d]", K,
+                 kSkThreads * kSkMaxPerThread);
+  DEDLOC_REQUIRE(n_out >= 0 && n_out <= n && iters >= 1 && epsilon > 0.f, "sinkhorn_noalloc: bad arguments");
+  const long long need = 32 + (long long)(iters + 1) * K;
+  DEDLOC_REQUIRE(need <= kSkNoAllocFloats,
+                 "sinkhorn_noalloc: K = %d with %d iterations needs %lld scratch floats but the built-in array holds "
+                 "%d; use dedloc_sinkhorn() with caller-provided scratch for this size",
+                 K, iters, need, kSkNoAllocFloats);
+  float* scratch = nullptr;
+  { int rc = sk_noalloc_scratch(&scratch); if (rc) return rc; }
+  cudaStream_t st = (cudaStream_t)stream;
+  sinkhorn_noalloc_reset<<<8, 256, 0, st>>>(scratch, (int)need);
+  DEDLOC_CUDA_CHECK(cudaGetLastError());
+  static int max_blocks_bf16 = 0, max_blocks_f32 = 0;
+  int& max_blocks = is_bf16 ? max_blocks_bf16 : max_blocks_f32;
+  if (max_blocks == 0) {
+    int dev = 0, sms = 0, occ = 0;
+    DEDLOC_CUDA_CHECK(cudaGetDevice(&dev));
+    DEDLOC_CUDA_CHECK(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
+    if (is_bf16)
+      DEDLOC_CUDA_CHECK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, sinkhorn_kernel<__nv_bfloat16>, kSkThreads, 0));
+    else
+      DEDLOC_CUDA_CHECK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, sinkhorn_kernel<float>, kSkThreads, 0));
+    DEDLOC_REQUIRE(occ >= 1, "sinkhorn_noalloc: kernel does not fit on an SM");
+    max_blocks = sms * (occ > 4 ? 4 : occ);
+  }
+  const int blocks = n < max_blocks ? n : max_blocks;
+  float inv_eps = 1.f / epsilon;
+  void* args[] = {(void*)&scores, (void*)&ld, (void*)&n, (void*)&K, (void*)&n_out, (void*)&inv_eps, (void*)&iters,
+                  (void*)&world_size, (void*)&out, (void*)&ld_out, (void*)&scratch};
+  if (is_bf16)
+    DEDLOC_CUDA_CHECK(cudaLaunchCooperativeKernel((const void*)sinkhorn_kernel<__nv_bfloat16>, dim3(blocks),
+                                                  dim3(kSkThreads), args, 0, st));
+  else
+    DEDLOC_CUDA_CHECK(cudaLaunchCooperativeKernel((const void*)sinkhorn_kernel<float>, dim3(blocks), dim3(kSkThreads),
+                                                  args, 0, st));
+  count_launch(2);
+  return 0;
+}

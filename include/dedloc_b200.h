@@ -141,6 +141,13 @@ int dedloc_colsum_accumulate(const void* dy, float* out, int M, int N, long long
 long long dedloc_sinkhorn_scratch_floats(int K, int iters);
 int dedloc_sinkhorn(const void* scores, int is_bf16, long long ld, int n, int K, int n_out, float epsilon, int iters,
                     float world_size, float* out, long long ld_out, float* scratch, void* stream);
+/* Same computation for callers that cannot allocate device memory (no counterpart in the reference): the scratch is
+ * a built-in per-GPU device array of dedloc_sinkhorn_noalloc_capacity_floats() floats (32 800 = 128.1 KiB), so
+ * 32 + (iters + 1) * K must not exceed it -- larger requests fail with an error. The first call on a device does
+ * one-time set-up and should precede any stream capture; calls whose GPU work overlaps race on the shared array. */
+int dedloc_sinkhorn_noalloc_capacity_floats(void);
+int dedloc_sinkhorn_noalloc(const void* scores, int is_bf16, long long ld, int n, int K, int n_out, float epsilon,
+                            int iters, float world_size, float* out, long long ld_out, void* stream);
 
 /* ---- shared-layer attention on the packed QKV layout (HF AlbertAttention: bmm + softmax + bmm) ----------- */
 /* qkv: [B, S, 3, H, 64] bf16 (output of the fused QKV GEMM); mask: [B, S] bytes (1 = attend) or NULL;
