@@ -116,10 +116,17 @@ __global__ void __launch_bounds__(kARThreads, 2) fused_allreduce_kernel(const __
 
     long long cur_cb = -1;
     unsigned int bad_count = 0;
-    for (long long c = c0; c < c1; ++c) {
-      const long long e = c * kChunk + tid * 8;
+    // Narrow payloads (<= 2 bytes / element) are processed two chunks per iteration: the loads of BOTH chunks from
+    // every peer are issued before any is consumed, doubling the bytes in flight per thread (NVLink needs ~2 MB in
+    // flight chip-wide; with few peers one chunk per thread is not enough).
+    constexpr int kUnroll = (CODEC == CODEC_NONE) ? 1 : 2;
+    constexpr int kBatch = (CODEC == CODEC_NONE) ? 4 : 8;  // fp32 payloads are 2x uint4 per peer
+    for (long long cbase = c0; cbase < c1;) {
+      int nch = (int)((c1 - cbase) < kUnroll ? (c1 - cbase) : kUnroll);
       if constexpr (kIsLut) {
-        const long long cb = c / kCodecBlockChunks;
+        // both chunks of an iteration must share one codebook block
+        if (nch == 2 && (cbase / kCodecBlockChunks) != ((cbase + 1) / kCodecBlockChunks)) nch = 1;
+        const long long cb = cbase / kCodecBlockChunks;
         if (cb != cur_cb) {
           __syncthreads();
           for (int q = 0; q < p.P; ++q)
@@ -128,70 +135,86 @@ __global__ void __launch_bounds__(kARThreads, 2) fused_allreduce_kernel(const __
           cur_cb = cb;
         }
       }
-      float acc[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
-      // issue the loads of up to 8 peers before consuming any of them (memory-level parallelism over NVLink)
-      constexpr int kBatch = (CODEC == CODEC_NONE) ? 4 : 8;  // fp32 payloads are 2x uint4 per peer
+      float accs[kUnroll][8];
+#pragma unroll
+      for (int u = 0; u < kUnroll; ++u)
+#pragma unroll
+        for (int i = 0; i < 8; ++i) accs[u][i] = 0.f;
       for (int q0 = 0; q0 < p.P; q0 += kBatch) {
-        Raw8 raw[kBatch];
+        Raw8 raw[kUnroll][kBatch];
 #pragma unroll
-        for (int k = 0; k < kBatch; ++k)
-          if (q0 + k < p.P && p.w[q0 + k] != 0.f) load_raw8<CODEC>(p.send[q0 + k], e, raw[k]);
+        for (int u = 0; u < kUnroll; ++u)
 #pragma unroll
-        for (int k = 0; k < kBatch; ++k) {
-          if (q0 + k < p.P && p.w[q0 + k] != 0.f) {
-            float x[8];
-            decode8<CODEC>(raw[k], p.aux[q0 + k], kIsLut ? &lut[(q0 + k) * 256] : nullptr, e, c, x);
-            const float w = p.w[q0 + k];
+          for (int k = 0; k < kBatch; ++k)
+            if (u < nch && q0 + k < p.P && p.w[q0 + k] != 0.f)
+              load_raw8<CODEC>(p.send[q0 + k], (cbase + u) * kChunk + tid * 8, raw[u][k]);
 #pragma unroll
-            for (int i = 0; i < 8; ++i) acc[i] = fmaf(w, x[i], acc[i]);
+        for (int u = 0; u < kUnroll; ++u)
+#pragma unroll
+          for (int k = 0; k < kBatch; ++k) {
+            if (u < nch && q0 + k < p.P && p.w[q0 + k] != 0.f) {
+              float x[8];
+              decode8<CODEC>(raw[u][k], p.aux[q0 + k], kIsLut ? &lut[(q0 + k) * 256] : nullptr,
+                             (cbase + u) * kChunk + tid * 8, cbase + u, x);
+              const float w = p.w[q0 + k];
+#pragma unroll
+              for (int i = 0; i < 8; ++i) accs[u][i] = fmaf(w, x[i], accs[u][i]);
+            }
           }
-        }
       }
-      if (any_nonfinite8(acc)) ++bad_count;
-
-      if constexpr (MODE == DEDLOC_AR_MEAN) {
-        const uint4 lo = make_uint4(__float_as_uint(acc[0]), __float_as_uint(acc[1]), __float_as_uint(acc[2]), __float_as_uint(acc[3]));
-        const uint4 hi = make_uint4(__float_as_uint(acc[4]), __float_as_uint(acc[5]), __float_as_uint(acc[6]), __float_as_uint(acc[7]));
-        const uint4 h16 = make_uint4(pack_bf16x2(acc[0], acc[1]), pack_bf16x2(acc[2], acc[3]),
-                                     pack_bf16x2(acc[4], acc[5]), pack_bf16x2(acc[6], acc[7]));
-        for (int q = 0; q < p.P; ++q) {
-          if (p.out32[q]) {
-            uint4* o = reinterpret_cast<uint4*>(p.out32[q] + e);
-            st_stream_v4(o, lo);
-            st_stream_v4(o + 1, hi);
-          }
-          if (p.out16[q]) st_stream_v4(p.out16[q] + e, h16);
-        }
-      } else {
-        float* gs = p.gavg + (e - cbeg * kChunk);
-        reinterpret_cast<float4*>(gs)[0] = make_float4(acc[0], acc[1], acc[2], acc[3]);
-        reinterpret_cast<float4*>(gs)[1] = make_float4(acc[4], acc[5], acc[6], acc[7]);
-        const float4* pp = reinterpret_cast<const float4*>(p.out32[me] + e);
-        const float4 pa = pp[0], pb = pp[1];
-        const float pv[8] = {pa.x, pa.y, pa.z, pa.w, pb.x, pb.y, pb.z, pb.w};
-        float s1 = 0.f, s2 = 0.f;
-        if constexpr (MODE == DEDLOC_AR_LAMB) {
-          const float4* mp = reinterpret_cast<const float4*>(p.m[me] + e);
-          const float4* vp = reinterpret_cast<const float4*>(p.v[me] + e);
-          const float4 ma = mp[0], mb = mp[1], va = vp[0], vb = vp[1];
-          const float mv[8] = {ma.x, ma.y, ma.z, ma.w, mb.x, mb.y, mb.z, mb.w};
-          const float vv[8] = {va.x, va.y, va.z, va.w, vb.x, vb.y, vb.z, vb.w};
-          const float wd = p.t_wd[p.chunk_tid[c]];
 #pragma unroll
-          for (int i = 0; i < 8; ++i) {
-            const float m1 = p.beta1 * mv[i] + (1.f - p.beta1) * acc[i];
-            const float v1 = p.beta2 * vv[i] + (1.f - p.beta2) * acc[i] * acc[i];
-            const float u = m1 / (sqrtf(v1) + p.eps) + wd * pv[i];
-            s1 = fmaf(pv[i], pv[i], s1);
-            s2 = fmaf(u, u, s2);
+      for (int u = 0; u < kUnroll; ++u) {
+        if (u >= nch) break;
+        const long long c = cbase + u;
+        const long long e = c * kChunk + tid * 8;
+        float (&acc)[8] = accs[u];
+      if (any_nonfinite8(acc)) ++bad_count;
+  
+        if constexpr (MODE == DEDLOC_AR_MEAN) {
+          const uint4 lo = make_uint4(__float_as_uint(acc[0]), __float_as_uint(acc[1]), __float_as_uint(acc[2]), __float_as_uint(acc[3]));
+          const uint4 hi = make_uint4(__float_as_uint(acc[4]), __float_as_uint(acc[5]), __float_as_uint(acc[6]), __float_as_uint(acc[7]));
+          const uint4 h16 = make_uint4(pack_bf16x2(acc[0], acc[1]), pack_bf16x2(acc[2], acc[3]),
+                                       pack_bf16x2(acc[4], acc[5]), pack_bf16x2(acc[6], acc[7]));
+          for (int q = 0; q < p.P; ++q) {
+            if (p.out32[q]) {
+              uint4* o = reinterpret_cast<uint4*>(p.out32[q] + e);
+              st_stream_v4(o, lo);
+              st_stream_v4(o + 1, hi);
+            }
+            if (p.out16[q]) st_stream_v4(p.out16[q] + e, h16);
           }
         } else {
-#pragma unroll
-          for (int i = 0; i < 8; ++i) { s1 = fmaf(pv[i], pv[i], s1); s2 = fmaf(acc[i], acc[i], s2); }
+          float* gs = p.gavg + (e - cbeg * kChunk);
+          reinterpret_cast<float4*>(gs)[0] = make_float4(acc[0], acc[1], acc[2], acc[3]);
+          reinterpret_cast<float4*>(gs)[1] = make_float4(acc[4], acc[5], acc[6], acc[7]);
+          const float4* pp = reinterpret_cast<const float4*>(p.out32[me] + e);
+          const float4 pa = pp[0], pb = pp[1];
+          const float pv[8] = {pa.x, pa.y, pa.z, pa.w, pb.x, pb.y, pb.z, pb.w};
+          float s1 = 0.f, s2 = 0.f;
+          if constexpr (MODE == DEDLOC_AR_LAMB) {
+            const float4* mp = reinterpret_cast<const float4*>(p.m[me] + e);
+            const float4* vp = reinterpret_cast<const float4*>(p.v[me] + e);
+            const float4 ma = mp[0], mb = mp[1], va = vp[0], vb = vp[1];
+            const float mv[8] = {ma.x, ma.y, ma.z, ma.w, mb.x, mb.y, mb.z, mb.w};
+            const float vv[8] = {va.x, va.y, va.z, va.w, vb.x, vb.y, vb.z, vb.w};
+            const float wd = p.t_wd[p.chunk_tid[c]];
+  #pragma unroll
+            for (int i = 0; i < 8; ++i) {
+              const float m1 = p.beta1 * mv[i] + (1.f - p.beta1) * acc[i];
+              const float v1 = p.beta2 * vv[i] + (1.f - p.beta2) * acc[i] * acc[i];
+              const float u = m1 / (sqrtf(v1) + p.eps) + wd * pv[i];
+              s1 = fmaf(pv[i], pv[i], s1);
+              s2 = fmaf(u, u, s2);
+            }
+          } else {
+  #pragma unroll
+            for (int i = 0; i < 8; ++i) { s1 = fmaf(pv[i], pv[i], s1); s2 = fmaf(acc[i], acc[i], s2); }
+          }
+          const float2 r = block_sum2(s1, s2, red);
+          if (tid == 0) reinterpret_cast<float2*>(p.chunk_stats)[c - cbeg] = r;
         }
-        const float2 r = block_sum2(s1, s2, red);
-        if (tid == 0) reinterpret_cast<float2*>(p.chunk_stats)[c - cbeg] = r;
       }
+      cbase += nch;
     }
     if (bad_count) atomicAdd(p.status + 2, bad_count);
 
