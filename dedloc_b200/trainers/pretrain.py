@@ -7,6 +7,8 @@ WikiText-shaped synthetic batches (15 % masked tokens, 50 % swapped sentence ord
 """
 from __future__ import annotations
 
+import collections
+
 import math
 from dataclasses import dataclass
 from typing import Dict, Iterator, List, Optional
@@ -99,6 +101,11 @@ class PeerConfig:
     default_refresh_period: float = 0.2
     client_mode: bool = False
     impl: str = "native"
+    # how many launched-but-unfinished micro-steps the host may run ahead of the GPU. The progress this peer
+    # reports to the collaboration counts launched samples, so an unbounded queue makes every peer overshoot
+    # target_batch_size by the queue depth; 1 keeps the GPU fed while the control plane (progress report, DHT
+    # re-fetch, matchmaking) of a global step hides under the micro-step that is still running.
+    max_inflight_micro_steps: int = 1
 
 
 class PeerTrainer:
@@ -110,6 +117,7 @@ class PeerTrainer:
         self._graph = None
         self._static_batch: Optional[Dict[str, torch.Tensor]] = None
         self._graph_launches = 0
+        self._inflight: collections.deque = collections.deque()
 
     # ---------------------------------------------------------------- CUDA-graph capture of the micro-step
     def _forward_backward(self, batch: Dict[str, torch.Tensor]) -> None:
@@ -174,6 +182,12 @@ class PeerTrainer:
             self._forward_backward(batch)
         self.mini_steps += 1
         self.samples_processed += n
+        if self.device.type == "cuda":
+            done = torch.cuda.Event()
+            done.record()
+            self._inflight.append(done)
+            while len(self._inflight) > max(self.cfg.max_inflight_micro_steps, 0):
+                self._inflight.popleft().synchronize()
         return bool(self.collab.step(batch_size=n))
 
     def pop_mean_loss(self) -> float:
