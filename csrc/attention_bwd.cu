@@ -1,29 +1,35 @@
 // Shared-layer attention, backward: dQ, dK, dV written straight into the PACKED [B, S, 3, H, 64]
 // gradient of the fused QKV projection -- the stack / unbind / contiguous copies of the autograd path disappear.
 //
-// One CTA owns one (batch, head). For every key block j (128 keys) and query block i (128 queries):
-//   MMA1  S^T  = K_j Q_i^T              (keys on TMEM lanes, queries on columns)
-//   MMA2  dP^T = V_j dO_i^T
-//   warps 4-7 (thread = key row): P^T = exp2(S^T*c - lse_q), dS^T = P^T (dP^T - D_q) * scale, both written as
-//         bf16 into 128B-swizzled shared memory [key][query]
-//   MMA3  dV_j += P^T dO_i      MMA4  dK_j += dS^T Q_i      (A = the swizzled tiles, K-major; accumulators stay
-//                                                            in tensor memory across the i loop)
-//   MMA5  dQ_i(partial) = dS K_j   (A = the SAME dS^T tile read as an MN-major operand -> no transposed copy)
-//   warps 4-7 (thread = query row): dQ partial += into an fp32 L2-resident scratch; on the last key block the
-//         row is converted to bf16 and stored into dqkv
-// D_q = rowsum(dO * O) and lse_q are staged in shared memory once per (batch, head). MMA1/2 of the next step are
-// issued right behind MMA3-5, so they overlap with the dQ read-out.
+// One CTA owns one (batch, head) at a time; a step is (key block j of 128 keys) x (query block i of 128 queries),
+// handled as two HALVES of 64 queries (a, b) so that the tensor core works on one half while the other half is in
+// the exp / dS arithmetic:
+//   warp 0      TMA: K_j, V_j (2 stages), Q_i, dO_i (2 stages)
+//   warp 1      tcgen05.mma issuer
+//                 1h  S^T_h  = K_j Q_h^T,  dP^T_h = V_j dO_h^T          (keys on TMEM lanes, 64 queries on columns)
+//                 2h  dV_j  += P^T_h dO_h, dK_j  += dS^T_h Q_h          (A = bf16 P^T / dS^T read FROM TENSOR MEMORY)
+//                 3   dQ_i(partial) = dS K_j    (A = the dS^T tile in shared memory read as an MN-major operand)
+//               issue order per step t:  wait P_a -> 2a(t), 1a(t+1);  wait P_b -> 2b(t), 3(t), 1b(t+1)
+//   warp 2      TMEM allocator
+//   warp 3      per (batch, head): lse*log2(e), D = rowsum(dO * O) * scale and the key mask, staged in shared memory
+//               one (batch, head) ahead of the compute warps
+//   warps 4-7   half a, warps 8-11 half b (thread = key row): P^T = exp2(S^T c - lse_q), dS^T = P^T (dP^T c' - D_q),
+//               both packed to bf16 IN PLACE over the fp32 scores (tcgen05.st); dS^T also goes to 128B-swizzled
+//               shared memory for MMA 3. The same warps drain dQ (thread = query row, 32 of the 64 columns per
+//               half-group) through an fp32 L2-resident scratch that accumulates over the key blocks, and dK_j / dV_j
+//               after the last query block.
 #include "gemm_common.cuh"
 
 namespace dedloc {
 
-constexpr int kAbThreads = 256;
+constexpr int kAbThreads = 384;
 constexpr int kAbD = 64;
 constexpr int kAbBlk = 128;
 constexpr int kAbMaxS = 512;
 constexpr int kAbTile = kAbBlk * 128;               // 16 KB: 128 rows x 128 B
-// smem: K_j, V_j, Q_i x2, dO_i x2 (6 tiles) + P^T, dS^T (2 x 2 tiles) + vectors + barriers
-constexpr int kAbSmem = 6 * kAbTile + 4 * kAbTile + 3 * kAbMaxS * 4 + 256 + 1024;
+// smem: K, V x 2 stages; Q, dO x 2 stages; dS^T x 2 buffers x 2 halves (12 tiles) + staged vectors x 2 + barriers
+constexpr int kAbVecBytes = kAbMaxS * (8 + 4);      // float2 {lse2, D*scale} + float key_ok per query / key
+constexpr int kAbSmem = 12 * kAbTile + 2 * kAbVecBytes + 512 + 1024;
 
 struct AttBwdParams {
   int B, S, H;
@@ -33,7 +39,7 @@ struct AttBwdParams {
   const __nv_bfloat16* dout;       // [B, S, H*64]
   const float* lse;                // [B, H, S]
   __nv_bfloat16* dqkv;             // [B, S, 3, H, 64]
-  float* dq_scratch;               // [gridDim.x, S, 64] fp32
+  float* dq_scratch;               // [gridDim.x, S, 64] fp32, see drain_dq for the layout
 };
 
 __device__ __forceinline__ float ex2f_b(float x) {
@@ -42,46 +48,51 @@ __device__ __forceinline__ float ex2f_b(float x) {
   return y;
 }
 
+template <int NBLK>
 __global__ void __launch_bounds__(kAbThreads, 1)
 attention_bwd_kernel(const __grid_constant__ CUtensorMap tmap_qkv, const __grid_constant__ CUtensorMap tmap_do,
                      const __grid_constant__ AttBwdParams p) {
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
-  uint8_t* sK = smem;
-  uint8_t* sV = smem + kAbTile;
-  uint8_t* sQ = smem + 2 * kAbTile;                 // 2 stages
-  uint8_t* sdO = smem + 4 * kAbTile;                // 2 stages
-  uint8_t* sP = smem + 6 * kAbTile;                 // [2 blocks of 64 queries][128 keys][128 B]
-  uint8_t* sdS = smem + 8 * kAbTile;
-  float* sLse = reinterpret_cast<float*>(smem + 10 * kAbTile);   // lse * log2(e), per query
-  float* sD = sLse + kAbMaxS;                                     // rowsum(dO * O), per query
-  float* sKeyOk = sD + kAbMaxS;                                   // 1 / 0 per key
-  uint64_t* bars = reinterpret_cast<uint64_t*>(sKeyOk + kAbMaxS);
-  uint64_t* kv_full = bars + 0;
-  uint64_t* kv_empty = bars + 1;
-  uint64_t* qdo_full = bars + 2;    // [2]
-  uint64_t* qdo_empty = bars + 4;   // [2]
-  uint64_t* s_full = bars + 6;
-  uint64_t* pds_full = bars + 7;
-  uint64_t* dq_full = bars + 8;
-  uint64_t* dq_empty = bars + 9;
-  uint64_t* dkv_full = bars + 10;
-  uint64_t* dkv_empty = bars + 11;
-  uint64_t* vec_ready = bars + 12;  // lse / D / key mask of this (b, h) are staged
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 13);
+  uint8_t* sK = smem;                               // 2 stages
+  uint8_t* sV = smem + 2 * kAbTile;                 // 2 stages
+  uint8_t* sQ = smem + 4 * kAbTile;                 // 2 stages
+  uint8_t* sdO = smem + 6 * kAbTile;                // 2 stages
+  uint8_t* sdS = smem + 8 * kAbTile;                // [2 buffers][2 halves of 64 queries][128 keys][128 B]
+  uint8_t* sVecBase = smem + 12 * kAbTile;          // [2 stages]{ float2 vec[512]; float key_ok[512]; }
+  uint64_t* bars = reinterpret_cast<uint64_t*>(sVecBase + 2 * kAbVecBytes);
+  uint64_t* kv_full = bars + 0;     // [2]
+  uint64_t* kv_empty = bars + 2;    // [2]
+  uint64_t* qdo_full = bars + 4;    // [2]
+  uint64_t* qdo_empty = bars + 6;   // [2]
+  uint64_t* s_full = bars + 8;      // [2] per half
+  uint64_t* p_full = bars + 10;     // [2] per half
+  uint64_t* dq_full = bars + 12;
+  uint64_t* dq_empty = bars + 13;
+  uint64_t* dkv_full = bars + 14;
+  uint64_t* dkv_empty = bars + 15;
+  uint64_t* vec_full = bars + 16;   // [2]
+  uint64_t* vec_empty = bars + 18;  // [2]
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 20);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int S = p.S, H = p.H, nblk = S / kAbBlk;
+  constexpr int nblk = NBLK;                      // key / query blocks of 128 (compile time: no integer divisions)
+  const int S = p.S, H = p.H;
   const int total_bh = p.B * H;
+  const int my_bh = (total_bh - (int)blockIdx.x + (int)gridDim.x - 1) / (int)gridDim.x;   // (batch, head)s of this CTA
+  constexpr int steps_per_bh = nblk * nblk;
+  const int T = my_bh * steps_per_bh;                                                     // steps of this CTA
 
   if (warp == 0 && lane == 0) { tma_prefetch_desc(&tmap_qkv); tma_prefetch_desc(&tmap_do); }
   if (warp == 1 && lane == 0) {
-    mbar_init(kv_full, 1); mbar_init(kv_empty, 1);
-    for (int i = 0; i < 2; ++i) { mbar_init(&qdo_full[i], 1); mbar_init(&qdo_empty[i], 1); }
-    mbar_init(s_full, 1); mbar_init(pds_full, 4);
-    mbar_init(dq_full, 1); mbar_init(dq_empty, 4);
-    mbar_init(dkv_full, 1); mbar_init(dkv_empty, 4);
-    mbar_init(vec_ready, 4);
+    for (int i = 0; i < 2; ++i) {
+      mbar_init(&kv_full[i], 1); mbar_init(&kv_empty[i], 1);
+      mbar_init(&qdo_full[i], 1); mbar_init(&qdo_empty[i], 1);
+      mbar_init(&s_full[i], 1); mbar_init(&p_full[i], 4);
+      mbar_init(&vec_full[i], 1); mbar_init(&vec_empty[i], 8);
+    }
+    mbar_init(dq_full, 1); mbar_init(dq_empty, 8);
+    mbar_init(dkv_full, 1); mbar_init(dkv_empty, 8);
     mbar_fence_init();
   }
   if (warp == 2) { tmem_alloc(tmem_slot, 512); tmem_relinquish(); }
@@ -89,244 +100,321 @@ attention_bwd_kernel(const __grid_constant__ CUtensorMap tmap_qkv, const __grid_
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
-  const uint32_t t_S = tmem_base, t_dP = tmem_base + 128, t_dV = tmem_base + 256, t_dK = tmem_base + 320,
-                 t_dQ = tmem_base + 384;
+  // columns: S^T_a | dP^T_a | S^T_b | dP^T_b (64 each; the bf16 P^T / dS^T reuse the first 32 of each) | dV | dK | dQ
+  const uint32_t t_dV = tmem_base + 256, t_dK = tmem_base + 320, t_dQ = tmem_base + 384;
 
   if (warp == 0) {
     // ===================== TMA producer =====================
     if (lane == 0) {
-      uint32_t kv_phase = 0, qphase = 0;
-      int qs = 0;
+      int t = 0, jc = 0;
       for (int bh = blockIdx.x; bh < total_bh; bh += gridDim.x) {
         const int b = bh / H, h = bh % H;
-        for (int j = 0; j < nblk; ++j) {
-          mbar_wait(kv_empty, kv_phase ^ 1);
-          mbar_expect_tx(kv_full, 2 * kAbTile);
-          tma_load_2d(sK, &tmap_qkv, kv_full, (1 * H + h) * kAbD, b * S + j * kAbBlk);
-          tma_load_2d(sV, &tmap_qkv, kv_full, (2 * H + h) * kAbD, b * S + j * kAbBlk);
-          kv_phase ^= 1;
-          for (int i = 0; i < nblk; ++i) {
-            mbar_wait(&qdo_empty[qs], qphase ^ 1);
+        for (int j = 0; j < nblk; ++j, ++jc) {
+          const int ks = jc & 1;
+          mbar_wait(&kv_empty[ks], ((jc >> 1) & 1) ^ 1);
+          mbar_expect_tx(&kv_full[ks], 2 * kAbTile);
+          tma_load_2d(sK + ks * kAbTile, &tmap_qkv, &kv_full[ks], (1 * H + h) * kAbD, b * S + j * kAbBlk);
+          tma_load_2d(sV + ks * kAbTile, &tmap_qkv, &kv_full[ks], (2 * H + h) * kAbD, b * S + j * kAbBlk);
+          for (int i = 0; i < nblk; ++i, ++t) {
+            const int qs = t & 1;
+            mbar_wait(&qdo_empty[qs], ((t >> 1) & 1) ^ 1);
             mbar_expect_tx(&qdo_full[qs], 2 * kAbTile);
             tma_load_2d(sQ + qs * kAbTile, &tmap_qkv, &qdo_full[qs], (0 * H + h) * kAbD, b * S + i * kAbBlk);
             tma_load_2d(sdO + qs * kAbTile, &tmap_do, &qdo_full[qs], h * kAbD, b * S + i * kAbBlk);
-            if (++qs == 2) { qs = 0; qphase ^= 1; }
           }
         }
       }
     }
   } else if (warp == 1) {
     // ===================== MMA issuer =====================
-    const uint32_t id_kk = make_idesc_f16(128, 128, 0, 0, 1);   // S^T, dP^T: A K-major, B K-major
-    const uint32_t id_kmn = make_idesc_f16(128, 64, 0, 1, 1);   // dV, dK: A K-major (P^T / dS^T), B MN-major (dO / Q)
+    // The whole warp runs this code and the tcgen05 instructions are predicated on the leader lane, so that every
+    // operand stays warp-uniform; descriptors are a precomputed low word plus an immediate (the high word -- SBO =
+    // 1024, version 1, SWIZZLE_128B -- is the same for all of them). A 32-clock MMA leaves no room for more.
+    const uint32_t leader = (lane == 0) ? 1u : 0u;
+    const uint32_t tb = __shfl_sync(0xffffffffu, tmem_base, 0);   // provably warp-uniform copy
+    const uint32_t u_dV = tb + 256, u_dK = tb + 320, u_dQ = tb + 384;
+    constexpr uint32_t kHi = 0x40004040u;
+    constexpr uint32_t kLboK = 1u << 16;                         // K-major: LBO = 16 B (ignored under swizzle)
+    constexpr uint32_t kLboMN = (uint32_t)(kAbTile >> 4) << 16;  // MN-major: next 64-element group = next tile
+    constexpr uint32_t kStage = kAbTile >> 4;                    // one tile, in descriptor address units
+    const uint32_t id_s = make_idesc_f16(128, 64, 0, 0, 1);     // S^T_h, dP^T_h: A K-major, B K-major, N = 64
+    const uint32_t id_ts = make_idesc_f16(128, 64, 0, 1, 1);    // dV, dK: A from TMEM, B MN-major (dO / Q)
     const uint32_t id_mnmn = make_idesc_f16(128, 64, 1, 1, 1);  // dQ: A MN-major (dS^T read as dS), B MN-major (K)
-    uint32_t kv_phase = 0, qphase = 0, step_phase = 0, j_phase = 0;
-    int qs = 0;
-    for (int bh = blockIdx.x; bh < total_bh; bh += gridDim.x) {
-      for (int j = 0; j < nblk; ++j) {
-        mbar_wait(kv_full, kv_phase);
-        kv_phase ^= 1;
-        mbar_wait(dkv_empty, j_phase ^ 1);       // previous dK_j / dV_j accumulators have been drained
-        for (int i = 0; i < nblk; ++i) {
-          mbar_wait(&qdo_full[qs], qphase);
-          tc_fence_after();
-          const uint32_t aK = smem_u32(sK), aV = smem_u32(sV);
-          const uint32_t aQ = smem_u32(sQ + qs * kAbTile), aO = smem_u32(sdO + qs * kAbTile);
-          if (lane == 0) {
+    const uint32_t bK = (smem_u32(sK) & 0x3FFFF) >> 4, bV = (smem_u32(sV) & 0x3FFFF) >> 4;
+    const uint32_t bQ = (smem_u32(sQ) & 0x3FFFF) >> 4, bO = (smem_u32(sdO) & 0x3FFFF) >> 4;
+    const uint32_t bS = (smem_u32(sdS) & 0x3FFFF) >> 4;
+    // 1h: scores of half hf for the step whose operands sit in K/V stage ks and Q/dO stage qs
+    auto issue_scores = [&](int ks, int qs, int hf) {
+      const uint32_t aK = (bK + ks * kStage) | kLboK, aV = (bV + ks * kStage) | kLboK;
+      const uint32_t aQ = (bQ + qs * kStage + hf * 512) | kLboK, aO = (bO + qs * kStage + hf * 512) | kLboK;
+      const uint32_t tS = tb + hf * 128, tP = tS + 64;
 #pragma unroll
-            for (int kk = 0; kk < 4; ++kk) {      // reduction over d = 64
-              umma_f16_ss(t_S, make_smem_desc_sw128(aK + kk * 32, 16, 1024), make_smem_desc_sw128(aQ + kk * 32, 16, 1024),
-                          id_kk, kk > 0);
-            }
+      for (int kk = 0; kk < 4; ++kk) umma_f16_ss_lo(tS, aK + kk * 2, aQ + kk * 2, kHi, id_s, kk > 0, leader);
 #pragma unroll
-            for (int kk = 0; kk < 4; ++kk) {
-              umma_f16_ss(t_dP, make_smem_desc_sw128(aV + kk * 32, 16, 1024), make_smem_desc_sw128(aO + kk * 32, 16, 1024),
-                          id_kk, kk > 0);
-            }
-            umma_commit(s_full);
-          }
-          __syncwarp();
-          mbar_wait(pds_full, step_phase);        // P^T / dS^T are in shared memory
-          mbar_wait(dq_empty, step_phase ^ 1);    // previous dQ partial has been read out
-          tc_fence_after();
-          if (lane == 0) {
-            const uint32_t aP = smem_u32(sP), aS = smem_u32(sdS);
+      for (int kk = 0; kk < 4; ++kk) umma_f16_ss_lo(tP, aV + kk * 2, aO + kk * 2, kHi, id_s, kk > 0, leader);
+      umma_commit_pred(&s_full[hf], leader);
+    };
+    // 2h: dV += P^T_h dO_h, dK += dS^T_h Q_h with A in tensor memory (16 queries = 8 columns per k-step)
+    auto issue_dkv = [&](int qs, int hf, uint32_t first) {
+      const uint32_t aQ = (bQ + qs * kStage + hf * 512) | kLboMN, aO = (bO + qs * kStage + hf * 512) | kLboMN;
+      const uint32_t tS = tb + hf * 128, tP = tS + 64;
 #pragma unroll
-            for (int kk = 0; kk < 8; ++kk) {      // reduction over the 128 queries
-              const uint32_t aoff = (kk >> 2) * kAbTile + (kk & 3) * 32;
-              umma_f16_ss(t_dV, make_smem_desc_sw128(aP + aoff, 16, 1024),
-                          make_smem_desc_sw128(aO + kk * 2048, kAbTile, 1024), id_kmn, (i > 0 || kk > 0));
-            }
+      for (int kk = 0; kk < 4; ++kk) umma_f16_ts_lo(u_dV, tS + kk * 8, aO + kk * 128, kHi, id_ts, kk > 0 ? 1u : first, leader);
 #pragma unroll
-            for (int kk = 0; kk < 8; ++kk) {
-              const uint32_t aoff = (kk >> 2) * kAbTile + (kk & 3) * 32;
-              umma_f16_ss(t_dK, make_smem_desc_sw128(aS + aoff, 16, 1024),
-                          make_smem_desc_sw128(aQ + kk * 2048, kAbTile, 1024), id_kmn, (i > 0 || kk > 0));
-            }
-#pragma unroll
-            for (int kk = 0; kk < 8; ++kk) {      // reduction over the 128 keys
-              umma_f16_ss(t_dQ, make_smem_desc_sw128(aS + kk * 2048, kAbTile, 1024),
-                          make_smem_desc_sw128(aK + kk * 2048, kAbTile, 1024), id_mnmn, kk > 0);
-            }
-            umma_commit(&qdo_empty[qs]);
-            umma_commit(dq_full);
-            if (i == nblk - 1) { umma_commit(dkv_full); umma_commit(kv_empty); }
-          }
-          __syncwarp();
-          step_phase ^= 1;
-          if (++qs == 2) { qs = 0; qphase ^= 1; }
-        }
-        j_phase ^= 1;
+      for (int kk = 0; kk < 4; ++kk) umma_f16_ts_lo(u_dK, tP + kk * 8, aQ + kk * 128, kHi, id_ts, kk > 0 ? 1u : first, leader);
+    };
+    if (T > 0) {
+      mbar_wait(&kv_full[0], 0);
+      mbar_wait(&qdo_full[0], 0);
+      tc_fence_after();
+      issue_scores(0, 0, 0);
+      issue_scores(0, 0, 1);
+    }
+    int i = 0, jc = 0;                       // query block of step t, running key-block counter
+    for (int t = 0; t < T; ++t) {
+      const int ks = jc & 1, qs = t & 1;
+      const bool last_i = (i == nblk - 1);
+      // operands of step t+1
+      const int n_jc = last_i ? jc + 1 : jc, n_ks = n_jc & 1, n_qs = qs ^ 1;
+      mbar_wait(&p_full[0], t & 1);
+      if (i == 0 && jc > 0) mbar_wait(dkv_empty, (jc - 1) & 1);   // dK / dV of the previous key block are drained
+      tc_fence_after();
+      issue_dkv(qs, 0, i == 0 ? 0u : 1u);
+      if (t + 1 < T) {
+        if (last_i) mbar_wait(&kv_full[n_ks], (n_jc >> 1) & 1);
+        mbar_wait(&qdo_full[n_qs], ((t + 1) >> 1) & 1);
+        tc_fence_after();
+        issue_scores(n_ks, n_qs, 0);
       }
+      mbar_wait(&p_full[1], t & 1);
+      tc_fence_after();
+      issue_dkv(qs, 1, 1u);
+      umma_commit_pred(&qdo_empty[qs], leader);                   // Q_i / dO_i are not needed by MMA 3
+      if (t > 0) mbar_wait(dq_empty, (t - 1) & 1);                // dQ partial of step t-1 has been read out
+      tc_fence_after();
+      {
+        const uint32_t aS = (bS + (t & 1) * 2 * kStage) | kLboMN, aK = (bK + ks * kStage) | kLboMN;
+#pragma unroll
+        for (int kk = 0; kk < 8; ++kk)       // reduction over the 128 keys
+          umma_f16_ss_lo(u_dQ, aS + kk * 128, aK + kk * 128, kHi, id_mnmn, kk > 0, leader);
+        umma_commit_pred(dq_full, leader);
+        if (last_i) { umma_commit_pred(dkv_full, leader); umma_commit_pred(&kv_empty[ks], leader); }
+      }
+      if (t + 1 < T) issue_scores(n_ks, n_qs, 1);
+      if (last_i) { i = 0; ++jc; } else { ++i; }
+    }
+  } else if (warp == 3) {
+    // ===================== per-(batch, head) vectors, one (batch, head) ahead =====================
+    int bc = 0;
+    for (int bh = blockIdx.x; bh < total_bh; bh += gridDim.x, ++bc) {
+      const int b = bh / H, h = bh % H, st = bc & 1;
+      float2* vec = reinterpret_cast<float2*>(sVecBase + st * kAbVecBytes);
+      float* key_ok = reinterpret_cast<float*>(sVecBase + st * kAbVecBytes + kAbMaxS * 8);
+      mbar_wait(&vec_empty[st], ((bc >> 1) & 1) ^ 1);
+      // lse and the key mask: one row per lane
+      for (int r = lane; r < S; r += 32) {
+        const float l = p.lse[((size_t)b * H + h) * S + r];
+        // fully masked row: lse = -inf -> +inf here -> P = exp2(-inf) = 0
+        vec[r].x = (l == -INFINITY) ? INFINITY : l * 1.4426950408889634f;
+        key_ok[r] = (p.mask == nullptr || p.mask[(size_t)b * S + r]) ? 1.f : 0.f;
+      }
+      // D = rowsum(dO * O) * scale: 8 lanes x 16 B cover one 128-byte row (4 rows per warp instruction -> 4 cache
+      // lines instead of 32), 16 row groups in flight
+      {
+        const int sub = lane >> 3, ch = lane & 7;
+        for (int r0 = 0; r0 < S; r0 += 64) {
+          uint4 a[16], g[16];
+#pragma unroll
+          for (int u = 0; u < 16; ++u) {
+            const size_t off = ((size_t)(b * S + r0 + u * 4 + sub) * H + h) * kAbD + ch * 8;
+            a[u] = *reinterpret_cast<const uint4*>(p.out + off);
+            g[u] = *reinterpret_cast<const uint4*>(p.dout + off);
+          }
+#pragma unroll
+          for (int u = 0; u < 16; ++u) {
+            float2 x, y;
+            float acc = 0.f;
+            x = unpack_bf16x2(a[u].x); y = unpack_bf16x2(g[u].x); acc = fmaf(x.x, y.x, acc); acc = fmaf(x.y, y.y, acc);
+            x = unpack_bf16x2(a[u].y); y = unpack_bf16x2(g[u].y); acc = fmaf(x.x, y.x, acc); acc = fmaf(x.y, y.y, acc);
+            x = unpack_bf16x2(a[u].z); y = unpack_bf16x2(g[u].z); acc = fmaf(x.x, y.x, acc); acc = fmaf(x.y, y.y, acc);
+            x = unpack_bf16x2(a[u].w); y = unpack_bf16x2(g[u].w); acc = fmaf(x.x, y.x, acc); acc = fmaf(x.y, y.y, acc);
+            acc += __shfl_xor_sync(0xffffffffu, acc, 1);
+            acc += __shfl_xor_sync(0xffffffffu, acc, 2);
+            acc += __shfl_xor_sync(0xffffffffu, acc, 4);
+            if (ch == 0) vec[r0 + u * 4 + sub].y = acc * p.scale;
+          }
+        }
+      }
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&vec_full[st]);
     }
   } else if (warp >= 4) {
-    // ===================== softmax-backward + read-out warps =====================
+    // ===================== exp / dS arithmetic + read-out: warps 4-7 = half a, warps 8-11 = half b =====================
+    const int hf = (warp - 4) >> 2;                // 0: queries [0, 64) of the block, 1: queries [64, 128)
     const int quad = warp & 3;
     const int row = quad * 32 + lane;              // TMEM lane: key row for S^T/dP^T/dK/dV, query row for dQ
     const uint32_t lane_off = (uint32_t)(quad * 32) << 16;
-    const int tid = threadIdx.x - 128;
-    uint32_t step_phase = 0, j_phase = 0;
+    const uint32_t tS = tmem_base + hf * 128 + lane_off, tP = tS + 64;
     float* dq_acc = p.dq_scratch + (size_t)blockIdx.x * S * kAbD;
-    for (int bh = blockIdx.x; bh < total_bh; bh += gridDim.x) {
+
+    // dQ partial of step t (query row `row`, columns [hf*32, hf*32+32)) accumulated over the key blocks in an fp32
+    // scratch private to this CTA. Scratch layout [query block][16-byte column chunk (16)][row (128)][4 floats]: the
+    // 32 lanes of a warp touch 512 contiguous bytes per access. The running sum needed by the NEXT drain is fetched
+    // right after the current one, a whole arithmetic phase ahead of its use.
+    float4 prev[8];
+    auto scratch_of = [&](int t) {
+      const int i = t % nblk;
+      return dq_acc + ((size_t)(i * 16 + hf * 8) * kAbBlk + row) * 4;
+    };
+    auto prefetch_dq = [&](int t) {
+      if ((t % steps_per_bh) / nblk > 0) {
+        const float* acc = scratch_of(t);
+#pragma unroll
+        for (int q = 0; q < 8; ++q) prev[q] = *reinterpret_cast<const float4*>(acc + (size_t)q * kAbBlk * 4);
+      }
+    };
+    auto drain_dq = [&](int t) {
+      const int bh = blockIdx.x + (t / steps_per_bh) * gridDim.x;
       const int b = bh / H, h = bh % H;
-      // ---- stage lse, D = rowsum(dO * O) and the key mask of this (b, h) ----
-      asm volatile("bar.sync 1, 128;");
-      for (int r = tid; r < S; r += 128) {
-        const size_t off = ((size_t)(b * S + r) * H + h) * kAbD;
-        float acc = 0.f;
+      const int j = (t % steps_per_bh) / nblk, i = t % nblk;
+      mbar_wait(dq_full, t & 1);
+      tc_fence_after();
+      uint32_t r[32];
+      tmem_ld_32x32b_x32(t_dQ + lane_off + hf * 32, r);
+      tmem_ld_wait();
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(dq_empty);        // the values are in registers: MMA 3 of the next step may start
+      float v[32];
 #pragma unroll
-        for (int c = 0; c < kAbD; c += 8) {
-          const uint4 a = *reinterpret_cast<const uint4*>(p.out + off + c);
-          const uint4 g = *reinterpret_cast<const uint4*>(p.dout + off + c);
-          float2 x, y;
-          x = unpack_bf16x2(a.x); y = unpack_bf16x2(g.x); acc = fmaf(x.x, y.x, acc); acc = fmaf(x.y, y.y, acc);
-          x = unpack_bf16x2(a.y); y = unpack_bf16x2(g.y); acc = fmaf(x.x, y.x, acc); acc = fmaf(x.y, y.y, acc);
-          x = unpack_bf16x2(a.z); y = unpack_bf16x2(g.z); acc = fmaf(x.x, y.x, acc); acc = fmaf(x.y, y.y, acc);
-          x = unpack_bf16x2(a.w); y = unpack_bf16x2(g.w); acc = fmaf(x.x, y.x, acc); acc = fmaf(x.y, y.y, acc);
+      for (int q = 0; q < 32; ++q) v[q] = __uint_as_float(r[q]);
+      if (j > 0) {
+#pragma unroll
+        for (int q = 0; q < 8; ++q) {
+          v[4 * q] += prev[q].x; v[4 * q + 1] += prev[q].y; v[4 * q + 2] += prev[q].z; v[4 * q + 3] += prev[q].w;
         }
-        sD[r] = acc;
-        const float l = p.lse[((size_t)b * H + h) * S + r];
-        sLse[r] = (l == -INFINITY) ? INFINITY : l * 1.4426950408889634f;   // fully masked row -> P = 0
-        sKeyOk[r] = (p.mask == nullptr || p.mask[(size_t)b * S + r]) ? 1.f : 0.f;
       }
-      asm volatile("bar.sync 1, 128;");
-      for (int j = 0; j < nblk; ++j) {
-        const float key_ok = sKeyOk[j * kAbBlk + row];
-        for (int i = 0; i < nblk; ++i) {
-          mbar_wait(s_full, step_phase);
-          tc_fence_after();
-          // ---- P^T and dS^T for key `row` against the 128 queries of block i ----
-          uint32_t rsA[32], rpA[32], rsB[32], rpB[32];
-          tmem_ld_32x32b_x32(t_S + lane_off, rsA);
-          tmem_ld_32x32b_x32(t_dP + lane_off, rpA);
+      if (j < nblk - 1) {
+        float* acc = scratch_of(t);
 #pragma unroll
-          for (int cidx4 = 0; cidx4 < 4; ++cidx4) {
-            const int c = cidx4 * 32;
-            tmem_ld_wait();
-            uint32_t (&rs)[32] = (cidx4 & 1) ? rsB : rsA;
-            uint32_t (&rp)[32] = (cidx4 & 1) ? rpB : rpA;
-            if (cidx4 < 3) {   // next chunk in flight while this one is processed
-              tmem_ld_32x32b_x32(t_S + lane_off + c + 32, (cidx4 & 1) ? rsA : rsB);
-              tmem_ld_32x32b_x32(t_dP + lane_off + c + 32, (cidx4 & 1) ? rpA : rpB);
-            }
-            uint32_t pk[16], dk[16];
+        for (int q = 0; q < 8; ++q)
+          *reinterpret_cast<float4*>(acc + (size_t)q * kAbBlk * 4) = make_float4(v[4 * q], v[4 * q + 1], v[4 * q + 2], v[4 * q + 3]);
+      } else {
+        __nv_bfloat16* dst = p.dqkv + (((size_t)(b * S + i * kAbBlk + row) * 3 + 0) * H + h) * kAbD + hf * 32;
 #pragma unroll
-            for (int q = 0; q < 32; q += 2) {
-              const int qi = i * kAbBlk + c + q;
-              const float p0 = key_ok * ex2f_b(fmaf(__uint_as_float(rs[q]), p.scale_log2, -sLse[qi]));
-              const float p1 = key_ok * ex2f_b(fmaf(__uint_as_float(rs[q + 1]), p.scale_log2, -sLse[qi + 1]));
-              const float d0 = p0 * (__uint_as_float(rp[q]) - sD[qi]) * p.scale;
-              const float d1 = p1 * (__uint_as_float(rp[q + 1]) - sD[qi + 1]) * p.scale;
-              pk[q >> 1] = pack_bf16x2(p0, p1);
-              dk[q >> 1] = pack_bf16x2(d0, d1);
-            }
-            // 32 queries = 64 B = four 16-byte chunks of this key's 128-byte row in query-block (c / 64)
-            const uint32_t blk = (c >> 6) * kAbTile + row * 128;
+        for (int q = 0; q < 32; q += 8)
+          *reinterpret_cast<uint4*>(dst + q) =
+              make_uint4(pack_bf16x2(v[q], v[q + 1]), pack_bf16x2(v[q + 2], v[q + 3]),
+                         pack_bf16x2(v[q + 4], v[q + 5]), pack_bf16x2(v[q + 6], v[q + 7]));
+      }
+    };
+    // dV_j (half-group a) / dK_j (half-group b) of key `row` after the last query block of key block jc
+    auto drain_dkv = [&](int jc) {
+      const int bh = blockIdx.x + (jc / nblk) * gridDim.x;
+      const int b = bh / H, h = bh % H, j = jc % nblk;
+      mbar_wait(dkv_full, jc & 1);
+      tc_fence_after();
+      const size_t tok = (size_t)(b * S + j * kAbBlk + row);
+      __nv_bfloat16* dst = p.dqkv + ((tok * 3 + (hf == 0 ? 2 : 1)) * H + h) * kAbD;
+      const uint32_t tacc = (hf == 0 ? t_dV : t_dK) + lane_off;
+      uint32_t r0[32], r1[32];
+      tmem_ld_32x32b_x32(tacc, r0);
+      tmem_ld_32x32b_x32(tacc + 32, r1);
+      tmem_ld_wait();
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(dkv_empty);
 #pragma unroll
-            for (int ch = 0; ch < 4; ++ch) {
-              const uint32_t cidx = ((c & 63) >> 3) + ch;                 // 16-byte chunk index inside the row
-              const uint32_t off = blk + ((cidx ^ (row & 7)) << 4);      // SWIZZLE_128B
-              *reinterpret_cast<uint4*>(sP + off) = make_uint4(pk[4 * ch], pk[4 * ch + 1], pk[4 * ch + 2], pk[4 * ch + 3]);
-              *reinterpret_cast<uint4*>(sdS + off) = make_uint4(dk[4 * ch], dk[4 * ch + 1], dk[4 * ch + 2], dk[4 * ch + 3]);
-            }
-          }
-          fence_proxy_async_smem();     // generic-proxy smem writes -> visible to the tensor-core (async) proxy
-          tc_fence_before();
-          __syncwarp();
-          if (lane == 0) mbar_arrive(pds_full);
-          // ---- dQ partial of query `row` of block i ----
-          {
-            float* acc = dq_acc + (size_t)(i * kAbBlk + row) * kAbD;
-            __nv_bfloat16* dst = p.dqkv + (((size_t)(b * S + i * kAbBlk + row) * 3 + 0) * H + h) * kAbD;
-            // the running fp32 sum of this row (L2-resident scratch) is fetched while MMA3-5 are still running
-            float4 prev[16];
-            if (j > 0) {
+      for (int q = 0; q < 32; q += 8)
+        *reinterpret_cast<uint4*>(dst + q) =
+            make_uint4(pack_bf16x2(__uint_as_float(r0[q]), __uint_as_float(r0[q + 1])),
+                       pack_bf16x2(__uint_as_float(r0[q + 2]), __uint_as_float(r0[q + 3])),
+                       pack_bf16x2(__uint_as_float(r0[q + 4]), __uint_as_float(r0[q + 5])),
+                       pack_bf16x2(__uint_as_float(r0[q + 6]), __uint_as_float(r0[q + 7])));
 #pragma unroll
-              for (int q = 0; q < 16; ++q) prev[q] = *reinterpret_cast<const float4*>(acc + 4 * q);
-            }
-            mbar_wait(dq_full, step_phase);
-            tc_fence_after();
-            uint32_t r0[32], r1[32];
-            tmem_ld_32x32b_x32(t_dQ + lane_off, r0);
-            tmem_ld_32x32b_x32(t_dQ + lane_off + 32, r1);
-            tmem_ld_wait();
-            float v[64];
+      for (int q = 0; q < 32; q += 8)
+        *reinterpret_cast<uint4*>(dst + 32 + q) =
+            make_uint4(pack_bf16x2(__uint_as_float(r1[q]), __uint_as_float(r1[q + 1])),
+                       pack_bf16x2(__uint_as_float(r1[q + 2]), __uint_as_float(r1[q + 3])),
+                       pack_bf16x2(__uint_as_float(r1[q + 4]), __uint_as_float(r1[q + 5])),
+                       pack_bf16x2(__uint_as_float(r1[q + 6]), __uint_as_float(r1[q + 7])));
+    };
+    // P^T and dS^T of key `row` against the 64 queries of this half
+    auto compute_half = [&](int t) {
+      const int bc = t / steps_per_bh, st = bc & 1;
+      const int j = (t % steps_per_bh) / nblk, i = t % nblk;
+      const uint32_t vec_a = smem_u32(sVecBase) + st * kAbVecBytes + (i * kAbBlk + hf * 64) * 8;
+      const uint32_t kok_a = smem_u32(sVecBase) + st * kAbVecBytes + kAbMaxS * 8 + (j * kAbBlk + row) * 4;
+      if (t % steps_per_bh == 0) mbar_wait(&vec_full[st], (bc >> 1) & 1);
+      const bool kok = lds_f1(kok_a) != 0.f;
+      const uint32_t ds_row = smem_u32(sdS) + ((t & 1) * 2 + hf) * kAbTile + row * 128;
+      mbar_wait(&s_full[hf], t & 1);
+      tc_fence_after();
 #pragma unroll
-            for (int q = 0; q < 32; ++q) { v[q] = __uint_as_float(r0[q]); v[32 + q] = __uint_as_float(r1[q]); }
-            if (j > 0) {
+      for (int c = 0; c < 2; ++c) {
+        uint32_t rs[32], rp[32];
+        tmem_ld_32x32b_x32(tS + c * 32, rs);
+        tmem_ld_32x32b_x32(tP + c * 32, rp);
+        tmem_ld_wait();
+        uint32_t pk[16], dk[16];
 #pragma unroll
-              for (int q = 0; q < 16; ++q) {
-                v[4 * q] += prev[q].x; v[4 * q + 1] += prev[q].y; v[4 * q + 2] += prev[q].z; v[4 * q + 3] += prev[q].w;
-              }
-            }
-            if (j < nblk - 1) {
-#pragma unroll
-              for (int q = 0; q < 64; q += 4)
-                *reinterpret_cast<float4*>(acc + q) = make_float4(v[q], v[q + 1], v[q + 2], v[q + 3]);
-            } else {
-#pragma unroll
-              for (int q = 0; q < 64; q += 8)
-                *reinterpret_cast<uint4*>(dst + q) =
-                    make_uint4(pack_bf16x2(v[q], v[q + 1]), pack_bf16x2(v[q + 2], v[q + 3]),
-                               pack_bf16x2(v[q + 4], v[q + 5]), pack_bf16x2(v[q + 6], v[q + 7]));
-            }
-          }
-          tc_fence_before();
-          __syncwarp();
-          if (lane == 0) mbar_arrive(dq_empty);
-          step_phase ^= 1;
+        for (int q = 0; q < 32; q += 2) {
+          const float4 v = lds_f4(vec_a + (c * 16 + (q >> 1)) * 16);   // {lse2, D*scale} of queries q, q+1 (broadcast)
+          const float p0 = ex2f_b(fmaf(__uint_as_float(rs[q]), p.scale_log2, -v.x));
+          const float p1 = ex2f_b(fmaf(__uint_as_float(rs[q + 1]), p.scale_log2, -v.z));
+          const float d0 = p0 * fmaf(__uint_as_float(rp[q]), p.scale, -v.y);
+          const float d1 = p1 * fmaf(__uint_as_float(rp[q + 1]), p.scale, -v.w);
+          pk[q >> 1] = pack_bf16x2(p0, p1);
+          dk[q >> 1] = pack_bf16x2(d0, d1);
         }
-        // ---- dK_j, dV_j of key `row` ----
-        mbar_wait(dkv_full, j_phase);
-        tc_fence_after();
-        {
-          const size_t tok = (size_t)(b * S + j * kAbBlk + row);
-          __nv_bfloat16* dk_dst = p.dqkv + ((tok * 3 + 1) * H + h) * kAbD;
-          __nv_bfloat16* dv_dst = p.dqkv + ((tok * 3 + 2) * H + h) * kAbD;
+        if (!kok) {                                          // padded key: contributes nothing
 #pragma unroll
-          for (int which = 0; which < 2; ++which) {
-            __nv_bfloat16* dst = which == 0 ? dk_dst : dv_dst;
-            const uint32_t t = (which == 0 ? t_dK : t_dV) + lane_off;
-#pragma unroll
-            for (int c = 0; c < kAbD; c += 32) {
-              uint32_t r[32];
-              tmem_ld_32x32b_x32(t + c, r);
-              tmem_ld_wait();
-#pragma unroll
-              for (int q = 0; q < 32; q += 8)
-                *reinterpret_cast<uint4*>(dst + c + q) =
-                    make_uint4(pack_bf16x2(__uint_as_float(r[q]), __uint_as_float(r[q + 1])),
-                               pack_bf16x2(__uint_as_float(r[q + 2]), __uint_as_float(r[q + 3])),
-                               pack_bf16x2(__uint_as_float(r[q + 4]), __uint_as_float(r[q + 5])),
-                               pack_bf16x2(__uint_as_float(r[q + 6]), __uint_as_float(r[q + 7])));
-            }
-          }
+          for (int q = 0; q < 16; ++q) { pk[q] = 0u; dk[q] = 0u; }
         }
-        tc_fence_before();
+        // in place: chunk c occupies columns [16c, 16c+16) of the bf16 view; the fp32 columns it overwrites
+        // ([0,16) / [16,32)) belong to chunk 0, which has been read
+        tmem_st_32x32b_x16(tS + c * 16, pk);
+        tmem_st_32x32b_x16(tP + c * 16, dk);
+        // 32 queries = 64 B = four 16-byte chunks of this key's 128-byte row (SWIZZLE_128B)
+#pragma unroll
+        for (int ch = 0; ch < 4; ++ch) {
+          const uint32_t cidx = c * 4 + ch;
+          sts_u4(ds_row + ((cidx ^ (row & 7)) << 4), dk[4 * ch], dk[4 * ch + 1], dk[4 * ch + 2], dk[4 * ch + 3]);
+        }
+      }
+      tmem_st_wait();
+      fence_proxy_async_smem();     // generic-proxy smem writes -> visible to the tensor-core (async) proxy
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&p_full[hf]);
+      if (t % steps_per_bh == steps_per_bh - 1) {            // last use of this (batch, head)'s staged vectors
         __syncwarp();
-        if (lane == 0) mbar_arrive(dkv_empty);
-        j_phase ^= 1;
+        if (lane == 0) mbar_arrive(&vec_empty[st]);
       }
+    };
+
+    if (hf == 0) {
+      for (int t = 0; t < T; ++t) {
+        compute_half(t);
+        if (t > 0) {
+          drain_dq(t - 1);
+          if (t % nblk == 0) drain_dkv(t / nblk - 1);
+        }
+        prefetch_dq(t);
+      }
+    } else {
+      for (int t = 0; t < T; ++t) {
+        if (t > 0) {
+          drain_dq(t - 1);
+          if (t % nblk == 0) drain_dkv(t / nblk - 1);
+        }
+        prefetch_dq(t);
+        compute_half(t);
+      }
+    }
+    if (T > 0) {
+      drain_dq(T - 1);
+      drain_dkv(T / nblk - 1);
     }
   }
 
@@ -362,7 +450,10 @@ extern "C" int dedloc_attention_bwd(const void* qkv, const void* out, const void
     int dev = 0;
     DEDLOC_CUDA_CHECK(cudaGetDevice(&dev));
     DEDLOC_CUDA_CHECK(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
-    DEDLOC_CUDA_CHECK(cudaFuncSetAttribute(attention_bwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kAbSmem));
+    DEDLOC_CUDA_CHECK(cudaFuncSetAttribute(attention_bwd_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, kAbSmem));
+    DEDLOC_CUDA_CHECK(cudaFuncSetAttribute(attention_bwd_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, kAbSmem));
+    DEDLOC_CUDA_CHECK(cudaFuncSetAttribute(attention_bwd_kernel<3>, cudaFuncAttributeMaxDynamicSharedMemorySize, kAbSmem));
+    DEDLOC_CUDA_CHECK(cudaFuncSetAttribute(attention_bwd_kernel<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, kAbSmem));
   }
   AttBwdParams p;
   p.B = B; p.S = S; p.H = H;
@@ -375,7 +466,12 @@ extern "C" int dedloc_attention_bwd(const void* qkv, const void* out, const void
   p.dqkv = (__nv_bfloat16*)dqkv;
   p.dq_scratch = scratch;
   const int grid = B * H < sms ? B * H : sms;
-  attention_bwd_kernel<<<grid, kAbThreads, kAbSmem, (cudaStream_t)stream>>>(tq, td, p);
+  switch (S / kAbBlk) {
+    case 1: attention_bwd_kernel<1><<<grid, kAbThreads, kAbSmem, (cudaStream_t)stream>>>(tq, td, p); break;
+    case 2: attention_bwd_kernel<2><<<grid, kAbThreads, kAbSmem, (cudaStream_t)stream>>>(tq, td, p); break;
+    case 3: attention_bwd_kernel<3><<<grid, kAbThreads, kAbSmem, (cudaStream_t)stream>>>(tq, td, p); break;
+    default: attention_bwd_kernel<4><<<grid, kAbThreads, kAbSmem, (cudaStream_t)stream>>>(tq, td, p); break;
+  }
   count_launch();
   DEDLOC_CUDA_CHECK(cudaGetLastError());
   return 0;
