@@ -67,13 +67,13 @@ attention_bwd_kernel(const __grid_constant__ CUtensorMap tmap_qkv, const __grid_
   uint64_t* qdo_empty = bars + 6;   // [2]
   uint64_t* s_full = bars + 8;      // [2] per half
   uint64_t* p_full = bars + 10;     // [2] per half
-  uint64_t* dq_full = bars + 12;
-  uint64_t* dq_empty = bars + 13;
-  uint64_t* dkv_full = bars + 14;
-  uint64_t* dkv_empty = bars + 15;
-  uint64_t* vec_full = bars + 16;   // [2]
-  uint64_t* vec_empty = bars + 18;  // [2]
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 20);
+  uint64_t* dq_full = bars + 12;    // [2] dQ partial buffers (step parity)
+  uint64_t* dq_empty = bars + 14;   // [2]
+  uint64_t* dkv_full = bars + 16;
+  uint64_t* dkv_empty = bars + 17;
+  uint64_t* vec_full = bars + 18;   // [2]
+  uint64_t* vec_empty = bars + 20;  // [2]
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 22);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   constexpr int nblk = NBLK;                      // key / query blocks of 128 (compile time: no integer divisions)
@@ -90,8 +90,8 @@ attention_bwd_kernel(const __grid_constant__ CUtensorMap tmap_qkv, const __grid_
       mbar_init(&qdo_full[i], 1); mbar_init(&qdo_empty[i], 1);
       mbar_init(&s_full[i], 1); mbar_init(&p_full[i], 4);
       mbar_init(&vec_full[i], 1); mbar_init(&vec_empty[i], 8);
+      mbar_init(&dq_full[i], 1); mbar_init(&dq_empty[i], 8);
     }
-    mbar_init(dq_full, 1); mbar_init(dq_empty, 8);
     mbar_init(dkv_full, 1); mbar_init(dkv_empty, 8);
     mbar_fence_init();
   }
@@ -100,7 +100,7 @@ attention_bwd_kernel(const __grid_constant__ CUtensorMap tmap_qkv, const __grid_
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
-  // columns: S^T_a | dP^T_a | S^T_b | dP^T_b (64 each; the bf16 P^T / dS^T reuse the first 32 of each) | dV | dK | dQ
+  // columns: S^T_a | dP^T_a | S^T_b | dP^T_b (64 each; the bf16 P^T / dS^T reuse the first 32 of each) | dV | dK | dQ x 2
   const uint32_t t_dV = tmem_base + 256, t_dK = tmem_base + 320, t_dQ = tmem_base + 384;
 
   if (warp == 0) {
@@ -127,12 +127,9 @@ attention_bwd_kernel(const __grid_constant__ CUtensorMap tmap_qkv, const __grid_
     }
   } else if (warp == 1) {
     // ===================== MMA issuer =====================
-    // The whole warp runs this code and the tcgen05 instructions are predicated on the leader lane, so that every
-    // operand stays warp-uniform; descriptors are a precomputed low word plus an immediate (the high word -- SBO =
-    // 1024, version 1, SWIZZLE_128B -- is the same for all of them). A 32-clock MMA leaves no room for more.
-    const uint32_t leader = (lane == 0) ? 1u : 0u;
-    const uint32_t tb = __shfl_sync(0xffffffffu, tmem_base, 0);   // provably warp-uniform copy
-    const uint32_t u_dV = tb + 256, u_dK = tb + 320, u_dQ = tb + 384;
+    // Issue cost matters here (a 128 x 64 x 16 MMA runs for 32 clocks): descriptors are a precomputed low word plus
+    // an immediate -- the high word (SBO = 1024, version 1, SWIZZLE_128B) is the same for all of them -- and the
+    // single-thread regions are entered through elect.sync so that the operands stay in uniform registers.
     constexpr uint32_t kHi = 0x40004040u;
     constexpr uint32_t kLboK = 1u << 16;                         // K-major: LBO = 16 B (ignored under swizzle)
     constexpr uint32_t kLboMN = (uint32_t)(kAbTile >> 4) << 16;  // MN-major: next 64-element group = next tile
@@ -140,28 +137,36 @@ attention_bwd_kernel(const __grid_constant__ CUtensorMap tmap_qkv, const __grid_
     const uint32_t id_s = make_idesc_f16(128, 64, 0, 0, 1);     // S^T_h, dP^T_h: A K-major, B K-major, N = 64
     const uint32_t id_ts = make_idesc_f16(128, 64, 0, 1, 1);    // dV, dK: A from TMEM, B MN-major (dO / Q)
     const uint32_t id_mnmn = make_idesc_f16(128, 64, 1, 1, 1);  // dQ: A MN-major (dS^T read as dS), B MN-major (K)
+    const uint32_t tb = __shfl_sync(0xffffffffu, tmem_base, 0);  // provably warp-uniform copy
+    const uint32_t u_dV = tb + 256, u_dK = tb + 320, u_dQ = tb + 384;
     const uint32_t bK = (smem_u32(sK) & 0x3FFFF) >> 4, bV = (smem_u32(sV) & 0x3FFFF) >> 4;
     const uint32_t bQ = (smem_u32(sQ) & 0x3FFFF) >> 4, bO = (smem_u32(sdO) & 0x3FFFF) >> 4;
     const uint32_t bS = (smem_u32(sdS) & 0x3FFFF) >> 4;
     // 1h: scores of half hf for the step whose operands sit in K/V stage ks and Q/dO stage qs
     auto issue_scores = [&](int ks, int qs, int hf) {
-      const uint32_t aK = (bK + ks * kStage) | kLboK, aV = (bV + ks * kStage) | kLboK;
-      const uint32_t aQ = (bQ + qs * kStage + hf * 512) | kLboK, aO = (bO + qs * kStage + hf * 512) | kLboK;
-      const uint32_t tS = tb + hf * 128, tP = tS + 64;
+      if (elect_one()) {
+        const uint32_t aK = (bK + ks * kStage) | kLboK, aV = (bV + ks * kStage) | kLboK;
+        const uint32_t aQ = (bQ + qs * kStage + hf * 512) | kLboK, aO = (bO + qs * kStage + hf * 512) | kLboK;
+        const uint32_t tS = tb + hf * 128, tP = tS + 64;
 #pragma unroll
-      for (int kk = 0; kk < 4; ++kk) umma_f16_ss_lo(tS, aK + kk * 2, aQ + kk * 2, kHi, id_s, kk > 0, leader);
+        for (int kk = 0; kk < 4; ++kk) umma_f16_ss_lohi(tS, aK + kk * 2, aQ + kk * 2, kHi, id_s, kk > 0);
 #pragma unroll
-      for (int kk = 0; kk < 4; ++kk) umma_f16_ss_lo(tP, aV + kk * 2, aO + kk * 2, kHi, id_s, kk > 0, leader);
-      umma_commit_pred(&s_full[hf], leader);
+        for (int kk = 0; kk < 4; ++kk) umma_f16_ss_lohi(tP, aV + kk * 2, aO + kk * 2, kHi, id_s, kk > 0);
+        umma_commit(&s_full[hf]);
+      }
+      __syncwarp();
     };
     // 2h: dV += P^T_h dO_h, dK += dS^T_h Q_h with A in tensor memory (16 queries = 8 columns per k-step)
     auto issue_dkv = [&](int qs, int hf, uint32_t first) {
-      const uint32_t aQ = (bQ + qs * kStage + hf * 512) | kLboMN, aO = (bO + qs * kStage + hf * 512) | kLboMN;
-      const uint32_t tS = tb + hf * 128, tP = tS + 64;
+      if (elect_one()) {
+        const uint32_t aQ = (bQ + qs * kStage + hf * 512) | kLboMN, aO = (bO + qs * kStage + hf * 512) | kLboMN;
+        const uint32_t tS = tb + hf * 128, tP = tS + 64;
 #pragma unroll
-      for (int kk = 0; kk < 4; ++kk) umma_f16_ts_lo(u_dV, tS + kk * 8, aO + kk * 128, kHi, id_ts, kk > 0 ? 1u : first, leader);
+        for (int kk = 0; kk < 4; ++kk) umma_f16_ts_lohi(u_dV, tS + kk * 8, aO + kk * 128, kHi, id_ts, kk > 0 ? 1u : first);
 #pragma unroll
-      for (int kk = 0; kk < 4; ++kk) umma_f16_ts_lo(u_dK, tP + kk * 8, aQ + kk * 128, kHi, id_ts, kk > 0 ? 1u : first, leader);
+        for (int kk = 0; kk < 4; ++kk) umma_f16_ts_lohi(u_dK, tP + kk * 8, aQ + kk * 128, kHi, id_ts, kk > 0 ? 1u : first);
+      }
+      __syncwarp();
     };
     if (T > 0) {
       mbar_wait(&kv_full[0], 0);
@@ -189,18 +194,21 @@ attention_bwd_kernel(const __grid_constant__ CUtensorMap tmap_qkv, const __grid_
       mbar_wait(&p_full[1], t & 1);
       tc_fence_after();
       issue_dkv(qs, 1, 1u);
-      umma_commit_pred(&qdo_empty[qs], leader);                   // Q_i / dO_i are not needed by MMA 3
-      if (t > 0) mbar_wait(dq_empty, (t - 1) & 1);                // dQ partial of step t-1 has been read out
+      if (elect_one()) umma_commit(&qdo_empty[qs]);               // Q_i / dO_i are not needed by MMA 3
+      __syncwarp();
+      if (t + 1 < T) issue_scores(n_ks, n_qs, 1);                 // before MMA 3: half b waits for these scores
+      if (t > 1) mbar_wait(&dq_empty[t & 1], ((t - 2) >> 1) & 1); // dQ partial of step t-2 (same buffer) was read out
       tc_fence_after();
-      {
+      if (elect_one()) {
         const uint32_t aS = (bS + (t & 1) * 2 * kStage) | kLboMN, aK = (bK + ks * kStage) | kLboMN;
+        const uint32_t tQ = u_dQ + (t & 1) * 64;
 #pragma unroll
         for (int kk = 0; kk < 8; ++kk)       // reduction over the 128 keys
-          umma_f16_ss_lo(u_dQ, aS + kk * 128, aK + kk * 128, kHi, id_mnmn, kk > 0, leader);
-        umma_commit_pred(dq_full, leader);
-        if (last_i) { umma_commit_pred(dkv_full, leader); umma_commit_pred(&kv_empty[ks], leader); }
+          umma_f16_ss_lohi(tQ, aS + kk * 128, aK + kk * 128, kHi, id_mnmn, kk > 0);
+        umma_commit(&dq_full[t & 1]);
+        if (last_i) { umma_commit(dkv_full); umma_commit(&kv_empty[ks]); }
       }
-      if (t + 1 < T) issue_scores(n_ks, n_qs, 1);
+      __syncwarp();
       if (last_i) { i = 0; ++jc; } else { ++i; }
     }
   } else if (warp == 3) {
@@ -277,14 +285,14 @@ attention_bwd_kernel(const __grid_constant__ CUtensorMap tmap_qkv, const __grid_
       const int bh = blockIdx.x + (t / steps_per_bh) * gridDim.x;
       const int b = bh / H, h = bh % H;
       const int j = (t % steps_per_bh) / nblk, i = t % nblk;
-      mbar_wait(dq_full, t & 1);
+      mbar_wait(&dq_full[t & 1], (t >> 1) & 1);
       tc_fence_after();
       uint32_t r[32];
-      tmem_ld_32x32b_x32(t_dQ + lane_off + hf * 32, r);
+      tmem_ld_32x32b_x32(t_dQ + (t & 1) * 64 + lane_off + hf * 32, r);
       tmem_ld_wait();
       tc_fence_before();
       __syncwarp();
-      if (lane == 0) mbar_arrive(dq_empty);        // the values are in registers: MMA 3 of the next step may start
+      if (lane == 0) mbar_arrive(&dq_empty[t & 1]);   // the values are in registers: this dQ buffer may be rewritten
       float v[32];
 #pragma unroll
       for (int q = 0; q < 32; ++q) v[q] = __uint_as_float(r[q]);
@@ -393,24 +401,15 @@ attention_bwd_kernel(const __grid_constant__ CUtensorMap tmap_qkv, const __grid_
       }
     };
 
-    if (hf == 0) {
-      for (int t = 0; t < T; ++t) {
-        compute_half(t);
-        if (t > 0) {
-          drain_dq(t - 1);
-          if (t % nblk == 0) drain_dkv(t / nblk - 1);
-        }
-        prefetch_dq(t);
+    // both half-groups: arithmetic of step t first, then the read-out of step t-1 (its MMA 3 finished long ago: the dQ
+    // partials are double-buffered in tensor memory, so neither side waits for the other here)
+    for (int t = 0; t < T; ++t) {
+      compute_half(t);
+      if (t > 0) {
+        drain_dq(t - 1);
+        if (t % nblk == 0) drain_dkv(t / nblk - 1);
       }
-    } else {
-      for (int t = 0; t < T; ++t) {
-        if (t > 0) {
-          drain_dq(t - 1);
-          if (t % nblk == 0) drain_dkv(t / nblk - 1);
-        }
-        prefetch_dq(t);
-        compute_half(t);
-      }
+      prefetch_dq(t);
     }
     if (T > 0) {
       drain_dq(T - 1);
