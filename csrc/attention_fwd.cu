@@ -116,6 +116,13 @@ attention_fwd_kernel(const __grid_constant__ CUtensorMap tmap_qkv, const __grid_
     // ===================== MMA issuer =====================
     const uint32_t idesc_s = make_idesc_f16(128, 128, 0, 0, 1);   // S: A = Q (K-major), B = K (K-major)
     const uint32_t idesc_o = make_idesc_f16(128, 64, 0, 1, 1);    // O: A = P (TMEM), B = V (MN-major)
+    // descriptor low words (address | LBO) + immediates; shared high word; elect.sync single-thread regions
+    constexpr uint32_t kHi = 0x40004040u;
+    const uint32_t bQ = ((smem_u32(sQ) & 0x3FFFF) >> 4) | (1u << 16);
+    const uint32_t bK = ((smem_u32(sK) & 0x3FFFF) >> 4) | (1u << 16);
+    const uint32_t bV = ((smem_u32(sV) & 0x3FFFF) >> 4) | ((uint32_t)(128 * 128 >> 4) << 16);
+    const uint32_t tb = __shfl_sync(0xffffffffu, tmem_base, 0);
+    const uint32_t tb_o = tb + 448;
     int cur_bh = -1;
     uint32_t kv_phase = 0, unit_phase = 0;
     int qs = 0;
@@ -131,16 +138,12 @@ attention_fwd_kernel(const __grid_constant__ CUtensorMap tmap_qkv, const __grid_
       mbar_wait(&q_full[qs], qphase);
       mbar_wait(o_empty, unit_phase ^ 1);      // previous unit's O has been read out of tensor memory
       tc_fence_after();
-      if (lane == 0) {
-        const uint32_t aq = smem_u32(sQ + qs * kAttQBytes);
-        const uint32_t ak = smem_u32(sK);
+      if (elect_one()) {
+        const uint32_t aq = bQ + qs * (kAttQBytes >> 4);
         for (int kb = 0; kb < S / 128; ++kb) {
 #pragma unroll
-          for (int j = 0; j < kAttD / 16; ++j) {
-            const uint64_t da = make_smem_desc_sw128(aq + j * 32, 16, 1024);
-            const uint64_t db = make_smem_desc_sw128(ak + kb * (128 * 128) + j * 32, 16, 1024);
-            umma_f16_ss(tmem_base + kb * 128, da, db, idesc_s, j > 0 ? 1u : 0u);
-          }
+          for (int j = 0; j < kAttD / 16; ++j)
+            umma_f16_ss_lohi(tb + kb * 128, aq + j * 2, bK + kb * (128 * 128 >> 4) + j * 2, kHi, idesc_s, j > 0 ? 1u : 0u);
         }
         umma_commit(&q_empty[qs]);
         umma_commit(s_full);
@@ -148,13 +151,11 @@ attention_fwd_kernel(const __grid_constant__ CUtensorMap tmap_qkv, const __grid_
       __syncwarp();
       mbar_wait(p_full, unit_phase);           // softmax warps have written P (bf16) into tensor memory
       tc_fence_after();
-      if (lane == 0) {
-        const uint32_t av = smem_u32(sV);
-        for (int k = 0; k < S / 16; ++k) {
-          // 16 keys = 2 groups of 8 rows x 128 B of V; P occupies 8 TMEM columns per 16 keys
-          const uint64_t db = make_smem_desc_sw128(av + k * 2048, 128 * 128, 1024);
-          umma_f16_ts(tmem_o, tmem_base + k * 8, db, idesc_o, k > 0 ? 1u : 0u);
-        }
+      if (elect_one()) {
+        // 16 keys = 2 groups of 8 rows x 128 B of V; P occupies 8 TMEM columns per 16 keys
+#pragma unroll 8
+        for (int k = 0; k < S / 16; ++k)
+          umma_f16_ts_lohi(tb_o, tb + k * 8, bV + k * 128, kHi, idesc_o, k > 0 ? 1u : 0u);
         umma_commit(o_full);
         if (last_of_bh) umma_commit(kv_empty);
       }

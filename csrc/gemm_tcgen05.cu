@@ -118,6 +118,14 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_con
   } else if (warp == 1) {
     // ===================== MMA issuer =====================
     const uint32_t idesc = make_idesc_f16(BM, BN, p.a_mn, p.b_mn, p.fmt);
+    // Descriptors: precomputed low word (address | LBO) + immediate per k16 step; the high word (SBO = 1024,
+    // version 1, SWIZZLE_128B) is shared. K-major: 16 elements = 32 B further along the swizzled 128 B row;
+    // MN-major: 16 k-rows = 2 groups of 8 rows x 128 B = 2048 B further. elect.sync keeps the operands uniform.
+    constexpr uint32_t kHi = 0x40004040u;
+    const uint32_t a_step = p.a_mn ? 128u : 2u, b_step = p.b_mn ? 128u : 2u;
+    const uint32_t a0 = ((smem_u32(smem) & 0x3FFFF) >> 4) | ((p.a_mn ? (uint32_t)(BK * 128) >> 4 : 1u) << 16);
+    const uint32_t b0 = (((smem_u32(smem) + S::kABytes) & 0x3FFFF) >> 4) | ((p.b_mn ? (uint32_t)(BK * 128) >> 4 : 1u) << 16);
+    const uint32_t tb = __shfl_sync(0xffffffffu, tmem_base, 0);
     int stage = 0;
     uint32_t phase = 0;
     int acc = 0;
@@ -128,23 +136,15 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_con
       const int kb1 = min(kb_total, kb0 + p.kb_per_split);
       mbar_wait(&tmem_empty[acc], acc_phase ^ 1);
       tc_fence_after();
-      const uint32_t tmem_d = tmem_base + acc * BN;
+      const uint32_t tmem_d = tb + acc * BN;
       for (int kb = kb0; kb < kb1; ++kb) {
         mbar_wait(&full_bar[stage], phase);
         tc_fence_after();
-        if (lane == 0) {
-          const uint32_t sa = smem_u32(smem + stage * S::kStageBytes);
-          const uint32_t sb = sa + S::kABytes;
+        if (elect_one()) {
+          const uint32_t sa = a0 + stage * (S::kStageBytes >> 4), sb = b0 + stage * (S::kStageBytes >> 4);
+          umma_f16_ss_lohi(tmem_d, sa, sb, kHi, idesc, kb > kb0 ? 1u : 0u);
 #pragma unroll
-          for (int j = 0; j < BK / 16; ++j) {
-            // K-major: 16 elements = 32 B further along the swizzled 128 B row.
-            // MN-major: 16 k-rows = 2 groups of 8 rows x 128 B = 2048 B further.
-            const uint64_t da = p.a_mn ? make_smem_desc_sw128(sa + j * 2048, BK * 128, 1024)
-                                       : make_smem_desc_sw128(sa + j * 32, 16, 1024);
-            const uint64_t db = p.b_mn ? make_smem_desc_sw128(sb + j * 2048, BK * 128, 1024)
-                                       : make_smem_desc_sw128(sb + j * 32, 16, 1024);
-            umma_f16_ss(tmem_d, da, db, idesc, (kb > kb0 || j > 0) ? 1u : 0u);
-          }
+          for (int j = 1; j < BK / 16; ++j) umma_f16_ss_lohi(tmem_d, sa + j * a_step, sb + j * b_step, kHi, idesc, 1u);
           umma_commit(&empty_bar[stage]);                   // smem stage reusable once these MMAs retire
           if (kb == kb1 - 1) umma_commit(&tmem_full[acc]);  // accumulator complete
         }

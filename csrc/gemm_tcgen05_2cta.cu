@@ -41,13 +41,16 @@ __device__ __forceinline__ void tma_load_2d_2sm(void* smem_dst, const void* tmap
       ::"r"(smem_u32(smem_dst)), "l"(tmap), "r"(bar), "r"(c0), "r"(c1)
       : "memory");
 }
-__device__ __forceinline__ void umma_f16_ss_2cta(uint32_t tmem_d, uint64_t desc_a, uint64_t desc_b, uint32_t idesc,
-                                                 uint32_t accumulate) {
+// descriptors as a 32-bit low word (address | LBO) plus the high word shared by all of them
+__device__ __forceinline__ void umma_f16_ss_2cta(uint32_t tmem_d, uint32_t a_lo, uint32_t b_lo, uint32_t hi,
+                                                 uint32_t idesc, uint32_t accumulate) {
   asm volatile(
-      "{\n\t.reg .pred p;\n\t"
-      "setp.ne.b32 p, %4, 0;\n\t"
-      "tcgen05.mma.cta_group::2.kind::f16 [%0], %1, %2, %3, p;\n\t}" ::"r"(tmem_d),
-      "l"(desc_a), "l"(desc_b), "r"(idesc), "r"(accumulate)
+      "{\n\t.reg .pred p;\n\t.reg .b64 da, db;\n\t"
+      "setp.ne.b32 p, %5, 0;\n\t"
+      "mov.b64 da, {%1, %3};\n\t"
+      "mov.b64 db, {%2, %3};\n\t"
+      "tcgen05.mma.cta_group::2.kind::f16 [%0], da, db, %4, p;\n\t}" ::"r"(tmem_d),
+      "r"(a_lo), "r"(b_lo), "r"(hi), "r"(idesc), "r"(accumulate)
       : "memory");
 }
 // arrive (once MMAs retire) on the barrier at this smem offset in BOTH CTAs of the pair
@@ -154,6 +157,14 @@ gemm_tcgen05_2cta_kernel(const __grid_constant__ CUtensorMap tmap_a, const __gri
     // ===================== MMA issuer (leader CTA only) =====================
     if (leader) {
       const uint32_t idesc = make_idesc_f16(2 * k2BM, k2BN, p.a_mn, p.b_mn, p.fmt);
+      // Issue cost: descriptors are (precomputed low word + immediate) and the single-thread region is entered
+      // through elect.sync, which keeps every MMA operand in uniform registers (a dozen instructions fewer per MMA
+      // than a lane == 0 branch).
+      constexpr uint32_t kHi = 0x40004040u;                 // SBO = 1024, version 1, SWIZZLE_128B
+      const uint32_t a_step = p.a_mn ? 128u : 2u, b_step = p.b_mn ? 128u : 2u;     // one k16 step, in 16-byte units
+      const uint32_t a0 = ((smem_u32(smem) & 0x3FFFF) >> 4) | ((p.a_mn ? (uint32_t)(k2BK * 128) >> 4 : 1u) << 16);
+      const uint32_t b0 = (((smem_u32(smem) + k2ABytes) & 0x3FFFF) >> 4) | ((p.b_mn ? (uint32_t)(k2BK * 128) >> 4 : 1u) << 16);
+      const uint32_t tb = __shfl_sync(0xffffffffu, tmem_base, 0);
       int stage = 0;
       uint32_t phase = 0;
       int acc = 0;
@@ -164,21 +175,16 @@ gemm_tcgen05_2cta_kernel(const __grid_constant__ CUtensorMap tmap_a, const __gri
         const int kb1 = min(kb_total, kb0 + p.kb_per_split);
         mbar_wait(&tmem_empty[acc], acc_phase ^ 1);
         tc_fence_after();
-        const uint32_t tmem_d = tmem_base + acc * k2BN;
+        const uint32_t tmem_d = tb + acc * k2BN;
         for (int kb = kb0; kb < kb1; ++kb) {
           mbar_wait(&full_bar[stage], phase);
           tc_fence_after();
-          if (lane == 0) {
-            const uint32_t sa = smem_u32(smem + stage * k2StageBytes);
-            const uint32_t sb = sa + k2ABytes;
+          if (elect_one()) {
+            const uint32_t sa = a0 + stage * (k2StageBytes >> 4), sb = b0 + stage * (k2StageBytes >> 4);
+            umma_f16_ss_2cta(tmem_d, sa, sb, kHi, idesc, kb > kb0 ? 1u : 0u);
 #pragma unroll
-            for (int j = 0; j < k2BK / 16; ++j) {
-              const uint64_t da = p.a_mn ? make_smem_desc_sw128(sa + j * 2048, k2BK * 128, 1024)
-                                         : make_smem_desc_sw128(sa + j * 32, 16, 1024);
-              const uint64_t db = p.b_mn ? make_smem_desc_sw128(sb + j * 2048, k2BK * 128, 1024)
-                                         : make_smem_desc_sw128(sb + j * 32, 16, 1024);
-              umma_f16_ss_2cta(tmem_d, da, db, idesc, (kb > kb0 || j > 0) ? 1u : 0u);
-            }
+            for (int j = 1; j < k2BK / 16; ++j)
+              umma_f16_ss_2cta(tmem_d, sa + j * a_step, sb + j * b_step, kHi, idesc, 1u);
             umma_commit_2cta_mc(&empty_bar[stage]);                    // frees this stage in BOTH CTAs
             if (kb == kb1 - 1) umma_commit_2cta_mc(&tmem_full[acc]);   // accumulators ready in BOTH CTAs
           }
