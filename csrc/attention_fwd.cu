@@ -2,33 +2,39 @@
 // reading Q, K, V straight from the PACKED output of the fused QKV GEMM ([B, S, 3, H, 64] bf16) and writing the
 // context in [B, S, H*64] -- no head transposes, no unpack copies. Non-causal, optional key-padding mask.
 //
-// Because S <= 512 the whole score row fits in tensor memory (128 lanes x 512 fp32 columns), so softmax is exact
-// two-pass (no online rescaling):
-//   warp 0   TMA: K and V of one (batch, head) [S x 64] once, Q blocks [128 x 64] double-buffered
-//   warp 1   tcgen05.mma: S = Q K^T (N = 128 per instruction, 4 k-steps), later O = P V with P read FROM TENSOR
-//            MEMORY as the A operand (32 k-steps over the keys, B = V in MN-major form)
-//   warp 2   TMEM allocator (all 512 columns)
-//   warps 4-7  one thread per query row: row max, exp2, row sum, P packed to bf16 and stored back IN PLACE over the
-//            scores (tcgen05.st), then the epilogue O / sum -> bf16 -> global, log-sum-exp saved for backward
-// A CTA walks a contiguous range of (batch, head, q-block) units so K/V are fetched once per (batch, head).
+// The exponentials (MUFU, 16 / clock / SM) are the bound at head_dim 64, so the design keeps the MUFU pipe fed:
+// two query blocks (128 rows each) of one (batch, head) are in flight, one per softmax warpgroup, and the tensor
+// core serves whichever of them is ready. Softmax is exact two-pass WITHOUT keeping the 512-column score row: pass 1
+// computes the score blocks only for the row maximum, pass 2 recomputes each block (the tensor core has the
+// cycles to spare), exponentiates against the final maximum and feeds P straight back from tensor memory:
+//   warp 0      TMA: K / V blocks of 128 keys into fixed per-(batch, head) slots (a slot is refilled for the next
+//               (batch, head) as soon as its last MMA retired), Q blocks double-buffered per warpgroup
+//   warp 1      tcgen05.mma issuer, polling the barriers of both warpgroups:
+//                 pass 1  S_w = Q K_kb^T                      (128 x 128, fp32 in 128 TMEM columns)
+//                 pass 2  S_w = Q K_kb^T again; O_w += P_w V_kb with P (bf16, written in place over S_w by the
+//                         softmax warps) as the TMEM A operand and V as an MN-major B operand
+//   warp 2      TMEM allocator        warp 3  key-padding bias of the (batch) row, one (batch, head) ahead
+//   warps 4-7 / 8-11  one thread per query row: running max over the blocks (pass 1), exp2 / row sum / bf16 pack
+//               (pass 2), then O / sum -> bf16 -> swizzled shared memory (the Q buffer of the finished block) ->
+//               one TMA store per block; log-sum-exp saved for the backward kernel
 #include "gemm_common.cuh"
 
 namespace dedloc {
 
-constexpr int kAttThreads = 256;
+constexpr int kAttThreads = 384;
 constexpr int kAttD = 64;
 constexpr int kAttBQ = 128;
 constexpr int kAttMaxS = 512;
-constexpr int kAttKBytes = kAttMaxS * 128;          // 64 KB: S rows x 128 B
-constexpr int kAttQBytes = kAttBQ * 128;            // 16 KB
-constexpr int kAttSmem = 2 * kAttKBytes + 2 * kAttQBytes + kAttMaxS * 4 + 256 + 1024;
+constexpr int kAttTile = 128 * 128;                 // 16 KB: 128 rows x 128 B
+constexpr int kAttBiasBytes = kAttMaxS * 4;
+// smem: K x 4 slots, V x 4 slots, Q x 2 warpgroups x 2 stages (12 tiles) + bias x 2 + barriers
+constexpr int kAttSmem = 12 * kAttTile + 2 * kAttBiasBytes + 512 + 1024;
 
 struct AttFwdParams {
   int B, S, H;
   float scale_log2;          // softmax scale * log2(e)
   float scale;               // softmax scale
   const unsigned char* mask; // [B, S] 1 = attend, 0 = padding; may be null
-  __nv_bfloat16* out;        // [B, S, H*64]
   float* lse;                // [B, H, S]
 };
 
@@ -38,42 +44,49 @@ __device__ __forceinline__ float ex2f(float x) {
   return y;
 }
 
+template <bool HAS_MASK>
 __global__ void __launch_bounds__(kAttThreads, 1)
-attention_fwd_kernel(const __grid_constant__ CUtensorMap tmap_qkv, const __grid_constant__ AttFwdParams p) {
+attention_fwd_kernel(const __grid_constant__ CUtensorMap tmap_qkv, const __grid_constant__ CUtensorMap tmap_out,
+                     const __grid_constant__ AttFwdParams p) {
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
-  uint8_t* sK = smem;
-  uint8_t* sV = smem + kAttKBytes;
-  uint8_t* sQ = smem + 2 * kAttKBytes;                       // 2 buffers
-  float* sBias = reinterpret_cast<float*>(smem + 2 * kAttKBytes + 2 * kAttQBytes);   // [S] 0 or -inf
-  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + 2 * kAttKBytes + 2 * kAttQBytes + kAttMaxS * 4);
-  uint64_t* kv_full = bars + 0;
-  uint64_t* kv_empty = bars + 1;
-  uint64_t* q_full = bars + 2;     // [2]
-  uint64_t* q_empty = bars + 4;    // [2]
-  uint64_t* s_full = bars + 6;
-  uint64_t* p_full = bars + 7;
-  uint64_t* o_full = bars + 8;
-  uint64_t* o_empty = bars + 9;
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 10);
+  uint8_t* sK = smem;                               // 4 slots (key blocks)
+  uint8_t* sV = smem + 4 * kAttTile;                // 4 slots
+  uint8_t* sQ = smem + 8 * kAttTile;                // [warpgroup][stage]
+  uint8_t* sBias = smem + 12 * kAttTile;            // [2][S] 0 or -inf per key
+  uint64_t* bars = reinterpret_cast<uint64_t*>(sBias + 2 * kAttBiasBytes);
+  uint64_t* k_full = bars + 0;      // [4]
+  uint64_t* k_free = bars + 4;      // [4]
+  uint64_t* v_full = bars + 8;      // [4]
+  uint64_t* v_free = bars + 12;     // [4]
+  uint64_t* q_full = bars + 16;     // [wg*2 + stage]
+  uint64_t* q_free = bars + 20;     // [wg*2 + stage]
+  uint64_t* s_full = bars + 24;     // [wg]
+  uint64_t* s_free = bars + 26;     // [wg]
+  uint64_t* p_full = bars + 28;     // [wg]
+  uint64_t* o_full = bars + 30;     // [wg]
+  uint64_t* o_free = bars + 32;     // [wg]
+  uint64_t* bias_full = bars + 34;  // [2]
+  uint64_t* bias_free = bars + 36;  // [2]
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 38);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int S = p.S, H = p.H;
-  const int qblocks = S / kAttBQ;
-  const int total_units = p.B * H * qblocks;
-  const int per_cta = (total_units + gridDim.x - 1) / gridDim.x;
-  const int u0 = blockIdx.x * per_cta;
-  const int u1 = min(total_units, u0 + per_cta);
+  const int nkb = S / 128;                 // key blocks == query blocks of a (batch, head)
+  const int total_bh = p.B * H;
 
-  if (warp == 0 && lane == 0) tma_prefetch_desc(&tmap_qkv);
+  if (warp == 0 && lane == 0) { tma_prefetch_desc(&tmap_qkv); tma_prefetch_desc(&tmap_out); }
   if (warp == 1 && lane == 0) {
-    mbar_init(kv_full, 1);
-    mbar_init(kv_empty, 1);
-    for (int i = 0; i < 2; ++i) { mbar_init(&q_full[i], 1); mbar_init(&q_empty[i], 1); }
-    mbar_init(s_full, 1);
-    mbar_init(p_full, 4);
-    mbar_init(o_full, 1);
-    mbar_init(o_empty, 4);
+    for (int i = 0; i < 4; ++i) {
+      mbar_init(&k_full[i], 1); mbar_init(&k_free[i], 1);
+      mbar_init(&v_full[i], 1); mbar_init(&v_free[i], 1);
+      mbar_init(&q_full[i], 1); mbar_init(&q_free[i], 1);
+    }
+    for (int i = 0; i < 2; ++i) {
+      mbar_init(&s_full[i], 1); mbar_init(&s_free[i], 4); mbar_init(&p_full[i], 4);
+      mbar_init(&o_full[i], 1); mbar_init(&o_free[i], 4);
+      mbar_init(&bias_full[i], 1); mbar_init(&bias_free[i], 8);
+    }
     mbar_fence_init();
   }
   if (warp == 2) {
@@ -84,195 +97,276 @@ attention_fwd_kernel(const __grid_constant__ CUtensorMap tmap_qkv, const __grid_
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
-  const uint32_t tmem_o = tmem_base + 448;   // O accumulator: the last 64 columns (free once P has replaced S)
+  // columns: warpgroup w owns [192 w, 192 w + 128) for S / P and [192 w + 128, 192 w + 192) for O
 
   if (warp == 0) {
     // ===================== TMA producer =====================
     if (lane == 0) {
-      int cur_bh = -1;
-      uint32_t kv_phase = 0;
-      int qs = 0;
-      uint32_t qphase = 0;
-      for (int u = u0; u < u1; ++u) {
-        const int bh = u / qblocks, qb = u % qblocks;
+      int bc = 0, uq0 = 0, uq1 = 0;      // (batch, head) counter, per-warpgroup block counters
+      for (int bh = blockIdx.x; bh < total_bh; bh += gridDim.x, ++bc) {
         const int b = bh / H, h = bh % H;
-        if (bh != cur_bh) {
-          mbar_wait(kv_empty, kv_phase ^ 1);
-          mbar_expect_tx(kv_full, 2 * S * 128);
-          for (int r = 0; r < S; r += 128) {
-            tma_load_2d(sK + r * 128, &tmap_qkv, kv_full, (1 * H + h) * kAttD, b * S + r);
-            tma_load_2d(sV + r * 128, &tmap_qkv, kv_full, (2 * H + h) * kAttD, b * S + r);
-          }
-          kv_phase ^= 1;
-          cur_bh = bh;
+        auto load_q = [&](int qb) {
+          const int w = qb & 1;
+          int& uq = (w == 0) ? uq0 : uq1;
+          const int slot = w * 2 + (uq & 1);
+          mbar_wait(&q_free[slot], ((uq >> 1) & 1) ^ 1);
+          mbar_expect_tx(&q_full[slot], kAttTile);
+          tma_load_2d(sQ + slot * kAttTile, &tmap_qkv, &q_full[slot], (0 * H + h) * kAttD, b * S + qb * kAttBQ);
+          ++uq;
+        };
+        // order = the order in which the consumers free / need things: first-round Q, K blocks, V blocks, later Q
+        load_q(0);
+        if (nkb > 1) load_q(1);
+        for (int kb = 0; kb < nkb; ++kb) {
+          mbar_wait(&k_free[kb], (bc & 1) ^ 1);
+          mbar_expect_tx(&k_full[kb], kAttTile);
+          tma_load_2d(sK + kb * kAttTile, &tmap_qkv, &k_full[kb], (1 * H + h) * kAttD, b * S + kb * 128);
         }
-        mbar_wait(&q_empty[qs], qphase ^ 1);
-        mbar_expect_tx(&q_full[qs], kAttQBytes);
-        tma_load_2d(sQ + qs * kAttQBytes, &tmap_qkv, &q_full[qs], (0 * H + h) * kAttD, b * S + qb * kAttBQ);
-        if (++qs == 2) { qs = 0; qphase ^= 1; }
+        for (int kb = 0; kb < nkb; ++kb) {
+          mbar_wait(&v_free[kb], (bc & 1) ^ 1);
+          mbar_expect_tx(&v_full[kb], kAttTile);
+          tma_load_2d(sV + kb * kAttTile, &tmap_qkv, &v_full[kb], (2 * H + h) * kAttD, b * S + kb * 128);
+        }
+        for (int qb = 2; qb < nkb; ++qb) load_q(qb);
       }
     }
   } else if (warp == 1) {
-    // ===================== MMA issuer =====================
+    // ===================== MMA issuer: serves whichever warpgroup is ready =====================
     const uint32_t idesc_s = make_idesc_f16(128, 128, 0, 0, 1);   // S: A = Q (K-major), B = K (K-major)
     const uint32_t idesc_o = make_idesc_f16(128, 64, 0, 1, 1);    // O: A = P (TMEM), B = V (MN-major)
-    // descriptor low words (address | LBO) + immediates; shared high word; elect.sync single-thread regions
-    constexpr uint32_t kHi = 0x40004040u;
+    constexpr uint32_t kHi = 0x40004040u;                         // SBO = 1024, version 1, SWIZZLE_128B
+    constexpr uint32_t kT = kAttTile >> 4;                        // one tile in descriptor address units
     const uint32_t bQ = ((smem_u32(sQ) & 0x3FFFF) >> 4) | (1u << 16);
     const uint32_t bK = ((smem_u32(sK) & 0x3FFFF) >> 4) | (1u << 16);
-    const uint32_t bV = ((smem_u32(sV) & 0x3FFFF) >> 4) | ((uint32_t)(128 * 128 >> 4) << 16);
+    const uint32_t bV = ((smem_u32(sV) & 0x3FFFF) >> 4) | (kT << 16);
     const uint32_t tb = __shfl_sync(0xffffffffu, tmem_base, 0);
-    const uint32_t tb_o = tb + 448;
-    int cur_bh = -1;
-    uint32_t kv_phase = 0, unit_phase = 0;
-    int qs = 0;
-    uint32_t qphase = 0;
-    for (int u = u0; u < u1; ++u) {
-      const int bh = u / qblocks;
-      if (bh != cur_bh) {
-        mbar_wait(kv_full, kv_phase);
-        kv_phase ^= 1;
-        cur_bh = bh;
-      }
-      const bool last_of_bh = (u + 1 == u1) || ((u + 1) / qblocks != bh);
-      mbar_wait(&q_full[qs], qphase);
-      mbar_wait(o_empty, unit_phase ^ 1);      // previous unit's O has been read out of tensor memory
-      tc_fence_after();
+    const int my_bh = (total_bh - (int)blockIdx.x + (int)gridDim.x - 1) / (int)gridDim.x;
+    // per-warpgroup progress: (batch, head) index, block index inside it, event index inside the block, counters
+    int bi[2] = {0, 0}, qb[2] = {0, 1}, ev[2] = {0, 0}, uq[2] = {0, 0}, n_sfree[2] = {0, 0}, n_pfull[2] = {0, 0};
+    bool done[2] = {my_bh == 0, my_bh == 0 || nkb < 2};
+    uint32_t cnt_k = 0, cnt_v = 0;       // uses of each K / V slot inside the current (batch, head), 8 bits per slot
+    auto issue_s = [&](int w, int kb) {  // S_w = Q K_kb^T
       if (elect_one()) {
-        const uint32_t aq = bQ + qs * (kAttQBytes >> 4);
-        for (int kb = 0; kb < S / 128; ++kb) {
+        const uint32_t aq = bQ + (w * 2 + (uq[w] & 1)) * kT, ak = bK + kb * kT, td = tb + w * 192;
 #pragma unroll
-          for (int j = 0; j < kAttD / 16; ++j)
-            umma_f16_ss_lohi(tb + kb * 128, aq + j * 2, bK + kb * (128 * 128 >> 4) + j * 2, kHi, idesc_s, j > 0 ? 1u : 0u);
+        for (int j = 0; j < kAttD / 16; ++j) umma_f16_ss_lohi(td, aq + j * 2, ak + j * 2, kHi, idesc_s, j > 0 ? 1u : 0u);
+        umma_commit(&s_full[w]);
+      }
+      __syncwarp();
+    };
+    while (!(done[0] && done[1])) {
+      bool progressed = false;
+#pragma unroll
+      for (int w = 0; w < 2; ++w) {
+        if (done[w]) continue;
+        const int e = ev[w];
+        if (e <= nkb) {
+          // pass 1 block e, or (e == nkb) the first block of pass 2
+          const int kb = (e == nkb) ? 0 : e;
+          bool ready = mbar_test_wait(&k_full[kb], bi[w] & 1);
+          if (ready && e == 0) ready = mbar_test_wait(&q_full[w * 2 + (uq[w] & 1)], (uq[w] >> 1) & 1);
+          if (ready && e > 0) ready = mbar_test_wait(&s_free[w], (n_sfree[w] & 1));
+          if (!ready) continue;
+          if (e > 0) ++n_sfree[w];
+          tc_fence_after();
+          issue_s(w, kb);
+          if (e == nkb) {                 // pass-2 use of K slot 0
+            cnt_k += 1u;
+            if ((cnt_k & 0xFF) == (uint32_t)nkb) { cnt_k &= ~0xFFu; if (elect_one()) umma_commit(&k_free[0]); __syncwarp(); }
+          }
+          ev[w] = e + 1;
+        } else {
+          // pass 2: O_w += P_w V_kb, then the next score block
+          const int kb = e - nkb - 1;
+          bool ready = mbar_test_wait(&p_full[w], n_pfull[w] & 1);
+          if (ready) ready = mbar_test_wait(&v_full[kb], bi[w] & 1);
+          if (ready && kb == 0 && uq[w] > 0) ready = mbar_test_wait(&o_free[w], (uq[w] - 1) & 1);
+          if (!ready) continue;
+          ++n_pfull[w];
+          tc_fence_after();
+          if (elect_one()) {
+            const uint32_t av = bV + kb * kT, ts = tb + w * 192, to = ts + 128;
+            // 16 keys per k-step: 8 TMEM columns of bf16 P, 2 groups of 8 rows x 128 B of V
+#pragma unroll
+            for (int k = 0; k < 8; ++k) umma_f16_ts_lohi(to, ts + k * 8, av + k * 128, kHi, idesc_o, (kb > 0 || k > 0) ? 1u : 0u);
+            if (kb == nkb - 1) umma_commit(&o_full[w]);
+          }
+          __syncwarp();
+          cnt_v += 1u << (8 * kb);
+          if (((cnt_v >> (8 * kb)) & 0xFF) == (uint32_t)nkb) {
+            cnt_v &= ~(0xFFu << (8 * kb));
+            if (elect_one()) umma_commit(&v_free[kb]);
+            __syncwarp();
+          }
+          if (kb < nkb - 1) {
+            issue_s(w, kb + 1);
+            cnt_k += 1u << (8 * (kb + 1));
+            if (((cnt_k >> (8 * (kb + 1))) & 0xFF) == (uint32_t)nkb) {
+              cnt_k &= ~(0xFFu << (8 * (kb + 1)));
+              if (elect_one()) umma_commit(&k_free[kb + 1]);
+              __syncwarp();
+            }
+            ev[w] = e + 1;
+          } else {
+            // block finished: next block of this warpgroup
+            ev[w] = 0;
+            ++uq[w];
+            qb[w] += 2;
+            if (qb[w] >= nkb) {
+              qb[w] = w;
+              if (++bi[w] >= my_bh) done[w] = true;
+            }
+          }
         }
-        umma_commit(&q_empty[qs]);
-        umma_commit(s_full);
+        progressed = true;
       }
-      __syncwarp();
-      mbar_wait(p_full, unit_phase);           // softmax warps have written P (bf16) into tensor memory
-      tc_fence_after();
-      if (elect_one()) {
-        // 16 keys = 2 groups of 8 rows x 128 B of V; P occupies 8 TMEM columns per 16 keys
-#pragma unroll 8
-        for (int k = 0; k < S / 16; ++k)
-          umma_f16_ts_lohi(tb_o, tb + k * 8, bV + k * 128, kHi, idesc_o, k > 0 ? 1u : 0u);
-        umma_commit(o_full);
-        if (last_of_bh) umma_commit(kv_empty);
+      if (!progressed) __nanosleep(20);
+    }
+  } else if (warp == 3) {
+    // ===================== key-padding bias of the batch row, one (batch, head) ahead =====================
+    if (HAS_MASK) {
+      int bc = 0;
+      for (int bh = blockIdx.x; bh < total_bh; bh += gridDim.x, ++bc) {
+        const int b = bh / H, st = bc & 1;
+        mbar_wait(&bias_free[st], ((bc >> 1) & 1) ^ 1);
+        float* bias = reinterpret_cast<float*>(sBias + st * kAttBiasBytes);
+        for (int k = lane; k < S; k += 32) bias[k] = p.mask[(size_t)b * S + k] ? 0.f : -INFINITY;
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&bias_full[st]);
       }
-      __syncwarp();
-      unit_phase ^= 1;
-      if (++qs == 2) { qs = 0; qphase ^= 1; }
     }
   } else if (warp >= 4) {
-    // ===================== softmax + epilogue: one thread per query row =====================
+    // ===================== softmax + epilogue: one thread per query row, one warpgroup per query block =====================
+    const int w = (warp - 4) >> 2;
     const int quad = warp & 3;
     const int row = quad * 32 + lane;
-    const uint32_t t_row = tmem_base + ((uint32_t)(quad * 32) << 16);
-    uint32_t unit_phase = 0;
-    int cur_b = -1;
-    const bool has_mask = p.mask != nullptr;
-    for (int u = u0; u < u1; ++u) {
-      const int bh = u / qblocks, qb = u % qblocks;
+    const uint32_t t_s = tmem_base + w * 192 + ((uint32_t)(quad * 32) << 16);
+    const uint32_t t_o = t_s + 128;
+    const bool store_leader = (quad == 0 && lane == 0);
+    int n_sfull = 0, uq = 0, bc = 0, pending_slot = -1;
+    for (int bh = blockIdx.x; bh < total_bh; bh += gridDim.x, ++bc) {
       const int b = bh / H, h = bh % H;
-      if (has_mask && b != cur_b) {
-        // the 128 softmax threads refresh the additive key bias of this batch row
-        asm volatile("bar.sync 1, 128;");
-        for (int k = threadIdx.x - 128; k < S; k += 128) sBias[k] = p.mask[(size_t)b * S + k] ? 0.f : -INFINITY;
-        asm volatile("bar.sync 1, 128;");
-        cur_b = b;
-      }
-      mbar_wait(s_full, unit_phase);
-      tc_fence_after();
-      // Both passes are software-pipelined: the tcgen05.ld of chunk c+1 is in flight while chunk c is processed
-      // (tcgen05.wait::ld waits for every outstanding load, so the next load is issued right after the wait).
-      // pass 1: row maximum
-      float m = -INFINITY;
-      {
-        uint32_t ra[32], rb[32];
-        tmem_ld_32x32b_x32(t_row, ra);
-        for (int c = 0; c < S; c += 64) {
-          tmem_ld_wait();
-          tmem_ld_32x32b_x32(t_row + c + 32, rb);
-#pragma unroll
-          for (int i = 0; i < 32; ++i) {
-            float v = __uint_as_float(ra[i]);
-            if (has_mask) v += sBias[c + i];
-            m = fmaxf(m, v);
-          }
-          tmem_ld_wait();
-          if (c + 64 < S) tmem_ld_32x32b_x32(t_row + c + 64, ra);
-#pragma unroll
-          for (int i = 0; i < 32; ++i) {
-            float v = __uint_as_float(rb[i]);
-            if (has_mask) v += sBias[c + 32 + i];
-            m = fmaxf(m, v);
-          }
+      const uint32_t bias_a = smem_u32(sBias) + (bc & 1) * kAttBiasBytes;
+      if (HAS_MASK) mbar_wait(&bias_full[bc & 1], (bc >> 1) & 1);
+      for (int qb = w; qb < nkb; qb += 2, ++uq) {
+        const int slot = w * 2 + (uq & 1);
+        // the TMA store of the previous block read its staging buffer (= that block's Q stage): hand it back
+        if (store_leader && pending_slot >= 0) {
+          tma_store_wait_read<0>();
+          mbar_arrive(&q_free[pending_slot]);
+          pending_slot = -1;
         }
-      }
-      const float m_scaled = (m == -INFINITY) ? 0.f : m * p.scale_log2;
-      // pass 2: p = exp2(s * scale_log2 - m_scaled); packed bf16 pairs overwrite the scores in place
-      float sum = 0.f;
-      {
-        uint32_t ra[32], rb[32];
-        tmem_ld_32x32b_x32(t_row, ra);
-        for (int c = 0; c < S; c += 64) {
+        // ---------------- pass 1: row maximum over all key blocks ----------------
+        float m = -INFINITY;
+        for (int kb = 0; kb < nkb; ++kb) {
+          mbar_wait(&s_full[w], n_sfull & 1);
+          ++n_sfull;
+          tc_fence_after();
+          uint32_t ra[32], rb[32];
+          tmem_ld_32x32b_x32(t_s, ra);
+          tmem_ld_32x32b_x32(t_s + 32, rb);
 #pragma unroll
-          for (int half = 0; half < 2; ++half) {
+          for (int c = 0; c < 4; ++c) {
+            tmem_ld_wait();       // waits for every outstanding load: chunk c and the prefetched chunk c+1
+            uint32_t (&cur)[32] = (c & 1) ? rb : ra;
+#pragma unroll
+            for (int i = 0; i < 32; i += 4) {
+              float v0 = __uint_as_float(cur[i]), v1 = __uint_as_float(cur[i + 1]);
+              float v2 = __uint_as_float(cur[i + 2]), v3 = __uint_as_float(cur[i + 3]);
+              if (HAS_MASK) {
+                const float4 bb = lds_f4(bias_a + (kb * 128 + c * 32 + i) * 4);
+                v0 += bb.x; v1 += bb.y; v2 += bb.z; v3 += bb.w;
+              }
+              m = fmaxf(fmaxf(m, v0), fmaxf(v1, fmaxf(v2, v3)));
+            }
+            if (c + 2 < 4) tmem_ld_32x32b_x32(t_s + (c + 2) * 32, cur);   // refill the buffer just consumed
+          }
+          tc_fence_before();
+          __syncwarp();
+          if (lane == 0) mbar_arrive(&s_free[w]);
+        }
+        const float m_scaled = (m == -INFINITY) ? 0.f : m * p.scale_log2;
+        // ---------------- pass 2: p = exp2(s * scale_log2 - m_scaled), bf16 pairs in place over the scores ----------------
+        float sum = 0.f;
+        for (int kb = 0; kb < nkb; ++kb) {
+          mbar_wait(&s_full[w], n_sfull & 1);
+          ++n_sfull;
+          tc_fence_after();
+          uint32_t ra[32], rb[32];
+          tmem_ld_32x32b_x32(t_s, ra);
+          tmem_ld_32x32b_x32(t_s + 32, rb);
+#pragma unroll
+          for (int c = 0; c < 4; ++c) {
             tmem_ld_wait();
-            uint32_t (&cur)[32] = half == 0 ? ra : rb;
-            const int cc = c + half * 32;
-            if (half == 0) tmem_ld_32x32b_x32(t_row + c + 32, rb);
-            else if (c + 64 < S) tmem_ld_32x32b_x32(t_row + c + 64, ra);
+            uint32_t (&cur)[32] = (c & 1) ? rb : ra;
             uint32_t pk[16];
 #pragma unroll
-            for (int i = 0; i < 32; i += 2) {
+            for (int i = 0; i < 32; i += 4) {
               float v0 = __uint_as_float(cur[i]), v1 = __uint_as_float(cur[i + 1]);
-              if (has_mask) { v0 += sBias[cc + i]; v1 += sBias[cc + i + 1]; }
+              float v2 = __uint_as_float(cur[i + 2]), v3 = __uint_as_float(cur[i + 3]);
+              if (HAS_MASK) {
+                const float4 bb = lds_f4(bias_a + (kb * 128 + c * 32 + i) * 4);
+                v0 += bb.x; v1 += bb.y; v2 += bb.z; v3 += bb.w;
+              }
               const float e0 = ex2f(fmaf(v0, p.scale_log2, -m_scaled));
               const float e1 = ex2f(fmaf(v1, p.scale_log2, -m_scaled));
-              // the row sum uses the bf16-rounded probabilities that the P V product will actually see
-              const uint32_t packed = pack_bf16x2(e0, e1);
-              const float2 back = unpack_bf16x2(packed);
-              sum += back.x + back.y;
-              pk[i >> 1] = packed;
+              const float e2 = ex2f(fmaf(v2, p.scale_log2, -m_scaled));
+              const float e3 = ex2f(fmaf(v3, p.scale_log2, -m_scaled));
+              sum += (e0 + e1) + (e2 + e3);
+              pk[i >> 1] = pack_bf16x2(e0, e1);
+              pk[(i >> 1) + 1] = pack_bf16x2(e2, e3);
             }
-            // in-place: columns [cc/2, cc/2 + 16) were read two or more chunks ago; the load in flight reads
-            // columns >= cc + 32
-            tmem_st_32x32b_x16(t_row + (cc >> 1), pk);
+            // in place: bf16 columns [16c, 16c+16) overlay fp32 columns of chunk c/2, which has been read; the
+            // loads in flight read columns >= 32 (c + 1)
+            tmem_st_32x32b_x16(t_s + c * 16, pk);
+            if (c + 2 < 4) tmem_ld_32x32b_x32(t_s + (c + 2) * 32, cur);
           }
+          tmem_st_wait();
+          tc_fence_before();
+          __syncwarp();
+          if (lane == 0) mbar_arrive(&p_full[w]);
         }
-      }
-      tmem_st_wait();
-      tc_fence_before();
-      __syncwarp();
-      if (lane == 0) mbar_arrive(p_full);
-      // epilogue
-      mbar_wait(o_full, unit_phase);
-      tc_fence_after();
-      const float inv = sum > 0.f ? 1.f / sum : 0.f;
-      const int srow = qb * kAttBQ + row;
-      __nv_bfloat16* dst = p.out + ((size_t)(b * S + srow) * H + h) * kAttD;
-#pragma unroll
-      for (int c = 0; c < kAttD; c += 32) {
-        uint32_t r[32];
-        tmem_ld_32x32b_x32(t_row + 448 + c, r);
+        // ---------------- epilogue: O / sum -> bf16 -> swizzled smem (the Q stage of this block) -> TMA store ----------------
+        mbar_wait(&o_full[w], uq & 1);
+        tc_fence_after();
+        uint32_t r0[32], r1[32];
+        tmem_ld_32x32b_x32(t_o, r0);
+        tmem_ld_32x32b_x32(t_o + 32, r1);
         tmem_ld_wait();
+        tc_fence_before();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&o_free[w]);
+        const float inv = sum > 0.f ? 1.f / sum : 0.f;
+        const uint32_t stg = smem_u32(sQ) + slot * kAttTile + row * 128;
 #pragma unroll
-        for (int i = 0; i < 32; i += 8) {
-          uint4 v;
-          v.x = pack_bf16x2(__uint_as_float(r[i]) * inv, __uint_as_float(r[i + 1]) * inv);
-          v.y = pack_bf16x2(__uint_as_float(r[i + 2]) * inv, __uint_as_float(r[i + 3]) * inv);
-          v.z = pack_bf16x2(__uint_as_float(r[i + 4]) * inv, __uint_as_float(r[i + 5]) * inv);
-          v.w = pack_bf16x2(__uint_as_float(r[i + 6]) * inv, __uint_as_float(r[i + 7]) * inv);
-          *reinterpret_cast<uint4*>(dst + c + i) = v;
+        for (int ch = 0; ch < 4; ++ch) {
+          const int i = ch * 8;
+          sts_u4(stg + ((ch ^ (row & 7)) << 4),
+                 pack_bf16x2(__uint_as_float(r0[i]) * inv, __uint_as_float(r0[i + 1]) * inv),
+                 pack_bf16x2(__uint_as_float(r0[i + 2]) * inv, __uint_as_float(r0[i + 3]) * inv),
+                 pack_bf16x2(__uint_as_float(r0[i + 4]) * inv, __uint_as_float(r0[i + 5]) * inv),
+                 pack_bf16x2(__uint_as_float(r0[i + 6]) * inv, __uint_as_float(r0[i + 7]) * inv));
+          sts_u4(stg + (((ch + 4) ^ (row & 7)) << 4),
+                 pack_bf16x2(__uint_as_float(r1[i]) * inv, __uint_as_float(r1[i + 1]) * inv),
+                 pack_bf16x2(__uint_as_float(r1[i + 2]) * inv, __uint_as_float(r1[i + 3]) * inv),
+                 pack_bf16x2(__uint_as_float(r1[i + 4]) * inv, __uint_as_float(r1[i + 5]) * inv),
+                 pack_bf16x2(__uint_as_float(r1[i + 6]) * inv, __uint_as_float(r1[i + 7]) * inv));
+        }
+        if (p.lse) p.lse[((size_t)b * H + h) * S + qb * kAttBQ + row] = (sum > 0.f) ? m * p.scale + __logf(sum) : -INFINITY;
+        fence_proxy_async_smem();
+        asm volatile("bar.sync %0, 128;" ::"r"(1 + w) : "memory");
+        if (store_leader) {
+          tma_store_2d(&tmap_out, sQ + slot * kAttTile, h * kAttD, b * S + qb * kAttBQ);
+          tma_store_commit();
+          pending_slot = slot;
         }
       }
-      if (p.lse) p.lse[((size_t)b * H + h) * S + srow] = (sum > 0.f) ? m * p.scale + __logf(sum) : -INFINITY;
-      tc_fence_before();
-      __syncwarp();
-      if (lane == 0) mbar_arrive(o_empty);
-      unit_phase ^= 1;
+      if (HAS_MASK) {
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&bias_free[bc & 1]);
+      }
     }
+    if (store_leader) tma_store_wait<0>();
   }
 
   tc_fence_before();
@@ -294,27 +388,29 @@ extern "C" int dedloc_attention_fwd(const void* qkv, const unsigned char* mask, 
                  kAttMaxS);
   DEDLOC_REQUIRE(((uintptr_t)qkv & 15) == 0 && ((uintptr_t)out & 15) == 0, "attention: pointers must be 16-byte aligned");
   { int rc0 = bind_context_for_driver_calls(); if (rc0) return rc0; }
-  CUtensorMap tm;
+  CUtensorMap tm, to;
   // packed qkv as a 2-D matrix: rows = B*S tokens, cols = 3*H*64, box = 64 columns x 128 rows
   int rc = make_tmap_2d_16bit(&tm, qkv, (long long)B * S, 3LL * H * D, 3LL * H * D, 64, 128, 1);
+  if (rc) return rc;
+  rc = make_tmap_2d_16bit(&to, out, (long long)B * S, (long long)H * D, (long long)H * D, 64, 128, 1);
   if (rc) return rc;
   static int sms = 0;
   if (sms == 0) {
     int dev = 0;
     DEDLOC_CUDA_CHECK(cudaGetDevice(&dev));
     DEDLOC_CUDA_CHECK(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
-    DEDLOC_CUDA_CHECK(cudaFuncSetAttribute(attention_fwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kAttSmem));
+    DEDLOC_CUDA_CHECK(cudaFuncSetAttribute(attention_fwd_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, kAttSmem));
+    DEDLOC_CUDA_CHECK(cudaFuncSetAttribute(attention_fwd_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kAttSmem));
   }
   AttFwdParams p;
   p.B = B; p.S = S; p.H = H;
   p.scale = scale;
   p.scale_log2 = scale * 1.4426950408889634f;
   p.mask = mask;
-  p.out = (__nv_bfloat16*)out;
   p.lse = lse;
-  const int units = B * H * (S / kAttBQ);
-  const int grid = units < sms ? units : sms;
-  attention_fwd_kernel<<<grid, kAttThreads, kAttSmem, (cudaStream_t)stream>>>(tm, p);
+  const int grid = B * H < sms ? B * H : sms;
+  if (mask) attention_fwd_kernel<true><<<grid, kAttThreads, kAttSmem, (cudaStream_t)stream>>>(tm, to, p);
+  else attention_fwd_kernel<false><<<grid, kAttThreads, kAttSmem, (cudaStream_t)stream>>>(tm, to, p);
   count_launch();
   DEDLOC_CUDA_CHECK(cudaGetLastError());
   return 0;
