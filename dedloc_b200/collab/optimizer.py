@@ -51,12 +51,13 @@ class CollaborativeOptimizer:
                  throughput: Optional[float] = None, bandwidth: Optional[float] = None,
                  listen_on: str = "127.0.0.1:*", start: bool = True, max_grad_norm: Optional[float] = None,
                  peer_key: Optional[bytes] = None, expected_group_size_from_tracker: bool = True,
-                 replicate_state: bool = True, **unused_kwargs):
+                 replicate_state: bool = True, step_slack_fraction: float = 0.5, **unused_kwargs):
         if compression is not None:  # sgd_collaborative.py:150 spells the kwarg `compression=`
             compression_type = compression
         if isinstance(compression_type, str):
             compression_type = CompressionType.Value(compression_type)
         self.opt, self.dht, self.prefix, self.scheduler = opt, dht, prefix, scheduler
+        self.step_slack_fraction = step_slack_fraction
         self.target_batch_size, self.batch_size_per_step = target_batch_size, batch_size_per_step
         self.averaging_timeout = averaging_timeout if averaging_timeout is not None else 30.0
         self.averaging_expiration, self.target_group_size = averaging_expiration, target_group_size
@@ -250,7 +251,10 @@ class CollaborativeOptimizer:
         self.last_step_time = get_dht_time()
         self._maybe_republish_state_sharing()
 
-        if not self.tracker.locally_ready():
+        # do not start a micro-step the collaboration will not wait for: ready if the ETA is closer than a fraction of it
+        slack = self.step_slack_fraction * batch_size / max(self.performance_ema.samples_per_second, 1e-9)
+        slack = min(slack, 0.5 * self.averaging_expiration)
+        if not self.tracker.locally_ready(slack):
             return False
         try:
             report.result(timeout=5.0)  # our own latest sample count must be visible to the re-fetch below
@@ -261,7 +265,7 @@ class CollaborativeOptimizer:
             # the collaboration moved on without us: our accumulated samples belong to a finished step
             if not self.is_synchronized:
                 return False
-        elif not state.ready_for_step:
+        elif not state.ready_within(slack):
             return False
         self._global_step(state)
         return True

@@ -49,6 +49,12 @@ class CollaborationState:
     def ready_for_step(self) -> bool:
         return self.samples_accumulated >= self.target_batch_size or get_dht_time() >= self.eta_next_step
 
+    def ready_within(self, slack_seconds: float) -> bool:
+        """`ready_for_step`, or the collaboration will get there within `slack_seconds`. Peers of one NVSwitch box run
+        in lock step, which makes "exactly at a micro-step boundary" the COMMON case for the ETA; without a slack half
+        of them start one more micro-step and the other half idle in the all-reduce kernel for its whole duration."""
+        return self.ready_for_step or get_dht_time() + max(slack_seconds, 0.0) >= self.eta_next_step
+
     def register_step(self, local_step: int) -> "CollaborationState":
         return CollaborationState(max(local_step, self.optimizer_step), 0, self.target_batch_size, self.num_peers,
                                   self.num_clients, float("inf"), self.next_fetch_time, self.num_aux)
@@ -154,11 +160,11 @@ class ProgressTracker:
             fut.result()
         return fut
 
-    def locally_ready(self) -> bool:
+    def locally_ready(self, slack_seconds: float = 0.0) -> bool:
         """`ready_for_step` of the cached collaboration state, corrected by the samples this peer accumulated
         since that state was fetched (so a fast peer does not wait for the next DHT refresh to notice)."""
         st = self.collaboration_state
-        if st.ready_for_step:
+        if st.ready_within(slack_seconds):
             return True
         own_delta = self.local_samples_accumulated - getattr(self, "_own_samples_in_state", 0)
         return st.optimizer_step <= self.local_step and st.samples_accumulated + max(own_delta, 0) >= st.target_batch_size

@@ -97,6 +97,48 @@ def pick_split_k(m_out: int, n_out: int, k_red: int, sms: int, block_n: int = 25
     return best_s
 
 
+# ---------------------------------------------------------------- weight / bias gradients off the critical path
+# Nothing downstream of a layer's backward consumes dW / db before the optimizer, so (opt-in) they are launched on a
+# low-priority side stream: the bandwidth-bound kernels of the critical path (LayerNorm backward, bias-gradient
+# column sums, attention) then share the SMs with the compute-bound weight-gradient GEMMs instead of queueing behind
+# them. All of them accumulate into the same shared-layer main_grad buffers (red.add) and stay ordered on the one
+# side stream. The caller must `join_wgrad_stream()` before reading the gradients (PeerTrainer does).
+_OVERLAP = {"enabled": False, "streams": {}, "refs": []}
+
+
+def overlap_wgrad(enabled: bool) -> None:
+    _OVERLAP["enabled"] = bool(enabled)
+
+
+def _side_stream(device) -> "torch.cuda.Stream":
+    idx = device.index if device.index is not None else torch.cuda.current_device()
+    if idx not in _OVERLAP["streams"]:
+        _OVERLAP["streams"][idx] = torch.cuda.Stream(device=idx, priority=0)   # main work runs at default priority too;
+    return _OVERLAP["streams"][idx]                                             # kernels already resident keep their SMs
+
+
+def _run_wgrad(device, fn, *keep_alive) -> None:
+    """Run `fn` (weight / bias gradient launches) on the side stream when overlap is on, else inline."""
+    if not _OVERLAP["enabled"]:
+        fn()
+        return
+    side, cur = _side_stream(device), torch.cuda.current_stream(device)
+    side.wait_stream(cur)
+    with torch.cuda.stream(side):
+        fn()
+    # the operands were allocated on the main stream: keep them referenced until the join, so that the caching
+    # allocator (also inside a CUDA-graph capture) cannot hand their memory to a later main-stream tensor
+    _OVERLAP["refs"].append(keep_alive)
+
+
+def join_wgrad_stream(device=None) -> None:
+    """Make the current stream wait for every outstanding side-stream gradient launch."""
+    for idx, side in _OVERLAP["streams"].items():
+        if device is None or idx == (device.index if device.index is not None else torch.cuda.current_device()):
+            torch.cuda.current_stream(idx).wait_stream(side)
+    _OVERLAP["refs"].clear()
+
+
 class _LinearFn(torch.autograd.Function):
     """y = act(x W^T + b) (+ residual). Weight/bias gradients are ACCUMULATED into `.main_grad` (fp32)."""
 
@@ -138,11 +180,15 @@ class _LinearFn(torch.autograd.Function):
         dx = torch.empty(M, K, dtype=x2.dtype, device=x2.device)
         gemm(dy2, weight, dx, b_mn_major=True)
         # wgrad: dW[N,K] += dy^T[N,M] . x[M,K]  -> both operands MN-major, reduction over tokens
-        wg = ctx.wgrad_out
+        wg, bg, has_bias = ctx.wgrad_out, ctx.bgrad_out, ctx.has_bias
         sk = pick_split_k(N, K, M, _sms(x2.device))
-        gemm(dy2, x2, wg, a_mn_major=True, b_mn_major=True, accumulate=True, split_k=sk)
-        if ctx.has_bias:
-            _bias_grad(dy2, ctx.bgrad_out)
+
+        def grads():
+            gemm(dy2, x2, wg, a_mn_major=True, b_mn_major=True, accumulate=True, split_k=sk)
+            if has_bias:
+                _bias_grad(dy2, bg)
+
+        _run_wgrad(x2.device, grads, dy2, x2)
         return dx.view(ctx.x_shape), None, None, None, dres, None, None
 
 
@@ -190,12 +236,20 @@ class _FFNFn(torch.autograd.Function):
         sms = _sms(x2.device)
         dpre = torch.empty(M, I, dtype=x2.dtype, device=x2.device)
         gemm(dy2, w2, dpre, b_mn_major=True, dgelu_aux=pre)                      # (dy W2) * gelu'(pre)
-        gemm(dy2, h, g_w2, a_mn_major=True, b_mn_major=True, accumulate=True, split_k=pick_split_k(N, I, M, sms))
-        _bias_grad(dy2, g_b2)
+
+        def grads2():
+            gemm(dy2, h, g_w2, a_mn_major=True, b_mn_major=True, accumulate=True, split_k=pick_split_k(N, I, M, sms))
+            _bias_grad(dy2, g_b2)
+
+        _run_wgrad(x2.device, grads2, dy2, h)
         dx = torch.empty(M, K, dtype=x2.dtype, device=x2.device)
         gemm(dpre, w1, dx, b_mn_major=True)
-        gemm(dpre, x2, g_w1, a_mn_major=True, b_mn_major=True, accumulate=True, split_k=pick_split_k(I, K, M, sms))
-        _bias_grad(dpre, g_b1)
+
+        def grads1():
+            gemm(dpre, x2, g_w1, a_mn_major=True, b_mn_major=True, accumulate=True, split_k=pick_split_k(I, K, M, sms))
+            _bias_grad(dpre, g_b1)
+
+        _run_wgrad(x2.device, grads1, dpre, x2)
         return dx.view(ctx.x_shape), None, None, None, None, (dy if ctx.has_res else None), None, None, None, None
 
 

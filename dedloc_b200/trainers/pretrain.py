@@ -106,6 +106,8 @@ class PeerConfig:
     # target_batch_size by the queue depth; 1 keeps the GPU fed while the control plane (progress report, DHT
     # re-fetch, matchmaking) of a global step hides under the micro-step that is still running.
     max_inflight_micro_steps: int = 1
+    # launch weight / bias gradient kernels on a side stream (joined before the gradients are read)
+    overlap_wgrad: bool = True
 
 
 class PeerTrainer:
@@ -123,11 +125,21 @@ class PeerTrainer:
     def _forward_backward(self, batch: Dict[str, torch.Tensor]) -> None:
         chunks = self.cfg.gradient_accumulation_steps
         n = batch["input_ids"].shape[0]
-        for c in range(chunks):
-            sub = {k: v[c * n // chunks:(c + 1) * n // chunks] for k, v in batch.items()} if chunks > 1 else batch
-            out = self.model(**sub)
-            (out.loss / chunks).backward()
-            self.loss_sum += out.loss.detach().float() / chunks
+        overlap = self.device.type == "cuda" and self.cfg.overlap_wgrad
+        if overlap:
+            from ..ops import gemm as _gemm
+
+            _gemm.overlap_wgrad(True)          # weight / bias gradients go to a side stream ...
+        try:
+            for c in range(chunks):
+                sub = {k: v[c * n // chunks:(c + 1) * n // chunks] for k, v in batch.items()} if chunks > 1 else batch
+                out = self.model(**sub)
+                (out.loss / chunks).backward()
+                self.loss_sum += out.loss.detach().float() / chunks
+        finally:
+            if overlap:
+                _gemm.overlap_wgrad(False)
+                _gemm.join_wgrad_stream(self.device)   # ... and are joined before anybody reads the gradients
         if hasattr(self.model, "flush_fused_grads"):
             self.model.flush_fused_grads()
 
