@@ -39,6 +39,7 @@ def parse_args():
     ap.add_argument("--ops", default="native", choices=["native", "torch"], help="linear layers: tcgen05 or torch")
     ap.add_argument("--skip-e2e", action="store_true")
     ap.add_argument("--no-cuda-graph", action="store_true", help="run the micro-step eagerly")
+    ap.add_argument("--overlap-wgrad", action="store_true", help="launch weight/bias gradient kernels on a side stream")
     return ap.parse_args()
 
 
@@ -136,7 +137,8 @@ def main_ours(args):
     seq = min(args.seq_len, model_cfg.max_position_embeddings)
     cfg = PeerConfig(prefix="bench", target_batch_size=args.target_batch_size, micro_batch=args.micro_batch,
                      seq_len=seq, compression=args.compression, target_group_size=max(world, 2),
-                     averaging_expiration=5.0, averaging_timeout=60.0, impl=args.ops)
+                     averaging_expiration=5.0, averaging_timeout=60.0, impl=args.ops,
+                     overlap_wgrad=args.overlap_wgrad)
     trainer = build_albert_peer(dht, cfg, model_cfg, device=device, seed=0)
     data = SyntheticMLMBatches(model_cfg.vocab_size, seq, args.micro_batch, seed=1234 + rank)
     resident = [data.to_device(b, device) for b in data.batches]   # device-resident copies for the kernel-timed arm

@@ -106,8 +106,9 @@ class PeerConfig:
     # target_batch_size by the queue depth; 1 keeps the GPU fed while the control plane (progress report, DHT
     # re-fetch, matchmaking) of a global step hides under the micro-step that is still running.
     max_inflight_micro_steps: int = 1
-    # launch weight / bias gradient kernels on a side stream (joined before the gradients are read)
-    overlap_wgrad: bool = True
+    # launch weight / bias gradient kernels on a side stream (joined before the gradients are read). Measured neutral
+    # on B200 (804.0 vs 802.2 samples/s: the persistent GEMMs own the SMs and the step is power-capped), so off.
+    overlap_wgrad: bool = False
 
 
 class PeerTrainer:
