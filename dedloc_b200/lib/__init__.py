@@ -113,6 +113,10 @@ def _declare(lib: C.CDLL) -> None:
     lib.dedloc_attention_bwd_scratch_floats.restype = ll
     lib.dedloc_attention_bwd.argtypes = [vp, vp, vp, vp, vp, vp, vp, i, i, i, i, f, vp]
     lib.dedloc_attention_bwd.restype = i
+    lib.dedloc_ce_fwd.argtypes = [vp, ll, vp, i, i, vp, vp, vp]
+    lib.dedloc_ce_fwd.restype = i
+    lib.dedloc_ce_bwd.argtypes = [vp, ll, vp, vp, vp, vp, ll, i, i, vp]
+    lib.dedloc_ce_bwd.restype = i
     for name in ("dedloc_layernorm_fwd", "dedloc_layernorm_bwd", "dedloc_colsum_accumulate"):
         getattr(lib, name).restype = i
     for name in ("dedloc_symm_alloc", "dedloc_symm_open", "dedloc_symm_close", "dedloc_symm_free",

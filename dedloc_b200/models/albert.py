@@ -24,6 +24,7 @@ import torch
 import torch.nn as nn
 import torch.nn.functional as F
 
+from ..ops import cross_entropy as _ce
 from ..ops.elementwise import gelu_new
 
 
@@ -400,8 +401,12 @@ class AlbertForPreTraining(nn.Module):
             sel_labels = flat_labels[order]
             sel_valid = is_masked[order]
             h = self.predictions.hidden(seq.reshape(B * S, H)[order], self.impl)
-            logits = F.linear(h, dec_w, self.predictions.bias).float()
-            per_tok = F.cross_entropy(logits, sel_labels.clamp_min(0), reduction="none")
+            logits = F.linear(h, dec_w, self.predictions.bias)
+            if self.impl == "native" and _ce.supported(logits):
+                # one pass for loss + log-sum-exp, one for the bf16 gradient: no fp32 copy of [cap, vocab]
+                per_tok = _ce.cross_entropy_rows(logits, sel_labels.clamp_min(0))
+            else:
+                per_tok = F.cross_entropy(logits.float(), sel_labels.clamp_min(0), reduction="none")
             denom = is_masked.sum().clamp_min(1)
             # positions beyond the capacity (never with 15% masking) would be dropped from the numerator only
             mlm_loss = (per_tok * sel_valid).sum() / denom

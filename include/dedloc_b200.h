@@ -160,6 +160,14 @@ long long dedloc_attention_bwd_scratch_floats(int S);
 int dedloc_attention_bwd(const void* qkv, const void* out, const void* dout, const float* lse, const unsigned char* mask,
                          void* dqkv, float* scratch, int B, int S, int H, int D, float scale, void* stream);
 
+/* ---- masked-LM cross-entropy on bf16 logits (torch cross_entropy(logits.float(), labels, reduction="none")) ---- */
+/* logits: [rows, V] bf16, row pitch ld elements (ld % 8 == 0); labels: int64 per row (out of range -> loss 0);
+ * loss, lse: fp32 per row. Backward: dlogits = (softmax - onehot(label)) * row_scale[row], bf16, row pitch ldd. */
+int dedloc_ce_fwd(const void* logits, long long ld, const long long* labels, int rows, int V, float* loss, float* lse,
+                  void* stream);
+int dedloc_ce_bwd(const void* logits, long long ld, const long long* labels, const float* lse, const float* row_scale,
+                  void* dlogits, long long ldd, int rows, int V, void* stream);
+
 #ifdef __cplusplus
 }
 #endif
