@@ -70,7 +70,7 @@ __device__ __forceinline__ void gemm_epilogue_math(const GemmKernelParams& p, in
           v[i] += t.x; v[i + 1] += t.y; v[i + 2] += t.z; v[i + 3] += t.w;
         }
       } else {
-        for (int i = 0; i < 32 && col0 + i < p.N; ++i) v[i] += __ldg(b + i);
+        _Pragma("unroll") for (int i = 0; i < 32; ++i) if (col0 + i < p.N) v[i] += __ldg(b + i);
       }
     } else {
       const __nv_bfloat16* b = reinterpret_cast<const __nv_bfloat16*>(p.bias) + col0;
@@ -83,7 +83,7 @@ __device__ __forceinline__ void gemm_epilogue_math(const GemmKernelParams& p, in
           for (int k = 0; k < 8; ++k) v[i + k] += t[k];
         }
       } else {
-        for (int i = 0; i < 32 && col0 + i < p.N; ++i) v[i] += __bfloat162float(b[i]);
+        _Pragma("unroll") for (int i = 0; i < 32; ++i) if (col0 + i < p.N) v[i] += __bfloat162float(b[i]);
       }
     }
   }
@@ -106,7 +106,7 @@ __device__ __forceinline__ void gemm_epilogue_math(const GemmKernelParams& p, in
         for (int k = 0; k < 8; ++k) v[i + k] *= gelu_tanh_grad(t[k]);
       }
     } else {
-      for (int i = 0; i < 32 && col0 + i < p.N; ++i) v[i] *= gelu_tanh_grad(__bfloat162float(ai[i]));
+      _Pragma("unroll") for (int i = 0; i < 32; ++i) if (col0 + i < p.N) v[i] *= gelu_tanh_grad(__bfloat162float(ai[i]));
     }
   }
   if ((p.epi & DEDLOC_EPI_RESIDUAL) && row_ok) {
@@ -120,7 +120,7 @@ __device__ __forceinline__ void gemm_epilogue_math(const GemmKernelParams& p, in
         for (int k = 0; k < 8; ++k) v[i + k] += t[k];
       }
     } else {
-      for (int i = 0; i < 32 && col0 + i < p.N; ++i) v[i] += __bfloat162float(rs[i]);
+      _Pragma("unroll") for (int i = 0; i < 32; ++i) if (col0 + i < p.N) v[i] += __bfloat162float(rs[i]);
     }
   }
 }
@@ -133,7 +133,7 @@ __device__ __forceinline__ void store_bf16_32(__nv_bfloat16* dst, const float (&
       *reinterpret_cast<uint4*>(dst + i) = make_uint4(pack_bf16x2(v[i], v[i + 1]), pack_bf16x2(v[i + 2], v[i + 3]),
                                                       pack_bf16x2(v[i + 4], v[i + 5]), pack_bf16x2(v[i + 6], v[i + 7]));
   } else {
-    for (int i = 0; i < 32 && i < valid; ++i) dst[i] = __float2bfloat16(v[i]);
+    _Pragma("unroll") for (int i = 0; i < 32; ++i) if (i < valid) dst[i] = __float2bfloat16(v[i]);
   }
 }
 
@@ -149,7 +149,7 @@ __device__ __forceinline__ void gemm_epilogue_store(const GemmKernelParams& p, i
 #pragma unroll
       for (int i = 0; i < 32; i += 4) *reinterpret_cast<float4*>(co + i) = make_float4(v[i], v[i + 1], v[i + 2], v[i + 3]);
     } else {
-      for (int i = 0; i < 32 && i < valid; ++i) co[i] = v[i];
+      _Pragma("unroll") for (int i = 0; i < 32; ++i) if (i < valid) co[i] = v[i];
     }
   } else {
     float* co = reinterpret_cast<float*>(p.C) + (size_t)row * p.ldc + col0;
@@ -160,7 +160,7 @@ __device__ __forceinline__ void gemm_epilogue_store(const GemmKernelParams& p, i
                      "f"(v[i + 2]), "f"(v[i + 3])
                      : "memory");
     } else {
-      for (int i = 0; i < 32 && i < valid; ++i) atomicAdd(co + i, v[i]);
+      _Pragma("unroll") for (int i = 0; i < 32; ++i) if (i < valid) atomicAdd(co + i, v[i]);
     }
   }
 }

@@ -13,16 +13,18 @@
 
 namespace dedloc {
 
-constexpr int k2Threads = 256;
+constexpr int k2Threads = 352;    // TMA, MMA, TMEM-alloc + 8 epilogue warps (11 warps: 184 registers per thread)
 constexpr int k2BM = 128;       // rows per CTA (256 per pair)
 constexpr int k2BN = 256;       // columns per pair; each CTA stages 128 of them
 constexpr int k2BK = 64;
-constexpr int k2Stages = 6;
+constexpr int k2Stages = 5;
 constexpr int k2ABytes = k2BM * k2BK * 2;          // 16 KB
 constexpr int k2BBytes = (k2BN / 2) * k2BK * 2;    // 16 KB
 constexpr int k2StageBytes = k2ABytes + k2BBytes;  // 32 KB per CTA per stage
-constexpr int k2StagingBytes = 4 * 2 * 4096;           // per epilogue warp: two 32-row x 128-byte TMA-store buffers
-constexpr int k2SmemTotal = k2Stages * k2StageBytes + k2StagingBytes + 256 + 1024;
+constexpr int k2EpiWarps = 8;      // two per TMEM lane quadrant: columns [0,128) and [128,256) of the tile
+constexpr int k2StagingBytes = k2EpiWarps * 2 * 4096;  // per epilogue warp: two 32-row x 128-byte TMA-store buffers
+constexpr int k2BiasBytes = k2BN * 4;                   // fp32 bias of the current tile's columns
+constexpr int k2SmemTotal = k2Stages * k2StageBytes + k2StagingBytes + k2BiasBytes + 128 + 1024;
 constexpr uint32_t kPeerBitMask = 0xFEFFFFFFu;     // clears the CTA-pair bit of a shared::cluster address
 
 __device__ __forceinline__ uint32_t cluster_ctarank() {
@@ -81,7 +83,8 @@ gemm_tcgen05_2cta_kernel(const __grid_constant__ CUtensorMap tmap_a, const __gri
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   uint8_t* staging = smem + k2Stages * k2StageBytes;
-  uint64_t* bars = reinterpret_cast<uint64_t*>(staging + k2StagingBytes);
+  float* sbias = reinterpret_cast<float*>(staging + k2StagingBytes);
+  uint64_t* bars = reinterpret_cast<uint64_t*>(staging + k2StagingBytes + k2BiasBytes);
   uint64_t* full_bar = bars;                        // [k2Stages]  (leader's copy is the live one)
   uint64_t* empty_bar = bars + k2Stages;            // [k2Stages]  (live in both CTAs)
   uint64_t* tmem_full = bars + 2 * k2Stages;        // [2]         (live in both CTAs)
@@ -105,7 +108,7 @@ gemm_tcgen05_2cta_kernel(const __grid_constant__ CUtensorMap tmap_a, const __gri
   }
   if (warp == 1 && lane == 0) {
     for (int s = 0; s < k2Stages; ++s) { mbar_init(&full_bar[s], 1); mbar_init(&empty_bar[s], 1); }
-    for (int s = 0; s < 2; ++s) { mbar_init(&tmem_full[s], 1); mbar_init(&tmem_empty[s], 8); }
+    for (int s = 0; s < 2; ++s) { mbar_init(&tmem_full[s], 1); mbar_init(&tmem_empty[s], 2 * k2EpiWarps); }
     mbar_fence_init();
   }
   if (warp == 2) tmem_alloc_2cta(tmem_base_slot, 2 * k2BN);
@@ -194,75 +197,231 @@ gemm_tcgen05_2cta_kernel(const __grid_constant__ CUtensorMap tmap_a, const __gri
         if (++acc == 2) { acc = 0; acc_phase ^= 1; }
       }
     }
-  } else if (warp >= 4) {
-    // ===================== epilogue (both CTAs, own 128 rows) =====================
-    const int quad = warp & 3;
+  } else if (warp >= 3) {
+    // ===================== epilogue (both CTAs, own 128 rows; 8 warps) =====================
+    // The fused epilogues (bias, gelu, gelu', residual, second output) cost 20-40 instructions per element, which
+    // four warps cannot retire within one tile's MMA time (8192 clk): warps 3-6 take columns [0,128) of the tile,
+    // warps 7-10 columns [128,256), one TMEM lane quadrant (warp id % 4) each. Per tile and warp:
+    //   - the bias of the warp's 128 columns is staged once in shared memory as fp32 (broadcast LDS afterwards)
+    //   - the row-indexed operands (gelu' pre-activation, residual) of all four 32-column chunks are requested BEFORE
+    //     waiting for the accumulator, so their latency hides behind the mainloop instead of stalling every chunk
+    //   - bf16 outputs leave through swizzled smem + TMA stores (coalesced 128-byte rows, tails clipped by the tensor
+    //     map); fp32 / atomic outputs use direct register stores.
+    const int quad = warp & 3, half = (warp - 3) >> 2, ew = warp - 3;
     int acc = 0;
     uint32_t acc_phase = 0;
-    // bf16 outputs leave through swizzled smem + TMA stores (coalesced 128-byte rows, tails clipped by the tensor
-    // map); fp32 / atomic outputs use direct register stores.
     const bool tma_c = (p.out_kind == 0);
     const bool tma_pre = tma_c && (p.epi & DEDLOC_EPI_SAVE_PRE);
-    uint8_t* stg = staging + quad * 8192;
+    const bool has_bias = (p.epi & DEDLOC_EPI_BIAS) != 0;
+    const bool has_aux = (p.epi & DEDLOC_EPI_DGELU) != 0, has_res = (p.epi & DEDLOC_EPI_RESIDUAL) != 0;
+    const uint32_t stg = smem_u32(staging) + ew * 8192;
+    const uint32_t sbias_a = smem_u32(sbias) + half * 512;
     int sbuf = 0;
     for (int tile = cluster_id; tile < total_tiles; tile += num_clusters) {
       const int rem = tile % (m_tiles * n_tiles);
       int mt, nt;
       tile_coords(rem, m_tiles, n_tiles, mt, nt);
       const int m0 = mt * (2 * k2BM) + (int)cta_rank * k2BM;
-      const int n0 = nt * k2BN;
-      mbar_wait(&tmem_full[acc], acc_phase);
-      tc_fence_after();
+      const int n0 = nt * k2BN + half * (k2BN / 2);          // first column of this warp
       const int row = m0 + quad * 32 + lane;
       const bool row_ok = row < p.M;
-      const uint32_t taddr = tmem_base + ((uint32_t)(quad * 32) << 16) + acc * k2BN;
-      if (!tma_c) {
-#pragma unroll 1
-        for (int cb = 0; cb < k2BN; cb += 32) {
-          uint32_t r[32];
-          tmem_ld_32x32b_x32(taddr + cb, r);
-          tmem_ld_wait();
-          const int col0 = n0 + cb;
-          if (col0 >= p.N) continue;  // warp-uniform
-          gemm_epilogue_32cols(p, row, row_ok, col0, r);
-        }
-      } else {
-#pragma unroll 1
-        for (int cb = 0; cb < k2BN; cb += 64) {
-          const int col0 = n0 + cb;
-          if (col0 >= p.N) break;  // warp-uniform
-          uint8_t* buf_out = stg + sbuf * 4096;
-          uint8_t* buf_pre = stg + (sbuf ^ 1) * 4096;
-          // the buffer(s) written below must have been fully read by their previous TMA store
-          if (lane == 0) { if (tma_pre) tma_store_wait_read<0>(); else tma_store_wait_read<1>(); }
-          __syncwarp();
-#pragma unroll
-          for (int half = 0; half < 2; ++half) {
-            uint32_t r[32];
-            tmem_ld_32x32b_x32(taddr + cb + half * 32, r);
-            tmem_ld_wait();
-            float v[32], pre[32];
-            gemm_epilogue_math(p, row, row_ok, col0 + half * 32, r, v, pre);
-#pragma unroll
-            for (int ch = 0; ch < 4; ++ch) {
-              const uint32_t off = (uint32_t)lane * 128 + (((uint32_t)(half * 4 + ch) ^ ((uint32_t)lane & 7)) << 4);
-              *reinterpret_cast<uint4*>(buf_out + off) =
-                  make_uint4(pack_bf16x2(v[8 * ch], v[8 * ch + 1]), pack_bf16x2(v[8 * ch + 2], v[8 * ch + 3]),
-                             pack_bf16x2(v[8 * ch + 4], v[8 * ch + 5]), pack_bf16x2(v[8 * ch + 6], v[8 * ch + 7]));
-              if (tma_pre)
-                *reinterpret_cast<uint4*>(buf_pre + off) =
-                    make_uint4(pack_bf16x2(pre[8 * ch], pre[8 * ch + 1]), pack_bf16x2(pre[8 * ch + 2], pre[8 * ch + 3]),
-                               pack_bf16x2(pre[8 * ch + 4], pre[8 * ch + 5]), pack_bf16x2(pre[8 * ch + 6], pre[8 * ch + 7]));
+      if (has_bias) {
+        // everybody in this half is done with the previous tile's bias; quadrant 0 stages the next 128 values
+        asm volatile("bar.sync %0, 128;" ::"r"(1 + half) : "memory");
+        if (quad == 0) {
+          float4 b4 = make_float4(0.f, 0.f, 0.f, 0.f);
+          const int c = n0 + lane * 4;
+          if (p.epi & DEDLOC_EPI_BIAS_F32) {
+            const float* bp = reinterpret_cast<const float*>(p.bias);
+            if (c + 3 < p.N) b4 = __ldg(reinterpret_cast<const float4*>(bp + c));
+            else { if (c < p.N) b4.x = bp[c]; if (c + 1 < p.N) b4.y = bp[c + 1]; if (c + 2 < p.N) b4.z = bp[c + 2]; }
+          } else {
+            const __nv_bfloat16* bp = reinterpret_cast<const __nv_bfloat16*>(p.bias);
+            if (c + 3 < p.N) {
+              const uint2 u = __ldg(reinterpret_cast<const uint2*>(bp + c));
+              const float2 lo = unpack_bf16x2(u.x), hi = unpack_bf16x2(u.y);
+              b4 = make_float4(lo.x, lo.y, hi.x, hi.y);
+            } else {
+              if (c < p.N) b4.x = __bfloat162float(bp[c]);
+              if (c + 1 < p.N) b4.y = __bfloat162float(bp[c + 1]);
+              if (c + 2 < p.N) b4.z = __bfloat162float(bp[c + 2]);
             }
           }
-          fence_proxy_async_smem();
-          __syncwarp();
-          if (lane == 0) {
-            if (tma_pre) { tma_store_2d(&tmap_pre, buf_pre, col0, m0 + quad * 32); tma_store_commit(); }
-            tma_store_2d(&tmap_c, buf_out, col0, m0 + quad * 32);
-            tma_store_commit();
+          asm volatile("st.shared.v4.f32 [%0], {%1, %2, %3, %4};" ::"r"(sbias_a + lane * 16), "f"(b4.x), "f"(b4.y),
+                       "f"(b4.z), "f"(b4.w) : "memory");
+        }
+        asm volatile("bar.sync %0, 128;" ::"r"(1 + half) : "memory");
+      }
+      // Row-indexed operand (gelu' input or residual; if both are requested the residual is read directly below):
+      // requested BEFORE waiting for the accumulator with COALESCED loads -- 8 lanes x 16 B per 128-byte row segment,
+      // 4 rows per instruction (row-per-thread loads touch 32 lines per instruction and throttle the LSU to ~4 clk
+      // per request: 15 000 clk per tile) -- and transposed to row-per-thread through the warp's staging buffer.
+      uint4 pf[8];                                   // one 64-column box at a time (box 1 is requested after box 0 is staged)
+      const bool use_pf = tma_c && (has_aux || has_res) && (n0 + 128 <= p.N) && (m0 + quad * 32 + 32 <= p.M);
+      const __nv_bfloat16* pf_src = nullptr;
+      long long pf_ld = 0;
+      if (use_pf) {
+        pf_src = has_aux ? reinterpret_cast<const __nv_bfloat16*>(p.aux_in) : reinterpret_cast<const __nv_bfloat16*>(p.residual);
+        pf_ld = has_aux ? p.ld_aux : p.ld_res;
+        pf_src += (size_t)(m0 + quad * 32 + (lane >> 3)) * pf_ld + n0 + (lane & 7) * 8;
+#pragma unroll
+        for (int q = 0; q < 8; ++q) pf[q] = ld_stream_v4(pf_src + (size_t)(q * 4) * pf_ld);
+      }
+      mbar_wait(&tmem_full[acc], acc_phase);
+      tc_fence_after();
+      const uint32_t taddr = tmem_base + ((uint32_t)(quad * 32) << 16) + acc * k2BN + half * (k2BN / 2);
+      // v = epilogue(accumulator chunk c); `pre` only with SAVE_PRE; `rowop_a` = smem address of this row's 32 staged
+      // bf16 operand values (swizzled 16-byte pieces), read 8 at a time to keep the live set small
+      auto chunk_math = [&](int c, const uint32_t (&r)[32], float (&v)[32], float (&pre)[32], uint32_t rowop_a,
+                            bool have_rowop) {
+        const int col0 = n0 + c * 32;
+        if (p.alpha != 1.f) {
+#pragma unroll
+          for (int i = 0; i < 32; ++i) v[i] = __uint_as_float(r[i]) * p.alpha;
+        } else {
+#pragma unroll
+          for (int i = 0; i < 32; ++i) v[i] = __uint_as_float(r[i]);
+        }
+        if (has_bias) {
+#pragma unroll
+          for (int i = 0; i < 32; i += 4) {
+            const float4 b4 = lds_f4(sbias_a + (c * 32 + i) * 4);
+            v[i] += b4.x; v[i + 1] += b4.y; v[i + 2] += b4.z; v[i + 3] += b4.w;
           }
-          if (!tma_pre) sbuf ^= 1;
+        }
+        if (p.epi & DEDLOC_EPI_SAVE_PRE) {
+#pragma unroll
+          for (int i = 0; i < 32; ++i) pre[i] = v[i];
+        }
+        if (p.epi & DEDLOC_EPI_GELU) {
+#pragma unroll
+          for (int i = 0; i < 32; ++i) v[i] = gelu_tanh(v[i]);
+        }
+        if (has_aux && row_ok) {
+          if (have_rowop) {
+#pragma unroll
+            for (int pc = 0; pc < 4; ++pc) {
+              const float4 f = lds_f4(rowop_a + ((((uint32_t)((c & 1) * 4 + pc)) ^ ((uint32_t)lane & 7)) << 4));
+              const float2 a0 = unpack_bf16x2(__float_as_uint(f.x)), a1 = unpack_bf16x2(__float_as_uint(f.y));
+              const float2 a2 = unpack_bf16x2(__float_as_uint(f.z)), a3 = unpack_bf16x2(__float_as_uint(f.w));
+              v[pc * 8 + 0] *= gelu_tanh_grad(a0.x); v[pc * 8 + 1] *= gelu_tanh_grad(a0.y);
+              v[pc * 8 + 2] *= gelu_tanh_grad(a1.x); v[pc * 8 + 3] *= gelu_tanh_grad(a1.y);
+              v[pc * 8 + 4] *= gelu_tanh_grad(a2.x); v[pc * 8 + 5] *= gelu_tanh_grad(a2.y);
+              v[pc * 8 + 6] *= gelu_tanh_grad(a3.x); v[pc * 8 + 7] *= gelu_tanh_grad(a3.y);
+            }
+          } else {
+            const __nv_bfloat16* ai = reinterpret_cast<const __nv_bfloat16*>(p.aux_in) + (size_t)row * p.ld_aux + col0;
+            _Pragma("unroll") for (int i = 0; i < 32; ++i) if (col0 + i < p.N) v[i] *= gelu_tanh_grad(__bfloat162float(ai[i]));
+          }
+        }
+        if (has_res && row_ok) {
+          if (have_rowop && !has_aux) {
+#pragma unroll
+            for (int pc = 0; pc < 4; ++pc) {
+              const float4 f = lds_f4(rowop_a + ((((uint32_t)((c & 1) * 4 + pc)) ^ ((uint32_t)lane & 7)) << 4));
+              const float2 a0 = unpack_bf16x2(__float_as_uint(f.x)), a1 = unpack_bf16x2(__float_as_uint(f.y));
+              const float2 a2 = unpack_bf16x2(__float_as_uint(f.z)), a3 = unpack_bf16x2(__float_as_uint(f.w));
+              v[pc * 8 + 0] += a0.x; v[pc * 8 + 1] += a0.y; v[pc * 8 + 2] += a1.x; v[pc * 8 + 3] += a1.y;
+              v[pc * 8 + 4] += a2.x; v[pc * 8 + 5] += a2.y; v[pc * 8 + 6] += a3.x; v[pc * 8 + 7] += a3.y;
+            }
+          } else {
+            const __nv_bfloat16* rs = reinterpret_cast<const __nv_bfloat16*>(p.residual) + (size_t)row * p.ld_res + col0;
+            _Pragma("unroll") for (int i = 0; i < 32; ++i) if (col0 + i < p.N) v[i] += __bfloat162float(rs[i]);
+          }
+        }
+      };
+      if (!tma_c) {
+#pragma unroll
+        for (int c = 0; c < 4; ++c) {
+          const int col0 = n0 + c * 32;
+          if (col0 >= p.N) break;  // warp-uniform
+          uint32_t r[32];
+          tmem_ld_32x32b_x32(taddr + c * 32, r);
+          tmem_ld_wait();
+          float v[32], pre[32];
+          chunk_math(c, r, v, pre, 0u, false);
+          if (!row_ok) continue;
+          if (p.epi & DEDLOC_EPI_SAVE_PRE)
+            store_bf16_32(reinterpret_cast<__nv_bfloat16*>(p.pre_out) + (size_t)row * p.ld_pre + col0, pre, col0 + 32 <= p.N,
+                          p.N - col0);
+          gemm_epilogue_store(p, row, col0, v);
+        }
+      } else {
+        // two staging buffers per warp. Without a second output they alternate per 64-column box; with SAVE_PRE buffer
+        // 0 carries the pre-activation and buffer 1 the output, each waiting only for ITS previous store
+        // (wait_group.read 1 leaves the most recent store in flight).
+#pragma unroll
+        for (int cb = 0; cb < 2; ++cb) {
+          const int col0 = n0 + cb * 64;
+          if (col0 >= p.N) break;  // warp-uniform
+          const int b_first = tma_pre ? 0 : sbuf;
+          const uint32_t buf_first = stg + b_first * 4096;
+          if (lane == 0) tma_store_wait_read<1>();      // buf_first has been read by its previous store
+          __syncwarp();
+          if (use_pf) {
+            // coalesced registers -> swizzled smem; afterwards thread L only touches row L of the buffer (it reads the
+            // operand of a chunk and later writes the result of the same chunk in place), so one __syncwarp suffices
+#pragma unroll
+            for (int i = 0; i < 8; ++i) {
+              const uint32_t rr = i * 4 + (lane >> 3);
+              sts_u4(buf_first + rr * 128 + ((((uint32_t)lane & 7) ^ (rr & 7)) << 4), pf[i].x, pf[i].y, pf[i].z, pf[i].w);
+            }
+            __syncwarp();
+            if (cb == 0) {
+#pragma unroll
+              for (int q = 0; q < 8; ++q) pf[q] = ld_stream_v4(pf_src + (size_t)(q * 4) * pf_ld + 64);
+            }
+          }
+          auto stage_chunk = [&](const float (&x)[32], uint32_t buf, int hh) {
+#pragma unroll
+            for (int ch = 0; ch < 4; ++ch) {
+              const uint32_t off = (uint32_t)lane * 128 + (((uint32_t)(hh * 4 + ch) ^ ((uint32_t)lane & 7)) << 4);
+              sts_u4(buf + off, pack_bf16x2(x[8 * ch], x[8 * ch + 1]), pack_bf16x2(x[8 * ch + 2], x[8 * ch + 3]),
+                     pack_bf16x2(x[8 * ch + 4], x[8 * ch + 5]), pack_bf16x2(x[8 * ch + 6], x[8 * ch + 7]));
+            }
+          };
+          auto store_box = [&](int bsel, const CUtensorMap* tm) {
+            fence_proxy_async_smem();
+            __syncwarp();
+            if (lane == 0) {
+              tma_store_2d(tm, staging + ew * 8192 + bsel * 4096, col0, m0 + quad * 32);
+              tma_store_commit();
+            }
+          };
+          if (tma_pre) {
+            // second output: pass A stages the pre-activation (accumulator + bias), pass B re-reads the accumulator
+            // (tensor-memory loads are cheap; keeping 64 results live would spill) and stages the activated output
+#pragma unroll
+            for (int pass = 0; pass < 2; ++pass) {
+              const uint32_t buf = stg + pass * 4096;
+              if (pass == 1) {
+                if (lane == 0) tma_store_wait_read<1>();    // buffer 1's previous store (one box ago) is done
+                __syncwarp();
+              }
+#pragma unroll
+              for (int hh = 0; hh < 2; ++hh) {
+                uint32_t r[32];
+                tmem_ld_32x32b_x32(taddr + cb * 64 + hh * 32, r);
+                tmem_ld_wait();
+                float v[32], pre[32];
+                chunk_math(cb * 2 + hh, r, v, pre, 0u, false);
+                if (pass == 0) stage_chunk(pre, buf, hh); else stage_chunk(v, buf, hh);
+              }
+              store_box(pass, pass == 0 ? &tmap_pre : &tmap_c);
+            }
+          } else {
+#pragma unroll
+            for (int hh = 0; hh < 2; ++hh) {
+              uint32_t r[32];
+              tmem_ld_32x32b_x32(taddr + cb * 64 + hh * 32, r);
+              tmem_ld_wait();
+              float v[32], pre[32];
+              chunk_math(cb * 2 + hh, r, v, pre, buf_first + (uint32_t)lane * 128, use_pf);
+              stage_chunk(v, buf_first, hh);
+            }
+            store_box(sbuf, &tmap_c);
+            sbuf ^= 1;
+          }
         }
       }
       tc_fence_before();
