@@ -399,6 +399,16 @@ __device__ __forceinline__ float gelu_tanh(float x) {
   asm("tanh.approx.f32 %0, %1;" : "=f"(t) : "f"(inner));
   return 0.5f * x * (1.f + t);
 }
+// gelu_new and its derivative from ONE tanh
+__device__ __forceinline__ void gelu_tanh_both(float x, float& g, float& dg) {
+  const float k = 0.7978845608028654f, c = 0.044715f;
+  const float x2 = x * x;
+  float t;
+  asm("tanh.approx.f32 %0, %1;" : "=f"(t) : "f"(k * x * fmaf(c, x2, 1.f)));
+  const float h = fmaf(0.5f, t, 0.5f);                 // 0.5 (1 + t)
+  g = x * h;
+  dg = fmaf(0.5f * x * fmaf(-t, t, 1.f), k * fmaf(3.f * c, x2, 1.f), h);
+}
 __device__ __forceinline__ float gelu_tanh_grad(float x) {
   const float k = 0.7978845608028654f;
   float x2 = x * x;

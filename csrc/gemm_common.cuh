@@ -87,15 +87,21 @@ __device__ __forceinline__ void gemm_epilogue_math(const GemmKernelParams& p, in
       }
     }
   }
-  if (p.epi & DEDLOC_EPI_SAVE_PRE) {
+  if ((p.epi & DEDLOC_EPI_GELU) && (p.epi & DEDLOC_EPI_SAVE_DGELU)) {
 #pragma unroll
-    for (int i = 0; i < 32; ++i) pre[i] = v[i];
-  }
-  if (p.epi & DEDLOC_EPI_GELU) {
+    for (int i = 0; i < 32; ++i) gelu_tanh_both(v[i], v[i], pre[i]);
+  } else {
+    if (p.epi & DEDLOC_EPI_SAVE_PRE) {
 #pragma unroll
-    for (int i = 0; i < 32; ++i) v[i] = gelu_tanh(v[i]);
+      for (int i = 0; i < 32; ++i) pre[i] = v[i];
+    }
+    if (p.epi & DEDLOC_EPI_GELU) {
+#pragma unroll
+      for (int i = 0; i < 32; ++i) v[i] = gelu_tanh(v[i]);
+    }
   }
-  if ((p.epi & DEDLOC_EPI_DGELU) && row_ok) {
+  if ((p.epi & (DEDLOC_EPI_DGELU | DEDLOC_EPI_MUL_AUX)) && row_ok) {
+    const bool mul_aux = (p.epi & DEDLOC_EPI_MUL_AUX) != 0;
     const __nv_bfloat16* ai = reinterpret_cast<const __nv_bfloat16*>(p.aux_in) + (size_t)row * p.ld_aux + col0;
     if (full_cols) {
 #pragma unroll
@@ -103,10 +109,13 @@ __device__ __forceinline__ void gemm_epilogue_math(const GemmKernelParams& p, in
         float t[8];
         unpack8_bf16(*reinterpret_cast<const uint4*>(ai + i), t);
 #pragma unroll
-        for (int k = 0; k < 8; ++k) v[i + k] *= gelu_tanh_grad(t[k]);
+        for (int k = 0; k < 8; ++k) v[i + k] *= mul_aux ? t[k] : gelu_tanh_grad(t[k]);
       }
     } else {
-      _Pragma("unroll") for (int i = 0; i < 32; ++i) if (col0 + i < p.N) v[i] *= gelu_tanh_grad(__bfloat162float(ai[i]));
+      _Pragma("unroll") for (int i = 0; i < 32; ++i) if (col0 + i < p.N) {
+        const float a = __bfloat162float(ai[i]);
+        v[i] *= mul_aux ? a : gelu_tanh_grad(a);
+      }
     }
   }
   if ((p.epi & DEDLOC_EPI_RESIDUAL) && row_ok) {

@@ -316,7 +316,10 @@ extern "C" int dedloc_gemm(const DedlocGemmArgs* gp, void* stream) {
   if (g.a_mn_major) DEDLOC_REQUIRE(g.M % 8 == 0, "gemm: MN-major A needs M %% 8 == 0");
   cudaStream_t st = (cudaStream_t)stream;
   // CTA pairs halve the L2->SMEM traffic of the B operand; worth it once the problem fills 74 pairs
-  const bool pair_ok = g.block_n != 128 && g.N > 128;
+  // (the pair kernel's two-output epilogue does not combine with row-indexed operands)
+  const bool two_out_rowop = (g.epilogue & DEDLOC_EPI_SAVE_PRE) && g.out_kind == 0 &&
+                             (g.epilogue & (DEDLOC_EPI_RESIDUAL | DEDLOC_EPI_DGELU | DEDLOC_EPI_MUL_AUX));
+  const bool pair_ok = g.block_n != 128 && g.N > 128 && !two_out_rowop;
   const long long tiles_2cta = (long long)((g.M + 255) / 256) * ((g.N + 255) / 256) * (g.split_k > 1 ? g.split_k : 1);
   if (g.cta_pair == 2 || (g.cta_pair == 0 && pair_ok && tiles_2cta >= 64)) {
     DEDLOC_REQUIRE(pair_ok, "gemm: the CTA-pair kernel needs N > 128 and block_n != 128");

@@ -213,7 +213,8 @@ gemm_tcgen05_2cta_kernel(const __grid_constant__ CUtensorMap tmap_a, const __gri
     const bool tma_c = (p.out_kind == 0);
     const bool tma_pre = tma_c && (p.epi & DEDLOC_EPI_SAVE_PRE);
     const bool has_bias = (p.epi & DEDLOC_EPI_BIAS) != 0;
-    const bool has_aux = (p.epi & DEDLOC_EPI_DGELU) != 0, has_res = (p.epi & DEDLOC_EPI_RESIDUAL) != 0;
+    const bool has_aux = (p.epi & (DEDLOC_EPI_DGELU | DEDLOC_EPI_MUL_AUX)) != 0, has_res = (p.epi & DEDLOC_EPI_RESIDUAL) != 0;
+    const bool mul_aux = (p.epi & DEDLOC_EPI_MUL_AUX) != 0;     // aux is the saved derivative itself
     const uint32_t stg = smem_u32(staging) + ew * 8192;
     const uint32_t sbias_a = smem_u32(sbias) + half * 512;
     int sbuf = 0;
@@ -289,13 +290,18 @@ gemm_tcgen05_2cta_kernel(const __grid_constant__ CUtensorMap tmap_a, const __gri
             v[i] += b4.x; v[i + 1] += b4.y; v[i + 2] += b4.z; v[i + 3] += b4.w;
           }
         }
-        if (p.epi & DEDLOC_EPI_SAVE_PRE) {
+        if ((p.epi & DEDLOC_EPI_GELU) && (p.epi & DEDLOC_EPI_SAVE_DGELU)) {
 #pragma unroll
-          for (int i = 0; i < 32; ++i) pre[i] = v[i];
-        }
-        if (p.epi & DEDLOC_EPI_GELU) {
+          for (int i = 0; i < 32; ++i) gelu_tanh_both(v[i], v[i], pre[i]);
+        } else {
+          if (p.epi & DEDLOC_EPI_SAVE_PRE) {
 #pragma unroll
-          for (int i = 0; i < 32; ++i) v[i] = gelu_tanh(v[i]);
+            for (int i = 0; i < 32; ++i) pre[i] = v[i];
+          }
+          if (p.epi & DEDLOC_EPI_GELU) {
+#pragma unroll
+            for (int i = 0; i < 32; ++i) v[i] = gelu_tanh(v[i]);
+          }
         }
         if (has_aux && row_ok) {
           if (have_rowop) {
@@ -304,14 +310,22 @@ gemm_tcgen05_2cta_kernel(const __grid_constant__ CUtensorMap tmap_a, const __gri
               const float4 f = lds_f4(rowop_a + ((((uint32_t)((c & 1) * 4 + pc)) ^ ((uint32_t)lane & 7)) << 4));
               const float2 a0 = unpack_bf16x2(__float_as_uint(f.x)), a1 = unpack_bf16x2(__float_as_uint(f.y));
               const float2 a2 = unpack_bf16x2(__float_as_uint(f.z)), a3 = unpack_bf16x2(__float_as_uint(f.w));
-              v[pc * 8 + 0] *= gelu_tanh_grad(a0.x); v[pc * 8 + 1] *= gelu_tanh_grad(a0.y);
-              v[pc * 8 + 2] *= gelu_tanh_grad(a1.x); v[pc * 8 + 3] *= gelu_tanh_grad(a1.y);
-              v[pc * 8 + 4] *= gelu_tanh_grad(a2.x); v[pc * 8 + 5] *= gelu_tanh_grad(a2.y);
-              v[pc * 8 + 6] *= gelu_tanh_grad(a3.x); v[pc * 8 + 7] *= gelu_tanh_grad(a3.y);
+              if (mul_aux) {
+                v[pc * 8 + 0] *= a0.x; v[pc * 8 + 1] *= a0.y; v[pc * 8 + 2] *= a1.x; v[pc * 8 + 3] *= a1.y;
+                v[pc * 8 + 4] *= a2.x; v[pc * 8 + 5] *= a2.y; v[pc * 8 + 6] *= a3.x; v[pc * 8 + 7] *= a3.y;
+              } else {
+                v[pc * 8 + 0] *= gelu_tanh_grad(a0.x); v[pc * 8 + 1] *= gelu_tanh_grad(a0.y);
+                v[pc * 8 + 2] *= gelu_tanh_grad(a1.x); v[pc * 8 + 3] *= gelu_tanh_grad(a1.y);
+                v[pc * 8 + 4] *= gelu_tanh_grad(a2.x); v[pc * 8 + 5] *= gelu_tanh_grad(a2.y);
+                v[pc * 8 + 6] *= gelu_tanh_grad(a3.x); v[pc * 8 + 7] *= gelu_tanh_grad(a3.y);
+              }
             }
           } else {
             const __nv_bfloat16* ai = reinterpret_cast<const __nv_bfloat16*>(p.aux_in) + (size_t)row * p.ld_aux + col0;
-            _Pragma("unroll") for (int i = 0; i < 32; ++i) if (col0 + i < p.N) v[i] *= gelu_tanh_grad(__bfloat162float(ai[i]));
+            _Pragma("unroll") for (int i = 0; i < 32; ++i) if (col0 + i < p.N) {
+              const float a = __bfloat162float(ai[i]);
+              v[i] *= mul_aux ? a : gelu_tanh_grad(a);
+            }
           }
         }
         if (has_res && row_ok) {
@@ -389,26 +403,56 @@ gemm_tcgen05_2cta_kernel(const __grid_constant__ CUtensorMap tmap_a, const __gri
             }
           };
           if (tma_pre) {
-            // second output: pass A stages the pre-activation (accumulator + bias), pass B re-reads the accumulator
-            // (tensor-memory loads are cheap; keeping 64 results live would spill) and stages the activated output
+            // second output: the saved tensor (pre-activation or gelu') is staged chunk by chunk into buffer 0; the
+            // activated output waits -- packed to bf16, 32 registers -- until buffer 1's previous store has been read
+            uint32_t keep[2][16];
 #pragma unroll
-            for (int pass = 0; pass < 2; ++pass) {
-              const uint32_t buf = stg + pass * 4096;
-              if (pass == 1) {
-                if (lane == 0) tma_store_wait_read<1>();    // buffer 1's previous store (one box ago) is done
-                __syncwarp();
-              }
+            for (int hh = 0; hh < 2; ++hh) {
+              uint32_t r[32];
+              tmem_ld_32x32b_x32(taddr + cb * 64 + hh * 32, r);
+              tmem_ld_wait();
+              // 8 columns at a time (bias, activation, both packs) to keep the live set small
+              const int c = cb * 2 + hh;
+              const bool both = (p.epi & DEDLOC_EPI_GELU) && (p.epi & DEDLOC_EPI_SAVE_DGELU);
 #pragma unroll
-              for (int hh = 0; hh < 2; ++hh) {
-                uint32_t r[32];
-                tmem_ld_32x32b_x32(taddr + cb * 64 + hh * 32, r);
-                tmem_ld_wait();
-                float v[32], pre[32];
-                chunk_math(cb * 2 + hh, r, v, pre, 0u, false);
-                if (pass == 0) stage_chunk(pre, buf, hh); else stage_chunk(v, buf, hh);
+              for (int g8 = 0; g8 < 4; ++g8) {
+                float x[8], sv[8];
+#pragma unroll
+                for (int k = 0; k < 8; ++k) x[k] = __uint_as_float(r[g8 * 8 + k]);
+                if (p.alpha != 1.f) {
+#pragma unroll
+                  for (int k = 0; k < 8; ++k) x[k] *= p.alpha;
+                }
+                if (has_bias) {
+                  const float4 b0 = lds_f4(sbias_a + (c * 32 + g8 * 8) * 4), b1 = lds_f4(sbias_a + (c * 32 + g8 * 8 + 4) * 4);
+                  x[0] += b0.x; x[1] += b0.y; x[2] += b0.z; x[3] += b0.w;
+                  x[4] += b1.x; x[5] += b1.y; x[6] += b1.z; x[7] += b1.w;
+                }
+                if (both) {
+#pragma unroll
+                  for (int k = 0; k < 8; ++k) gelu_tanh_both(x[k], x[k], sv[k]);
+                } else {
+#pragma unroll
+                  for (int k = 0; k < 8; ++k) { sv[k] = x[k]; if (p.epi & DEDLOC_EPI_GELU) x[k] = gelu_tanh(x[k]); }
+                }
+                const uint32_t off = (uint32_t)lane * 128 + (((uint32_t)(hh * 4 + g8) ^ ((uint32_t)lane & 7)) << 4);
+                sts_u4(stg + off, pack_bf16x2(sv[0], sv[1]), pack_bf16x2(sv[2], sv[3]), pack_bf16x2(sv[4], sv[5]),
+                       pack_bf16x2(sv[6], sv[7]));
+                keep[hh][g8 * 4 + 0] = pack_bf16x2(x[0], x[1]); keep[hh][g8 * 4 + 1] = pack_bf16x2(x[2], x[3]);
+                keep[hh][g8 * 4 + 2] = pack_bf16x2(x[4], x[5]); keep[hh][g8 * 4 + 3] = pack_bf16x2(x[6], x[7]);
               }
-              store_box(pass, pass == 0 ? &tmap_pre : &tmap_c);
             }
+            store_box(0, &tmap_pre);
+            if (lane == 0) tma_store_wait_read<1>();    // buffer 1's previous store (one box ago) is done
+            __syncwarp();
+#pragma unroll
+            for (int hh = 0; hh < 2; ++hh)
+#pragma unroll
+              for (int ch = 0; ch < 4; ++ch) {
+                const uint32_t off = (uint32_t)lane * 128 + (((uint32_t)(hh * 4 + ch) ^ ((uint32_t)lane & 7)) << 4);
+                sts_u4(stg + 4096 + off, keep[hh][4 * ch], keep[hh][4 * ch + 1], keep[hh][4 * ch + 2], keep[hh][4 * ch + 3]);
+              }
+            store_box(1, &tmap_c);
           } else {
 #pragma unroll
             for (int hh = 0; hh < 2; ++hh) {

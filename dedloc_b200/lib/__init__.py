@@ -70,6 +70,7 @@ class GemmArgs(C.Structure):
 
 # epilogue / mode constants (include/dedloc_b200.h)
 EPI_BIAS, EPI_BIAS_F32, EPI_GELU, EPI_DGELU, EPI_RESIDUAL, EPI_SAVE_PRE = 1, 2, 4, 8, 16, 32
+EPI_SAVE_DGELU, EPI_MUL_AUX = 64, 128
 OUT_BF16, OUT_F32, OUT_F32_ATOMIC = 0, 1, 2
 AR_MEAN, AR_LAMB, AR_LARS = 0, 1, 2
 TF_FROZEN, TF_NO_LARS, TF_ROWNORM128 = 1, 2, 4

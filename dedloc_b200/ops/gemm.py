@@ -29,6 +29,7 @@ def gemm(a: torch.Tensor, b: torch.Tensor, out: torch.Tensor, *, a_mn_major: boo
          b_mn_major: bool = False, bias: Optional[torch.Tensor] = None, gelu: bool = False,
          dgelu_aux: Optional[torch.Tensor] = None, residual: Optional[torch.Tensor] = None,
          pre_out: Optional[torch.Tensor] = None, accumulate: bool = False, alpha: float = 1.0,
+         save_dgelu: bool = False, mul_aux: Optional[torch.Tensor] = None,
          split_k: int = 1, block_n: int = 0, max_ctas: int = 0, cta_pair: int = 0) -> torch.Tensor:
     """out[M,N] = epilogue(A . B^T).
 
@@ -64,8 +65,15 @@ def gemm(a: torch.Tensor, b: torch.Tensor, out: torch.Tensor, *, a_mn_major: boo
     if residual is not None:
         epi |= native.EPI_RESIDUAL
         g.residual, g.ld_residual = residual.data_ptr(), residual.stride(0)
+    if mul_aux is not None:
+        assert dgelu_aux is None
+        epi |= native.EPI_MUL_AUX
+        g.aux_in, g.ld_aux = mul_aux.data_ptr(), mul_aux.stride(0)
     if pre_out is not None:
         epi |= native.EPI_SAVE_PRE
+        if save_dgelu:          # pre_out receives gelu'(pre) (one tanh for both), for a multiply-only backward
+            assert gelu
+            epi |= native.EPI_SAVE_DGELU
         g.pre_out, g.ld_pre = pre_out.data_ptr(), pre_out.stride(0)
     g.epilogue = epi
     if out.dtype == torch.bfloat16:
@@ -213,9 +221,11 @@ class _FFNFn(torch.autograd.Function):
             x2 = x2.contiguous()
         M, K = x2.shape
         I, N = w1.shape[0], w2.shape[0]
+        # the epilogue saves gelu'(pre) instead of pre: the backward epilogue is then a multiply (no tanh per element
+        # in an epilogue that already is the bottleneck of that GEMM)
         pre = torch.empty(M, I, dtype=x.dtype, device=x.device)
         h = torch.empty(M, I, dtype=x.dtype, device=x.device)
-        gemm(x2, w1, h, bias=b1, gelu=True, pre_out=pre)
+        gemm(x2, w1, h, bias=b1, gelu=True, pre_out=pre, save_dgelu=True)
         out = torch.empty(M, N, dtype=x.dtype, device=x.device)
         res2 = residual.reshape(M, N) if residual is not None else None
         gemm(h, w2, out, bias=b2, residual=res2)
@@ -235,7 +245,7 @@ class _FFNFn(torch.autograd.Function):
             dy2 = dy2.contiguous()
         sms = _sms(x2.device)
         dpre = torch.empty(M, I, dtype=x2.dtype, device=x2.device)
-        gemm(dy2, w2, dpre, b_mn_major=True, dgelu_aux=pre)                      # (dy W2) * gelu'(pre)
+        gemm(dy2, w2, dpre, b_mn_major=True, mul_aux=pre)                        # (dy W2) * gelu'(pre), saved in forward
 
         def grads2():
             gemm(dy2, h, g_w2, a_mn_major=True, b_mn_major=True, accumulate=True, split_k=pick_split_k(N, I, M, sms))

@@ -98,7 +98,9 @@ enum {
   DEDLOC_EPI_GELU = 4,       /* gelu_new(x) */
   DEDLOC_EPI_DGELU = 8,      /* x * gelu_new'(aux_in[m,n]) */
   DEDLOC_EPI_RESIDUAL = 16,  /* + residual[m,n] (bf16) */
-  DEDLOC_EPI_SAVE_PRE = 32   /* also store the pre-activation (after bias) to pre_out as bf16 */
+  DEDLOC_EPI_SAVE_PRE = 32,  /* also store the pre-activation (after bias) to pre_out as bf16 */
+  DEDLOC_EPI_SAVE_DGELU = 64,/* with GELU + SAVE_PRE: pre_out receives gelu_new'(pre) instead (shares the tanh) */
+  DEDLOC_EPI_MUL_AUX = 128   /* x * aux_in[m,n] (bf16): backward of an activation whose derivative was saved */
 };
 
 typedef struct DedlocGemmArgs {

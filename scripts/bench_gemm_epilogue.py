@@ -47,7 +47,9 @@ cases = {
     "ffn_down bias": lambda: gemm(h, w2, y, bias=b2),
     "ffn_down bias+residual": lambda: gemm(h, w2, y, bias=b2, residual=res),
     "ffn_down dgrad plain": lambda: gemm(dy, w2, dpre, b_mn_major=True),
+    "ffn_up bias+gelu+save_dgelu": lambda: gemm(x, w1, h, bias=b1, gelu=True, pre_out=pre, save_dgelu=True),
     "ffn_down dgrad * gelu'(pre)": lambda: gemm(dy, w2, dpre, b_mn_major=True, dgelu_aux=pre),
+    "ffn_down dgrad * saved": lambda: gemm(dy, w2, dpre, b_mn_major=True, mul_aux=pre),
     "ffn_down wgrad": lambda: gemm(dy, h, g2, a_mn_major=True, b_mn_major=True, accumulate=True, split_k=pick_split_k(1024, 4096, M, 148)),
     "ffn_up dgrad": lambda: gemm(dpre, w1, dx, b_mn_major=True),
     "ffn_up wgrad": lambda: gemm(dpre, x, g1, a_mn_major=True, b_mn_major=True, accumulate=True, split_k=pick_split_k(4096, 1024, M, 148)),

@@ -104,6 +104,25 @@ def test_gemm_epilogues(native):
     _check(out, base * gelu_new_grad(aux.float()), "dgelu")
     gemm(a, b, out, alpha=0.125)
     _check(out, base * 0.125, "alpha")
+    # derivative saved by the forward epilogue (one tanh for gelu and gelu'), multiply-only backward epilogue
+    dact = torch.empty_like(out)
+    for pair in (0, 1, 2):     # auto, 1-CTA, CTA pair
+        gemm(a, b, out, bias=bias, gelu=True, pre_out=dact, save_dgelu=True, cta_pair=pair)
+        _check(out, gelu_new(base + bias.float()), f"gelu with saved derivative (cta_pair={pair})")
+        _check(dact, gelu_new_grad(base + bias.float()), f"saved gelu' (cta_pair={pair})")
+        gemm(a, b, out, mul_aux=aux, cta_pair=pair)
+        _check(out, base * aux.float(), f"mul_aux (cta_pair={pair})")
+    # wide tile path of the CTA-pair kernel (coalesced row-operand prefetch needs full 128-column halves)
+    M2, N2 = 512, 512
+    a2, b2, aux2, res2 = _rand((M2, K), 11, 0.3), _rand((N2, K), 12, 0.3), _rand((M2, N2), 13, 1.0), _rand((M2, N2), 14, 1.0)
+    out2 = torch.empty(M2, N2, dtype=torch.bfloat16, device="cuda")
+    base2 = a2.float() @ b2.float().t()
+    gemm(a2, b2, out2, mul_aux=aux2, cta_pair=2)
+    _check(out2, base2 * aux2.float(), "mul_aux pair kernel")
+    gemm(a2, b2, out2, dgelu_aux=aux2, cta_pair=2)
+    _check(out2, base2 * gelu_new_grad(aux2.float()), "dgelu pair kernel")
+    gemm(a2, b2, out2, residual=res2, cta_pair=2)
+    _check(out2, base2 + res2.float(), "residual pair kernel")
 
 
 def test_gemm_wgrad_splitk_accumulate(native):
