@@ -163,7 +163,23 @@ __global__ void __launch_bounds__(256) colsum_acc_kernel(const __nv_bfloat16* __
   const int col0 = blockIdx.x * 256 + lane * 8;
   float acc[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
   if (col0 < N) {
-    for (int row = blockIdx.y * 8 + warp; row < M; row += gridDim.y * 8) {
+    // four rows in flight per warp: one 16-byte load per lane does not cover the HBM latency-bandwidth product
+    const int stride = gridDim.y * 8;
+    int row = blockIdx.y * 8 + warp;
+    for (; row + 3 * stride < M; row += 4 * stride) {
+      uint4 u[4];
+#pragma unroll
+      for (int k = 0; k < 4; ++k) u[k] = ld_stream_v4(dy + (size_t)(row + k * stride) * ld + col0);
+#pragma unroll
+      for (int k = 0; k < 4; ++k) {
+        float2 t;
+        t = unpack_bf16x2(u[k].x); acc[0] += t.x; acc[1] += t.y;
+        t = unpack_bf16x2(u[k].y); acc[2] += t.x; acc[3] += t.y;
+        t = unpack_bf16x2(u[k].z); acc[4] += t.x; acc[5] += t.y;
+        t = unpack_bf16x2(u[k].w); acc[6] += t.x; acc[7] += t.y;
+      }
+    }
+    for (; row < M; row += stride) {
       const uint4 u = ld_stream_v4(dy + (size_t)row * ld + col0);
       float2 t;
       t = unpack_bf16x2(u.x); acc[0] += t.x; acc[1] += t.y;

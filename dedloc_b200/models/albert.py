@@ -169,6 +169,14 @@ class AlbertAttention(nn.Module):
     def forward(self, x, attn_bias, impl: str, fused_qkv=None, key_mask=None):
         B, S, H = x.shape
         if fused_qkv is not None:
+            if (impl == "native" and self.head_dim == 64 and S % 128 == 0 and 128 <= S <= 512
+                    and not ((self.attn_dropout_p > 0 or self.out_dropout_p > 0) and self.training)
+                    and _native_ok(x, fused_qkv, impl) and _native_ok(x, self.dense, impl)):
+                # the whole sub-layer as one autograd node: QKV GEMM -> tcgen05 attention on the packed projection ->
+                # output GEMM (+ bias + residual); backward folds the residual-branch gradient into a GEMM epilogue
+                from ..ops.attention import attention_block
+
+                return _ln(attention_block(x, fused_qkv, self.dense, self.num_heads, key_mask), self.LayerNorm, impl)
             qkv = fused_linear(x, fused_qkv, impl)                        # [B,S,3H] in one GEMM
             if impl == "native" and self.head_dim == 64 and not (self.attn_dropout_p > 0 and self.training):
                 from ..ops import attention as native_attention

@@ -232,6 +232,8 @@ class _FFNFn(torch.autograd.Function):
         ctx.save_for_backward(x2, w1, w2, pre, h)
         ctx.grads = (g_w1, g_b1, g_w2, g_b2)
         ctx.has_res, ctx.x_shape = residual is not None, x.shape
+        # residual IS the input (ALBERT: FFN(a) + a): its gradient is added in the epilogue of the last dgrad GEMM
+        ctx.res_is_x = residual is not None and residual.data_ptr() == x.data_ptr() and residual.shape == x.shape
         return out.view(*x.shape[:-1], N)
 
     @staticmethod
@@ -253,14 +255,15 @@ class _FFNFn(torch.autograd.Function):
 
         _run_wgrad(x2.device, grads2, dy2, h)
         dx = torch.empty(M, K, dtype=x2.dtype, device=x2.device)
-        gemm(dpre, w1, dx, b_mn_major=True)
+        gemm(dpre, w1, dx, b_mn_major=True, residual=dy2 if ctx.res_is_x else None)
 
         def grads1():
             gemm(dpre, x2, g_w1, a_mn_major=True, b_mn_major=True, accumulate=True, split_k=pick_split_k(I, K, M, sms))
             _bias_grad(dpre, g_b1)
 
         _run_wgrad(x2.device, grads1, dpre, x2)
-        return dx.view(ctx.x_shape), None, None, None, None, (dy if ctx.has_res else None), None, None, None, None
+        dres = None if ctx.res_is_x else (dy if ctx.has_res else None)
+        return dx.view(ctx.x_shape), None, None, None, None, dres, None, None, None, None
 
 
 def ffn(x, lin1, lin2, residual=None):
