@@ -51,7 +51,7 @@ __device__ __forceinline__ float ex2f_b(float x) {
 template <int NBLK>
 __global__ void __launch_bounds__(kAbThreads, 1)
 attention_bwd_kernel(const __grid_constant__ CUtensorMap tmap_qkv, const __grid_constant__ CUtensorMap tmap_do,
-                     const __grid_constant__ AttBwdParams p) {
+                     const __grid_constant__ CUtensorMap tmap_dqkv, const __grid_constant__ AttBwdParams p) {
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   uint8_t* sK = smem;                               // 2 stages
@@ -73,7 +73,8 @@ attention_bwd_kernel(const __grid_constant__ CUtensorMap tmap_qkv, const __grid_
   uint64_t* dkv_empty = bars + 17;
   uint64_t* vec_full = bars + 18;   // [2]
   uint64_t* vec_empty = bars + 20;  // [2]
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 22);
+  uint64_t* stage_free = bars + 22; // [2] per half-group: the dK / dV TMA store has read its staging tile
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 24);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   constexpr int nblk = NBLK;                      // key / query blocks of 128 (compile time: no integer divisions)
@@ -83,7 +84,7 @@ attention_bwd_kernel(const __grid_constant__ CUtensorMap tmap_qkv, const __grid_
   constexpr int steps_per_bh = nblk * nblk;
   const int T = my_bh * steps_per_bh;                                                     // steps of this CTA
 
-  if (warp == 0 && lane == 0) { tma_prefetch_desc(&tmap_qkv); tma_prefetch_desc(&tmap_do); }
+  if (warp == 0 && lane == 0) { tma_prefetch_desc(&tmap_qkv); tma_prefetch_desc(&tmap_do); tma_prefetch_desc(&tmap_dqkv); }
   if (warp == 1 && lane == 0) {
     for (int i = 0; i < 2; ++i) {
       mbar_init(&kv_full[i], 1); mbar_init(&kv_empty[i], 1);
@@ -91,6 +92,7 @@ attention_bwd_kernel(const __grid_constant__ CUtensorMap tmap_qkv, const __grid_
       mbar_init(&s_full[i], 1); mbar_init(&p_full[i], 4);
       mbar_init(&vec_full[i], 1); mbar_init(&vec_empty[i], 8);
       mbar_init(&dq_full[i], 1); mbar_init(&dq_empty[i], 8);
+      mbar_init(&stage_free[i], 1);
     }
     mbar_init(dkv_full, 1); mbar_init(dkv_empty, 8);
     mbar_fence_init();
@@ -316,14 +318,16 @@ attention_bwd_kernel(const __grid_constant__ CUtensorMap tmap_qkv, const __grid_
                          pack_bf16x2(v[q + 4], v[q + 5]), pack_bf16x2(v[q + 6], v[q + 7]));
       }
     };
-    // dV_j (half-group a) / dK_j (half-group b) of key `row` after the last query block of key block jc
+    // dV_j (half-group a) / dK_j (half-group b) after the last query block of key block jc: tensor memory -> bf16 ->
+    // this half-group's own half of the dS^T buffer of the step that just finished (free: its MMA 3 has retired and
+    // nobody but this half-group writes it) -> ONE TMA store of the [128 keys x 64] tile. Row-per-thread global
+    // stores touch 32 lines per instruction and kept the tensor core waiting for dkv_empty at every key block.
     auto drain_dkv = [&](int jc) {
       const int bh = blockIdx.x + (jc / nblk) * gridDim.x;
       const int b = bh / H, h = bh % H, j = jc % nblk;
+      const int t_last = jc * nblk + nblk - 1;
       mbar_wait(dkv_full, jc & 1);
       tc_fence_after();
-      const size_t tok = (size_t)(b * S + j * kAbBlk + row);
-      __nv_bfloat16* dst = p.dqkv + ((tok * 3 + (hf == 0 ? 2 : 1)) * H + h) * kAbD;
       const uint32_t tacc = (hf == 0 ? t_dV : t_dK) + lane_off;
       uint32_t r0[32], r1[32];
       tmem_ld_32x32b_x32(tacc, r0);
@@ -332,20 +336,30 @@ attention_bwd_kernel(const __grid_constant__ CUtensorMap tmap_qkv, const __grid_
       tc_fence_before();
       __syncwarp();
       if (lane == 0) mbar_arrive(dkv_empty);
+      uint8_t* stage = sdS + ((t_last & 1) * 2 + hf) * kAbTile;
+      const uint32_t st_row = smem_u32(stage) + row * 128;
 #pragma unroll
-      for (int q = 0; q < 32; q += 8)
-        *reinterpret_cast<uint4*>(dst + q) =
-            make_uint4(pack_bf16x2(__uint_as_float(r0[q]), __uint_as_float(r0[q + 1])),
-                       pack_bf16x2(__uint_as_float(r0[q + 2]), __uint_as_float(r0[q + 3])),
-                       pack_bf16x2(__uint_as_float(r0[q + 4]), __uint_as_float(r0[q + 5])),
-                       pack_bf16x2(__uint_as_float(r0[q + 6]), __uint_as_float(r0[q + 7])));
-#pragma unroll
-      for (int q = 0; q < 32; q += 8)
-        *reinterpret_cast<uint4*>(dst + 32 + q) =
-            make_uint4(pack_bf16x2(__uint_as_float(r1[q]), __uint_as_float(r1[q + 1])),
-                       pack_bf16x2(__uint_as_float(r1[q + 2]), __uint_as_float(r1[q + 3])),
-                       pack_bf16x2(__uint_as_float(r1[q + 4]), __uint_as_float(r1[q + 5])),
-                       pack_bf16x2(__uint_as_float(r1[q + 6]), __uint_as_float(r1[q + 7])));
+      for (int ch = 0; ch < 4; ++ch) {
+        const int q = ch * 8;
+        sts_u4(st_row + (((uint32_t)ch ^ ((uint32_t)row & 7)) << 4),
+               pack_bf16x2(__uint_as_float(r0[q]), __uint_as_float(r0[q + 1])),
+               pack_bf16x2(__uint_as_float(r0[q + 2]), __uint_as_float(r0[q + 3])),
+               pack_bf16x2(__uint_as_float(r0[q + 4]), __uint_as_float(r0[q + 5])),
+               pack_bf16x2(__uint_as_float(r0[q + 6]), __uint_as_float(r0[q + 7])));
+        sts_u4(st_row + (((uint32_t)(ch + 4) ^ ((uint32_t)row & 7)) << 4),
+               pack_bf16x2(__uint_as_float(r1[q]), __uint_as_float(r1[q + 1])),
+               pack_bf16x2(__uint_as_float(r1[q + 2]), __uint_as_float(r1[q + 3])),
+               pack_bf16x2(__uint_as_float(r1[q + 4]), __uint_as_float(r1[q + 5])),
+               pack_bf16x2(__uint_as_float(r1[q + 6]), __uint_as_float(r1[q + 7])));
+      }
+      fence_proxy_async_smem();
+      asm volatile("bar.sync %0, 128;" ::"r"(1 + hf) : "memory");
+      if (quad == 0 && lane == 0) {
+        tma_store_2d(&tmap_dqkv, stage, ((hf == 0 ? 2 : 1) * H + h) * kAbD, b * S + j * kAbBlk);
+        tma_store_commit();
+        tma_store_wait_read<0>();
+        mbar_arrive(&stage_free[hf]);              // compute_half two steps later overwrites this tile
+      }
     };
     // P^T and dS^T of key `row` against the 64 queries of this half
     auto compute_half = [&](int t) {
@@ -356,6 +370,7 @@ attention_bwd_kernel(const __grid_constant__ CUtensorMap tmap_qkv, const __grid_
       if (t % steps_per_bh == 0) mbar_wait(&vec_full[st], (bc >> 1) & 1);
       const bool kok = lds_f1(kok_a) != 0.f;
       const uint32_t ds_row = smem_u32(sdS) + ((t & 1) * 2 + hf) * kAbTile + row * 128;
+      if (t >= 2 && (t - 2) % nblk == nblk - 1) mbar_wait(&stage_free[hf], ((t - 2) / nblk) & 1);
       mbar_wait(&s_full[hf], t & 1);
       tc_fence_after();
 #pragma unroll
@@ -406,8 +421,8 @@ attention_bwd_kernel(const __grid_constant__ CUtensorMap tmap_qkv, const __grid_
     for (int t = 0; t < T; ++t) {
       compute_half(t);
       if (t > 0) {
+        if (t % nblk == 0) drain_dkv(t / nblk - 1);   // first: the tensor core waits for these accumulators
         drain_dq(t - 1);
-        if (t % nblk == 0) drain_dkv(t / nblk - 1);
       }
       prefetch_dq(t);
     }
@@ -415,6 +430,7 @@ attention_bwd_kernel(const __grid_constant__ CUtensorMap tmap_qkv, const __grid_
       drain_dq(T - 1);
       drain_dkv(T / nblk - 1);
     }
+    if (quad == 0 && lane == 0) tma_store_wait<0>();
   }
 
   tc_fence_before();
@@ -439,10 +455,12 @@ extern "C" int dedloc_attention_bwd(const void* qkv, const void* out, const void
   DEDLOC_REQUIRE(S % 128 == 0 && S >= 128 && S <= kAbMaxS, "attention: S (%d) must be a multiple of 128 up to %d", S, kAbMaxS);
   DEDLOC_REQUIRE(scratch != nullptr, "attention_bwd: scratch of dedloc_attention_bwd_scratch_floats(S) floats is required");
   { int rc0 = bind_context_for_driver_calls(); if (rc0) return rc0; }
-  CUtensorMap tq, td;
+  CUtensorMap tq, td, tg;
   int rc = make_tmap_2d_16bit(&tq, qkv, (long long)B * S, 3LL * H * D, 3LL * H * D, 64, 128, 1);
   if (rc) return rc;
   rc = make_tmap_2d_16bit(&td, dout, (long long)B * S, (long long)H * D, (long long)H * D, 64, 128, 1);
+  if (rc) return rc;
+  rc = make_tmap_2d_16bit(&tg, dqkv, (long long)B * S, 3LL * H * D, 3LL * H * D, 64, 128, 1);
   if (rc) return rc;
   static int sms = 0;
   if (sms == 0) {
@@ -466,10 +484,10 @@ extern "C" int dedloc_attention_bwd(const void* qkv, const void* out, const void
   p.dq_scratch = scratch;
   const int grid = B * H < sms ? B * H : sms;
   switch (S / kAbBlk) {
-    case 1: attention_bwd_kernel<1><<<grid, kAbThreads, kAbSmem, (cudaStream_t)stream>>>(tq, td, p); break;
-    case 2: attention_bwd_kernel<2><<<grid, kAbThreads, kAbSmem, (cudaStream_t)stream>>>(tq, td, p); break;
-    case 3: attention_bwd_kernel<3><<<grid, kAbThreads, kAbSmem, (cudaStream_t)stream>>>(tq, td, p); break;
-    default: attention_bwd_kernel<4><<<grid, kAbThreads, kAbSmem, (cudaStream_t)stream>>>(tq, td, p); break;
+    case 1: attention_bwd_kernel<1><<<grid, kAbThreads, kAbSmem, (cudaStream_t)stream>>>(tq, td, tg, p); break;
+    case 2: attention_bwd_kernel<2><<<grid, kAbThreads, kAbSmem, (cudaStream_t)stream>>>(tq, td, tg, p); break;
+    case 3: attention_bwd_kernel<3><<<grid, kAbThreads, kAbSmem, (cudaStream_t)stream>>>(tq, td, tg, p); break;
+    default: attention_bwd_kernel<4><<<grid, kAbThreads, kAbSmem, (cudaStream_t)stream>>>(tq, td, tg, p); break;
   }
   count_launch();
   DEDLOC_CUDA_CHECK(cudaGetLastError());
