@@ -253,6 +253,7 @@ class _FusedQKV:
         self.out_features = 3 * attn.query.out_features
         with torch.no_grad():
             self.weight = torch.cat([attn.query.weight, attn.key.weight, attn.value.weight], dim=0)
+            self.weight.weight_t = self.weight.t().contiguous()     # K-major operand for the dgrad GEMM
             self.bias = torch.cat([attn.query.bias, attn.key.bias, attn.value.bias], dim=0)
         dev = self.weight.device
         self.weight.main_grad = torch.zeros(self.weight.shape, dtype=torch.float32, device=dev)
@@ -293,9 +294,15 @@ class AlbertModel(nn.Module):
                     key = id(layer)
                     if key not in fused:
                         fused[key] = _FusedQKV(layer.attention)
+                        with torch.no_grad():   # K-major W^T for the dgrad GEMMs, refreshed once per forward
+                            for lin in (layer.attention.dense, layer.ffn, layer.ffn_output):
+                                lin.weight.weight_t = lin.weight.detach().t().contiguous()
                         if torch.is_grad_enabled():
                             pending_flush.append(fused[key])
                     fq = fused[key]
+                else:
+                    for lin in (layer.attention.dense, layer.ffn, layer.ffn_output):
+                        lin.weight.weight_t = None          # never leave a stale transposed copy behind
                 x = layer(x, attn_bias, impl, fq, attention_mask)
         pooled = torch.tanh(fused_linear(x[:, 0], self.pooler, "torch"))
         return x, pooled

@@ -104,11 +104,12 @@ class _AttentionBlockFn(torch.autograd.Function):
                               mask_u8 if mask_u8 is not None else torch.empty(0, device=x.device))
         ctx.has_mask, ctx.num_heads, ctx.shape = mask_u8 is not None, num_heads, (B, S, H)
         ctx.grads = (g_wqkv, g_bqkv, g_wo, g_bo)
+        ctx.wqkv_t, ctx.wo_t = getattr(w_qkv, "weight_t", None), getattr(w_o, "weight_t", None)
         return y.view(B, S, -1)
 
     @staticmethod
     def backward(ctx, dy):
-        from .gemm import _bias_grad, _run_wgrad, _sms, gemm, pick_split_k
+        from .gemm import _bias_grad, _run_wgrad, _sms, dgrad, gemm, pick_split_k
 
         x2, w_qkv, w_o, qkv, att, lse, mask_u8 = ctx.saved_tensors
         g_wqkv, g_bqkv, g_wo, g_bo = ctx.grads
@@ -120,7 +121,7 @@ class _AttentionBlockFn(torch.autograd.Function):
             dy2 = dy2.contiguous()
         att2 = att.view(M, -1)
         datt = torch.empty_like(att2)
-        gemm(dy2, w_o, datt, b_mn_major=True)
+        dgrad(dy2, w_o, ctx.wo_t, datt)
 
         def grads_o():
             gemm(dy2, att2, g_wo, a_mn_major=True, b_mn_major=True, accumulate=True,
@@ -131,7 +132,7 @@ class _AttentionBlockFn(torch.autograd.Function):
         dqkv = attention_bwd(qkv.view(B, S, -1), att, datt.view(B, S, -1), lse, ctx.num_heads,
                              mask_u8 if ctx.has_mask else None).view(M, -1)
         dx = torch.empty_like(x2)
-        gemm(dqkv, w_qkv, dx, b_mn_major=True, residual=dy2)     # + the gradient of the residual branch
+        dgrad(dqkv, w_qkv, ctx.wqkv_t, dx, residual=dy2)         # + the gradient of the residual branch
 
         def grads_qkv():
             gemm(dqkv, x2, g_wqkv, a_mn_major=True, b_mn_major=True, accumulate=True,

@@ -105,6 +105,15 @@ def pick_split_k(m_out: int, n_out: int, k_red: int, sms: int, block_n: int = 25
     return best_s
 
 
+def dgrad(dy2: torch.Tensor, weight: torch.Tensor, weight_t: Optional[torch.Tensor], dx: torch.Tensor, **epilogue):
+    """dx[M, in] = dy[M, out] . W[out, in] (+ epilogue). With a K-major copy of W^T ([in, out], refreshed by the model
+    once per forward -- cheap for ALBERT's shared layer) the B operand is K-major; MN-major operands cost 6-13 % each in
+    the tcgen05 kernel (profiles/README.md)."""
+    if weight_t is not None:
+        return gemm(dy2, weight_t, dx, **epilogue)
+    return gemm(dy2, weight, dx, b_mn_major=True, **epilogue)
+
+
 # ---------------------------------------------------------------- weight / bias gradients off the critical path
 # Nothing downstream of a layer's backward consumes dW / db before the optimizer, so (opt-in) they are launched on a
 # low-priority side stream: the bandwidth-bound kernels of the critical path (LayerNorm backward, bias-gradient
@@ -168,6 +177,7 @@ class _LinearFn(torch.autograd.Function):
         ctx.has_bias = bias is not None
         ctx.has_res = residual is not None
         ctx.wgrad_out, ctx.bgrad_out = wgrad_out, bgrad_out
+        ctx.weight_t = getattr(weight, "weight_t", None)
         ctx.x_shape = x.shape
         return out.view(*x.shape[:-1], N)
 
@@ -186,7 +196,7 @@ class _LinearFn(torch.autograd.Function):
             dy2 = dgelu_mul(dy2, pre)
         # dgrad: dx[M,K] = dy[M,N] . W[N,K]  -> B operand is W stored [N,K] = [K_red, N_out] MN-major
         dx = torch.empty(M, K, dtype=x2.dtype, device=x2.device)
-        gemm(dy2, weight, dx, b_mn_major=True)
+        dgrad(dy2, weight, ctx.weight_t, dx)
         # wgrad: dW[N,K] += dy^T[N,M] . x[M,K]  -> both operands MN-major, reduction over tokens
         wg, bg, has_bias = ctx.wgrad_out, ctx.bgrad_out, ctx.has_bias
         sk = pick_split_k(N, K, M, _sms(x2.device))
@@ -231,6 +241,7 @@ class _FFNFn(torch.autograd.Function):
         gemm(h, w2, out, bias=b2, residual=res2)
         ctx.save_for_backward(x2, w1, w2, pre, h)
         ctx.grads = (g_w1, g_b1, g_w2, g_b2)
+        ctx.w1t, ctx.w2t = getattr(w1, "weight_t", None), getattr(w2, "weight_t", None)
         ctx.has_res, ctx.x_shape = residual is not None, x.shape
         # residual IS the input (ALBERT: FFN(a) + a): its gradient is added in the epilogue of the last dgrad GEMM
         ctx.res_is_x = residual is not None and residual.data_ptr() == x.data_ptr() and residual.shape == x.shape
@@ -247,7 +258,7 @@ class _FFNFn(torch.autograd.Function):
             dy2 = dy2.contiguous()
         sms = _sms(x2.device)
         dpre = torch.empty(M, I, dtype=x2.dtype, device=x2.device)
-        gemm(dy2, w2, dpre, b_mn_major=True, mul_aux=pre)                        # (dy W2) * gelu'(pre), saved in forward
+        dgrad(dy2, w2, ctx.w2t, dpre, mul_aux=pre)                               # (dy W2) * gelu'(pre), saved in forward
 
         def grads2():
             gemm(dy2, h, g_w2, a_mn_major=True, b_mn_major=True, accumulate=True, split_k=pick_split_k(N, I, M, sms))
@@ -255,7 +266,7 @@ class _FFNFn(torch.autograd.Function):
 
         _run_wgrad(x2.device, grads2, dy2, h)
         dx = torch.empty(M, K, dtype=x2.dtype, device=x2.device)
-        gemm(dpre, w1, dx, b_mn_major=True, residual=dy2 if ctx.res_is_x else None)
+        dgrad(dpre, w1, ctx.w1t, dx, residual=dy2 if ctx.res_is_x else None)
 
         def grads1():
             gemm(dpre, x2, g_w1, a_mn_major=True, b_mn_major=True, accumulate=True, split_k=pick_split_k(I, K, M, sms))
