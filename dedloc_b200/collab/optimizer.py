@@ -366,6 +366,11 @@ class CollaborativeOptimizer:
 
     def _sync_scheduler(self) -> None:
         if self.scheduler is not None:
+            # the update itself ran inside the fused all-reduce kernel (or the generic step above), not through
+            # torch's patched Optimizer.step: tell the scheduler's order check that the optimizer did step
+            sched_opt = getattr(self.scheduler, "optimizer", None)
+            if sched_opt is not None:
+                sched_opt._opt_called = True
             while getattr(self.scheduler, "_step_count", 0) <= self.local_step:
                 self.scheduler.step()
 

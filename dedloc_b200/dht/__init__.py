@@ -76,6 +76,16 @@ class DHT:
                 loop.run_until_complete(self._node.shutdown())
             except Exception:
                 pass
+            # connection handlers / pumps still parked on a socket read: cancel and reap them before closing the loop
+            # (otherwise asyncio reports "Task was destroyed but it is pending" for each of them at interpreter exit)
+            try:
+                pending = [t for t in asyncio.all_tasks(loop) if not t.done()]
+                for t in pending:
+                    t.cancel()
+                if pending:
+                    loop.run_until_complete(asyncio.gather(*pending, return_exceptions=True))
+            except Exception:
+                pass
             loop.close()
 
     def shutdown(self) -> None:
