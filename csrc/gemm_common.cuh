@@ -16,6 +16,7 @@ struct GemmKernelParams {
   int epi;              // DEDLOC_EPI_* flags
   int out_kind;         // 0 bf16 store, 1 fp32 store, 2 fp32 atomic add
   int fmt;              // 1 = bf16 inputs, 0 = fp16 inputs
+  int a_mn3d, b_mn3d;   // MN-major operand described by a 3-D tensor map (one TMA per stage instead of one per 64 columns)
   float alpha;
   void* C;              // [M, ldc]
   long long ldc;
@@ -190,5 +191,9 @@ __device__ __forceinline__ void gemm_epilogue_32cols(const GemmKernelParams& p, 
 int make_tmap_2d_16bit(CUtensorMap* map, const void* base, long long rows, long long cols, long long ld,
                        int box_cols, int box_rows, int is_bf16);
 int bind_context_for_driver_calls();
+// MN-major operand [k_rows, mn_cols] (mn contiguous, mn_cols % 64 == 0) as (64 elements, k rows, mn_cols / 64 groups):
+// one box of (64, box_k, groups) lands in shared memory as `groups` consecutive [box_k x 128 B] swizzled tiles.
+int make_tmap_mn_3d_16bit(CUtensorMap* map, const void* base, long long k_rows, long long mn_cols, long long ld,
+                          int box_k, int groups, int is_bf16);
 
 }  // namespace dedloc

@@ -236,6 +236,29 @@ int make_tmap_2d_16bit(CUtensorMap* map, const void* base, long long rows, long 
   return 0;
 }
 
+int make_tmap_mn_3d_16bit(CUtensorMap* map, const void* base, long long k_rows, long long mn_cols, long long ld,
+                          int box_k, int groups, int is_bf16) {
+  EncodeTiledFn fn = get_encode_fn();
+  if (!fn) {
+    set_last_error("cuTensorMapEncodeTiled driver entry point not available");
+    return DEDLOC_EUNSUPPORTED;
+  }
+  cuuint64_t gdim[3] = {64, (cuuint64_t)k_rows, (cuuint64_t)(mn_cols / 64)};
+  cuuint64_t gstride[2] = {(cuuint64_t)ld * 2, 128};
+  cuuint32_t box[3] = {64, (cuuint32_t)box_k, (cuuint32_t)groups};
+  cuuint32_t estr[3] = {1, 1, 1};
+  CUresult r = fn(map, is_bf16 ? CU_TENSOR_MAP_DATA_TYPE_BFLOAT16 : CU_TENSOR_MAP_DATA_TYPE_FLOAT16, 3,
+                  const_cast<void*>(base), gdim, gstride, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                  CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                  CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) {
+    set_last_error("cuTensorMapEncodeTiled (3-D MN-major) failed with %d (base %p k %lld mn %lld ld %lld)", (int)r, base,
+                   k_rows, mn_cols, ld);
+    return DEDLOC_EINVAL;
+  }
+  return 0;
+}
+
 // cuTensorMapEncodeTiled is a driver call: it needs a context bound to THIS thread (autograd's backward threads
 // have none until a runtime call binds the primary context).
 int bind_context_for_driver_calls() {
@@ -256,6 +279,7 @@ static int launch_gemm(const DedlocGemmArgs& g, cudaStream_t st) {
   kp.M = g.M; kp.N = g.N; kp.K = g.K;
   kp.a_mn = g.a_mn_major; kp.b_mn = g.b_mn_major;
   kp.epi = g.epilogue; kp.out_kind = g.out_kind; kp.fmt = g.is_fp16 ? 0 : 1;
+  kp.a_mn3d = 0; kp.b_mn3d = 0;
   kp.alpha = g.alpha;
   kp.C = g.C; kp.ldc = g.ldc;
   kp.bias = g.bias; kp.residual = g.residual; kp.ld_res = g.ld_residual;
