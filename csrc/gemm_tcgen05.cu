@@ -56,7 +56,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_con
 
   const int m_tiles = (p.M + BM - 1) / BM;
   const int n_tiles = (p.N + BN - 1) / BN;
-  const int kb_total = p.K / BK;
+  const int kb_total = (p.K + BK - 1) / BK;   // a K tail is zero-filled by TMA (out-of-bounds box elements)
   const int total_tiles = m_tiles * n_tiles * p.splits;
 
   if (warp == 0 && lane == 0) {
@@ -284,7 +284,7 @@ static int launch_gemm(const DedlocGemmArgs& g, cudaStream_t st) {
   kp.C = g.C; kp.ldc = g.ldc;
   kp.bias = g.bias; kp.residual = g.residual; kp.ld_res = g.ld_residual;
   kp.aux_in = g.aux_in; kp.ld_aux = g.ld_aux; kp.pre_out = g.pre_out; kp.ld_pre = g.ld_pre;
-  const int kb_total = g.K / BK;
+  const int kb_total = (g.K + BK - 1) / BK;
   int splits = g.split_k < 1 ? 1 : g.split_k;
   if (splits > kb_total) splits = kb_total;
   int kb_per = (kb_total + splits - 1) / splits;
@@ -331,7 +331,7 @@ using namespace dedloc;
 extern "C" int dedloc_gemm(const DedlocGemmArgs* gp, void* stream) {
   const DedlocGemmArgs& g = *gp;
   DEDLOC_REQUIRE(g.M > 0 && g.N > 0 && g.K > 0, "gemm: empty problem %dx%dx%d", g.M, g.N, g.K);
-  DEDLOC_REQUIRE(g.K % BK == 0, "gemm: K (%d) must be a multiple of %d", g.K, BK);
+  DEDLOC_REQUIRE(g.K % 8 == 0, "gemm: K (%d) must be a multiple of 8 (16-byte rows); tails of the 64-wide K block are zero-filled", g.K);
   DEDLOC_REQUIRE(g.N % 8 == 0, "gemm: N (%d) must be a multiple of 8", g.N);
   DEDLOC_REQUIRE(g.lda % 8 == 0 && g.ldb % 8 == 0, "gemm: lda/ldb must be multiples of 8 elements (16 B)");
   DEDLOC_REQUIRE(((uintptr_t)g.A & 15) == 0 && ((uintptr_t)g.B & 15) == 0 && ((uintptr_t)g.C & 15) == 0,

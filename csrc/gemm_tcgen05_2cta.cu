@@ -105,7 +105,7 @@ gemm_tcgen05_2cta_kernel(const __grid_constant__ CUtensorMap tmap_a, const __gri
 
   const int m_tiles = (p.M + 2 * k2BM - 1) / (2 * k2BM);
   const int n_tiles = (p.N + k2BN - 1) / k2BN;
-  const int kb_total = p.K / k2BK;
+  const int kb_total = (p.K + k2BK - 1) / k2BK;   // a K tail is zero-filled by TMA (out-of-bounds box elements)
   const int total_tiles = m_tiles * n_tiles * p.splits;
 
   if (warp == 0 && lane == 0) {
@@ -505,7 +505,7 @@ int launch_gemm_2cta(const DedlocGemmArgs& g, cudaStream_t st) {
   kp.C = g.C; kp.ldc = g.ldc;
   kp.bias = g.bias; kp.residual = g.residual; kp.ld_res = g.ld_residual;
   kp.aux_in = g.aux_in; kp.ld_aux = g.ld_aux; kp.pre_out = g.pre_out; kp.ld_pre = g.ld_pre;
-  const int kb_total = g.K / k2BK;
+  const int kb_total = (g.K + k2BK - 1) / k2BK;
   int splits = g.split_k < 1 ? 1 : g.split_k;
   if (splits > kb_total) splits = kb_total;
   const int kb_per = (kb_total + splits - 1) / splits;

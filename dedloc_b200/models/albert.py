@@ -416,7 +416,18 @@ class AlbertForPreTraining(nn.Module):
             sel_labels = flat_labels[order]
             sel_valid = is_masked[order]
             h = self.predictions.hidden(seq.reshape(B * S, H)[order], self.impl)
-            logits = F.linear(h, dec_w, self.predictions.bias)
+            dec_b = self.predictions.bias
+            if (self.impl == "native" and h.is_cuda and h.dtype == torch.bfloat16 and h.shape[0] % 64 == 0
+                    and dec_w.shape[1] % 64 == 0 and dec_w.shape[0] % 8 == 0 and _main_grad(dec_w) is not None
+                    and _main_grad(dec_b) is not None):
+                # vocabulary projection on the tcgen05 GEMM as well (tied to the word embeddings: the weight gradient
+                # accumulates into the embedding's fp32 main_grad; the dgrad reduces over V = 30000, whose tail of the
+                # 64-wide K block is zero-filled by TMA)
+                from ..ops.gemm import linear as native_linear
+
+                logits = native_linear(h, dec_w, dec_b, wgrad_out=dec_w.main_grad, bgrad_out=dec_b.main_grad)
+            else:
+                logits = F.linear(h, dec_w, dec_b)
             if self.impl == "native" and _ce.supported(logits):
                 # one pass for loss + log-sum-exp, one for the bf16 gradient: no fp32 copy of [cap, vocab]
                 per_tok = _ce.cross_entropy_rows(logits, sel_labels.clamp_min(0))

@@ -175,4 +175,24 @@ def test_gemm_rejects_bad_arguments(native):
     a, b = _rand((128, 72), 1), _rand((128, 72), 2)
     out = torch.empty(128, 128, dtype=torch.bfloat16, device="cuda")
     with pytest.raises(NativeError):
-        gemm(a, b, out)  # K not a multiple of 64
+        gemm(a[:, :68], b[:, :68], out)  # K not a multiple of 8 (rows of the K tail are not 16-byte multiples)
+
+
+def test_gemm_k_tail_is_zero_filled(native):
+    """K need not be a multiple of the 64-wide K block: TMA zero-fills the out-of-bounds part of the last box (the
+    vocabulary reduction of the MLM decoder's dgrad has K = 30000)."""
+    from dedloc_b200.ops.gemm import gemm
+
+    for pair in (1, 2):
+        M, N, K = 512, 384, 200
+        a, b = _rand((M, K), 21, 0.3), _rand((N, K), 22, 0.3)
+        out = torch.empty(M, N, dtype=torch.bfloat16, device="cuda")
+        gemm(a, b, out, cta_pair=pair)
+        _check(out, a.float() @ b.float().t(), f"K tail, K-major (cta_pair={pair})")
+        bt = b.t().contiguous()          # [K, N]
+        gemm(a, bt, out, b_mn_major=True, cta_pair=pair)
+        _check(out, a.float() @ b.float().t(), f"K tail, MN-major B (cta_pair={pair})")
+        at = a.t().contiguous()          # [K, M]
+        wg = torch.zeros(M, N, dtype=torch.float32, device="cuda")
+        gemm(at, bt, wg, a_mn_major=True, b_mn_major=True, accumulate=True, split_k=2, cta_pair=pair)
+        _check(wg, a.float() @ b.float().t(), f"K tail, both MN-major split-K (cta_pair={pair})", rtol=2e-2, atol=2e-2)
