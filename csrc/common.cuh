@@ -246,40 +246,8 @@ __device__ __forceinline__ void umma_f16_ts(uint32_t tmem_d, uint32_t tmem_a, ui
       : "memory");
 }
 // Variants for issue-bound kernels (many small MMAs): the descriptor is passed as a 32-bit low word + a shared high
-// word, and the instruction is predicated on `leader` instead of sitting in a divergent branch, which keeps the
-// operands in uniform registers.
-__device__ __forceinline__ void umma_f16_ss_lo(uint32_t tmem_d, uint32_t a_lo, uint32_t b_lo, uint32_t hi,
-                                               uint32_t idesc, uint32_t accumulate, uint32_t leader) {
-  asm volatile(
-      "{\n\t.reg .pred p, q;\n\t.reg .b64 da, db;\n\t"
-      "setp.ne.b32 p, %5, 0;\n\t"
-      "setp.ne.b32 q, %6, 0;\n\t"
-      "mov.b64 da, {%1, %3};\n\t"
-      "mov.b64 db, {%2, %3};\n\t"
-      "@q tcgen05.mma.cta_group::1.kind::f16 [%0], da, db, %4, p;\n\t}" ::"r"(tmem_d),
-      "r"(a_lo), "r"(b_lo), "r"(hi), "r"(idesc), "r"(accumulate), "r"(leader)
-      : "memory");
-}
-__device__ __forceinline__ void umma_f16_ts_lo(uint32_t tmem_d, uint32_t tmem_a, uint32_t b_lo, uint32_t hi,
-                                               uint32_t idesc, uint32_t accumulate, uint32_t leader) {
-  asm volatile(
-      "{\n\t.reg .pred p, q;\n\t.reg .b64 db;\n\t"
-      "setp.ne.b32 p, %5, 0;\n\t"
-      "setp.ne.b32 q, %6, 0;\n\t"
-      "mov.b64 db, {%2, %3};\n\t"
-      "@q tcgen05.mma.cta_group::1.kind::f16 [%0], [%1], db, %4, p;\n\t}" ::"r"(tmem_d),
-      "r"(tmem_a), "r"(b_lo), "r"(hi), "r"(idesc), "r"(accumulate), "r"(leader)
-      : "memory");
-}
-__device__ __forceinline__ void umma_commit_pred(uint64_t* bar, uint32_t leader) {
-  asm volatile(
-      "{\n\t.reg .pred q;\n\t"
-      "setp.ne.b32 q, %1, 0;\n\t"
-      "@q tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];\n\t}" ::"r"(smem_u32(bar)),
-      "r"(leader)
-      : "memory");
-}
-// Same, unpredicated: for use inside `if (elect_one())`, which the assembler recognises as a single-thread region.
+// word (SBO / version / swizzle are the same for every operand of a kernel), for use inside `if (elect_one())`, which
+// the assembler recognises as a single-thread region (operands stay in uniform registers, back-to-back UTCHMMA).
 __device__ __forceinline__ void umma_f16_ss_lohi(uint32_t tmem_d, uint32_t a_lo, uint32_t b_lo, uint32_t hi,
                                                  uint32_t idesc, uint32_t accumulate) {
   asm volatile(

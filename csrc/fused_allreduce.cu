@@ -96,7 +96,10 @@ __device__ bool xgpu_barrier(const DedlocARParams& p, int bar, cg::grid_group& g
   return v == tag;
 }
 
-template <int CODEC, int MODE>
+// PB = peers per load batch (2, 4 or 8, the smallest >= the group size): the number of chunks processed per iteration is
+// chosen so that every thread keeps ~16 independent 16-byte loads in flight whatever the group size (with two peers and
+// two chunks only 32 remote bytes per thread were in flight -- 2.4 MB chip-wide, below NVLink's latency x bandwidth).
+template <int CODEC, int MODE, int PB>
 __global__ void __launch_bounds__(kARThreads, 2) fused_allreduce_kernel(const __grid_constant__ DedlocARParams p) {
   cg::grid_group grid = cg::this_grid();
   __shared__ float red[64];
@@ -116,16 +119,15 @@ __global__ void __launch_bounds__(kARThreads, 2) fused_allreduce_kernel(const __
 
     long long cur_cb = -1;
     unsigned int bad_count = 0;
-    // Narrow payloads (<= 2 bytes / element) are processed two chunks per iteration: the loads of BOTH chunks from
-    // every peer are issued before any is consumed, doubling the bytes in flight per thread (NVLink needs ~2 MB in
-    // flight chip-wide; with few peers one chunk per thread is not enough).
-    constexpr int kUnroll = (CODEC == CODEC_NONE) ? 1 : 2;
-    constexpr int kBatch = (CODEC == CODEC_NONE) ? 4 : 8;  // fp32 payloads are 2x uint4 per peer
+    // Loads of ALL chunks of an iteration from every peer are issued before any is consumed.
+    constexpr int kBatch = (CODEC == CODEC_NONE) ? (PB < 4 ? PB : 4) : PB;   // fp32 payloads are 2x uint4 per peer
+    constexpr int kUnroll = (CODEC == CODEC_NONE) ? 4 / kBatch : 16 / PB;
     for (long long cbase = c0; cbase < c1;) {
       int nch = (int)((c1 - cbase) < kUnroll ? (c1 - cbase) : kUnroll);
       if constexpr (kIsLut) {
-        // both chunks of an iteration must share one codebook block
-        if (nch == 2 && (cbase / kCodecBlockChunks) != ((cbase + 1) / kCodecBlockChunks)) nch = 1;
+        // all chunks of an iteration must share one codebook block
+        const long long blk_end = (cbase / kCodecBlockChunks + 1) * kCodecBlockChunks;
+        if (cbase + nch > blk_end) nch = (int)(blk_end - cbase);
         const long long cb = cbase / kCodecBlockChunks;
         if (cb != cur_cb) {
           __syncthreads();
@@ -364,14 +366,14 @@ __global__ void __launch_bounds__(kARThreads, 2) fused_allreduce_kernel(const __
   }
 }
 
-template <int CODEC, int MODE>
-static int launch_ar(const DedlocARParams& p, cudaStream_t st) {
+template <int CODEC, int MODE, int PB>
+static int launch_ar_pb(const DedlocARParams& p, cudaStream_t st) {
   static int max_blocks = 0;  // per (CODEC, MODE) instantiation; all devices on the box are identical
   if (max_blocks == 0) {
     int dev = 0, sms = 0, occ = 0;
     DEDLOC_CUDA_CHECK(cudaGetDevice(&dev));
     DEDLOC_CUDA_CHECK(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
-    DEDLOC_CUDA_CHECK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, fused_allreduce_kernel<CODEC, MODE>,
+    DEDLOC_CUDA_CHECK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, fused_allreduce_kernel<CODEC, MODE, PB>,
                                                                     kARThreads, 0));
     DEDLOC_REQUIRE(occ >= 1, "fused_allreduce: kernel does not fit on an SM");
     max_blocks = sms * (occ > 2 ? 2 : occ);
@@ -381,10 +383,17 @@ static int launch_ar(const DedlocARParams& p, cudaStream_t st) {
   if (p.max_blocks > 0 && p.max_blocks < blocks) blocks = p.max_blocks;
   if (nmy < blocks) blocks = nmy < 1 ? 1 : (int)nmy;
   void* args[] = {(void*)&p};
-  DEDLOC_CUDA_CHECK(cudaLaunchCooperativeKernel((const void*)fused_allreduce_kernel<CODEC, MODE>, dim3(blocks),
+  DEDLOC_CUDA_CHECK(cudaLaunchCooperativeKernel((const void*)fused_allreduce_kernel<CODEC, MODE, PB>, dim3(blocks),
                                                 dim3(kARThreads), args, 0, st));
   count_launch();
   return 0;
+}
+
+template <int CODEC, int MODE>
+static int launch_ar(const DedlocARParams& p, cudaStream_t st) {
+  if (p.P <= 2) return launch_ar_pb<CODEC, MODE, 2>(p, st);
+  if (p.P <= 4) return launch_ar_pb<CODEC, MODE, 4>(p, st);
+  return launch_ar_pb<CODEC, MODE, 8>(p, st);
 }
 
 template <int MODE>

@@ -52,7 +52,9 @@ def test_colsum_accumulate(native):
     _close(out, 1.0 + dy.float().sum(0), "colsum", rtol=1e-3, atol=1e-3)
 
 
-def test_fused_ffn_autograd(native):
+@pytest.mark.parametrize("side_stream", [False, True])
+def test_fused_ffn_autograd(native, side_stream):
+    from dedloc_b200.ops import gemm as gemm_ops
     from dedloc_b200.ops.elementwise import gelu_new
     from dedloc_b200.ops.gemm import ffn
 
@@ -68,8 +70,13 @@ def test_fused_ffn_autograd(native):
         l.bias.main_grad = torch.zeros(l.bias.shape, device="cuda")
     x = _rand((2, M // 2, K), 5, 0.5).requires_grad_(True)
     dy = _rand((2, M // 2, K), 6, 0.1)
-    y = ffn(x, l1, l2, residual=x)
-    y.backward(dy)
+    gemm_ops.overlap_wgrad(side_stream)      # weight / bias gradients on the side stream, joined before they are read
+    try:
+        y = ffn(x, l1, l2, residual=x)
+        y.backward(dy)
+    finally:
+        gemm_ops.overlap_wgrad(False)
+        gemm_ops.join_wgrad_stream()
     xr = x.detach().float().requires_grad_(True)
     ps = [t.float().requires_grad_(True) for t in (l1.weight, l1.bias, l2.weight, l2.bias)]
     yr = gelu_new(xr @ ps[0].t() + ps[1]) @ ps[2].t() + ps[3] + xr
