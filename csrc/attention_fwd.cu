@@ -17,6 +17,8 @@
 //   warps 4-7 / 8-11  one thread per query row: running max over the blocks (pass 1), exp2 / row sum / bf16 pack
 //               (pass 2), then O / sum -> bf16 -> swizzled shared memory (the Q buffer of the finished block) ->
 //               one TMA store per block; log-sum-exp saved for the backward kernel
+#include <type_traits>
+
 #include "gemm_common.cuh"
 
 namespace dedloc {
@@ -69,6 +71,7 @@ attention_fwd_kernel(const __grid_constant__ CUtensorMap tmap_qkv, const __grid_
   uint64_t* bias_full = bars + 34;  // [2]
   uint64_t* bias_free = bars + 36;  // [2]
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 38);
+  uint32_t* blk_pad = reinterpret_cast<uint32_t*>(bars + 40);   // [2][4]: does key block kb of this batch row contain padding?
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int S = p.S, H = p.H;
@@ -230,7 +233,14 @@ attention_fwd_kernel(const __grid_constant__ CUtensorMap tmap_qkv, const __grid_
         const int b = bh / H, st = bc & 1;
         mbar_wait(&bias_free[st], ((bc >> 1) & 1) ^ 1);
         float* bias = reinterpret_cast<float*>(sBias + st * kAttBiasBytes);
-        for (int k = lane; k < S; k += 32) bias[k] = p.mask[(size_t)b * S + k] ? 0.f : -INFINITY;
+        uint32_t pad_bits = 0;
+        for (int k = lane; k < S; k += 32) {
+          const bool ok = p.mask[(size_t)b * S + k] != 0;
+          bias[k] = ok ? 0.f : -INFINITY;
+          if (!ok) pad_bits |= 1u << (k >> 7);
+        }
+        pad_bits = __reduce_or_sync(0xffffffffu, pad_bits);
+        if (lane < 4) blk_pad[st * 4 + lane] = (pad_bits >> lane) & 1u;   // blocks without padding skip the bias adds
         __syncwarp();
         if (lane == 0) mbar_arrive(&bias_full[st]);
       }
@@ -265,22 +275,26 @@ attention_fwd_kernel(const __grid_constant__ CUtensorMap tmap_qkv, const __grid_
           uint32_t ra[32], rb[32];
           tmem_ld_32x32b_x32(t_s, ra);
           tmem_ld_32x32b_x32(t_s + 32, rb);
+          auto max_pass = [&](auto PAD) {
+            constexpr bool kPad = decltype(PAD)::value;
 #pragma unroll
-          for (int c = 0; c < 4; ++c) {
-            tmem_ld_wait();       // waits for every outstanding load: chunk c and the prefetched chunk c+1
-            uint32_t (&cur)[32] = (c & 1) ? rb : ra;
+            for (int c = 0; c < 4; ++c) {
+              tmem_ld_wait();       // waits for every outstanding load: chunk c and the prefetched chunk c+1
+              uint32_t (&cur)[32] = (c & 1) ? rb : ra;
 #pragma unroll
-            for (int i = 0; i < 32; i += 4) {
-              float v0 = __uint_as_float(cur[i]), v1 = __uint_as_float(cur[i + 1]);
-              float v2 = __uint_as_float(cur[i + 2]), v3 = __uint_as_float(cur[i + 3]);
-              if (HAS_MASK) {
-                const float4 bb = lds_f4(bias_a + (kb * 128 + c * 32 + i) * 4);
-                v0 += bb.x; v1 += bb.y; v2 += bb.z; v3 += bb.w;
+              for (int i = 0; i < 32; i += 4) {
+                float v0 = __uint_as_float(cur[i]), v1 = __uint_as_float(cur[i + 1]);
+                float v2 = __uint_as_float(cur[i + 2]), v3 = __uint_as_float(cur[i + 3]);
+                if (kPad) {
+                  const float4 bb = lds_f4(bias_a + (kb * 128 + c * 32 + i) * 4);
+                  v0 += bb.x; v1 += bb.y; v2 += bb.z; v3 += bb.w;
+                }
+                m = fmaxf(fmaxf(m, v0), fmaxf(v1, fmaxf(v2, v3)));
               }
-              m = fmaxf(fmaxf(m, v0), fmaxf(v1, fmaxf(v2, v3)));
+              if (c + 2 < 4) tmem_ld_32x32b_x32(t_s + (c + 2) * 32, cur);   // refill the buffer just consumed
             }
-            if (c + 2 < 4) tmem_ld_32x32b_x32(t_s + (c + 2) * 32, cur);   // refill the buffer just consumed
-          }
+          };
+          if (HAS_MASK && blk_pad[(bc & 1) * 4 + kb]) max_pass(std::true_type{}); else max_pass(std::false_type{});
           tc_fence_before();
           __syncwarp();
           if (lane == 0) mbar_arrive(&s_free[w]);
@@ -295,32 +309,36 @@ attention_fwd_kernel(const __grid_constant__ CUtensorMap tmap_qkv, const __grid_
           uint32_t ra[32], rb[32];
           tmem_ld_32x32b_x32(t_s, ra);
           tmem_ld_32x32b_x32(t_s + 32, rb);
+          auto exp_pass = [&](auto PAD) {
+            constexpr bool kPad = decltype(PAD)::value;
 #pragma unroll
-          for (int c = 0; c < 4; ++c) {
-            tmem_ld_wait();
-            uint32_t (&cur)[32] = (c & 1) ? rb : ra;
-            uint32_t pk[16];
+            for (int c = 0; c < 4; ++c) {
+              tmem_ld_wait();
+              uint32_t (&cur)[32] = (c & 1) ? rb : ra;
+              uint32_t pk[16];
 #pragma unroll
-            for (int i = 0; i < 32; i += 4) {
-              float v0 = __uint_as_float(cur[i]), v1 = __uint_as_float(cur[i + 1]);
-              float v2 = __uint_as_float(cur[i + 2]), v3 = __uint_as_float(cur[i + 3]);
-              if (HAS_MASK) {
-                const float4 bb = lds_f4(bias_a + (kb * 128 + c * 32 + i) * 4);
-                v0 += bb.x; v1 += bb.y; v2 += bb.z; v3 += bb.w;
+              for (int i = 0; i < 32; i += 4) {
+                float v0 = __uint_as_float(cur[i]), v1 = __uint_as_float(cur[i + 1]);
+                float v2 = __uint_as_float(cur[i + 2]), v3 = __uint_as_float(cur[i + 3]);
+                if (kPad) {
+                  const float4 bb = lds_f4(bias_a + (kb * 128 + c * 32 + i) * 4);
+                  v0 += bb.x; v1 += bb.y; v2 += bb.z; v3 += bb.w;
+                }
+                const float e0 = ex2f(fmaf(v0, p.scale_log2, -m_scaled));
+                const float e1 = ex2f(fmaf(v1, p.scale_log2, -m_scaled));
+                const float e2 = ex2f(fmaf(v2, p.scale_log2, -m_scaled));
+                const float e3 = ex2f(fmaf(v3, p.scale_log2, -m_scaled));
+                sum += (e0 + e1) + (e2 + e3);
+                pk[i >> 1] = pack_bf16x2(e0, e1);
+                pk[(i >> 1) + 1] = pack_bf16x2(e2, e3);
               }
-              const float e0 = ex2f(fmaf(v0, p.scale_log2, -m_scaled));
-              const float e1 = ex2f(fmaf(v1, p.scale_log2, -m_scaled));
-              const float e2 = ex2f(fmaf(v2, p.scale_log2, -m_scaled));
-              const float e3 = ex2f(fmaf(v3, p.scale_log2, -m_scaled));
-              sum += (e0 + e1) + (e2 + e3);
-              pk[i >> 1] = pack_bf16x2(e0, e1);
-              pk[(i >> 1) + 1] = pack_bf16x2(e2, e3);
+              // in place: bf16 columns [16c, 16c+16) overlay fp32 columns of chunk c/2, which has been read; the
+              // loads in flight read columns >= 32 (c + 1)
+              tmem_st_32x32b_x16(t_s + c * 16, pk);
+              if (c + 2 < 4) tmem_ld_32x32b_x32(t_s + (c + 2) * 32, cur);
             }
-            // in place: bf16 columns [16c, 16c+16) overlay fp32 columns of chunk c/2, which has been read; the
-            // loads in flight read columns >= 32 (c + 1)
-            tmem_st_32x32b_x16(t_s + c * 16, pk);
-            if (c + 2 < 4) tmem_ld_32x32b_x32(t_s + (c + 2) * 32, cur);
-          }
+          };
+          if (HAS_MASK && blk_pad[(bc & 1) * 4 + kb]) exp_pass(std::true_type{}); else exp_pass(std::false_type{});
           tmem_st_wait();
           tc_fence_before();
           __syncwarp();
