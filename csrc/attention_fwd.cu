@@ -4,18 +4,17 @@
 //
 // The exponentials (MUFU, 16 / clock / SM) are the bound at head_dim 64, so the design keeps the MUFU pipe fed:
 // two query blocks (128 rows each) of one (batch, head) are in flight, one per softmax warpgroup, and the tensor
-// core serves whichever of them is ready. Softmax is exact two-pass WITHOUT keeping the 512-column score row: pass 1
-// computes the score blocks only for the row maximum, pass 2 recomputes each block (the tensor core has the
-// cycles to spare), exponentiates against the final maximum and feeds P straight back from tensor memory:
+// core serves whichever of them is ready. Softmax is online over 128-key score blocks with a LAZY rescale: the exponent
+// offset only follows the running row maximum when it grew by more than 2^8, so the accumulated O row (tensor memory)
+// is rarely touched after the first block; P goes straight back to the tensor core from tensor memory:
 //   warp 0      TMA: K / V blocks of 128 keys into fixed per-(batch, head) slots (a slot is refilled for the next
 //               (batch, head) as soon as its last MMA retired), Q blocks double-buffered per warpgroup
 //   warp 1      tcgen05.mma issuer, polling the barriers of both warpgroups:
-//                 pass 1  S_w = Q K_kb^T                      (128 x 128, fp32 in 128 TMEM columns)
-//                 pass 2  S_w = Q K_kb^T again; O_w += P_w V_kb with P (bf16, written in place over S_w by the
-//                         softmax warps) as the TMEM A operand and V as an MN-major B operand
+//                 S_w = Q K_kb^T (128 x 128, fp32 in 128 TMEM columns); O_w += P_w V_kb with P (bf16, written in
+//                 place over S_w by the softmax warps) as the TMEM A operand and V as an MN-major B operand
 //   warp 2      TMEM allocator        warp 3  key-padding bias of the (batch) row, one (batch, head) ahead
-//   warps 4-7 / 8-11  one thread per query row: running max over the blocks (pass 1), exp2 / row sum / bf16 pack
-//               (pass 2), then O / sum -> bf16 -> swizzled shared memory (the Q buffer of the finished block) ->
+//   warps 4-7 / 8-11  one thread per query row: block max, exp2 / row sum / bf16 pack (two reads of the block), rare O
+//               rescale, then O / sum -> bf16 -> swizzled shared memory (the Q buffer of the finished block) ->
 //               one TMA store per block; log-sum-exp saved for the backward kernel
 #include <type_traits>
 
@@ -64,7 +63,7 @@ attention_fwd_kernel(const __grid_constant__ CUtensorMap tmap_qkv, const __grid_
   uint64_t* q_full = bars + 16;     // [wg*2 + stage]
   uint64_t* q_free = bars + 20;     // [wg*2 + stage]
   uint64_t* s_full = bars + 24;     // [wg]
-  uint64_t* s_free = bars + 26;     // [wg]
+  uint64_t* pv_done = bars + 26;    // [wg] committed after every P V product
   uint64_t* p_full = bars + 28;     // [wg]
   uint64_t* o_full = bars + 30;     // [wg]
   uint64_t* o_free = bars + 32;     // [wg]
@@ -86,7 +85,7 @@ attention_fwd_kernel(const __grid_constant__ CUtensorMap tmap_qkv, const __grid_
       mbar_init(&q_full[i], 1); mbar_init(&q_free[i], 1);
     }
     for (int i = 0; i < 2; ++i) {
-      mbar_init(&s_full[i], 1); mbar_init(&s_free[i], 4); mbar_init(&p_full[i], 4);
+      mbar_init(&s_full[i], 1); mbar_init(&pv_done[i], 1); mbar_init(&p_full[i], 4);
       mbar_init(&o_full[i], 1); mbar_init(&o_free[i], 4);
       mbar_init(&bias_full[i], 1); mbar_init(&bias_free[i], 8);
     }
@@ -145,7 +144,7 @@ attention_fwd_kernel(const __grid_constant__ CUtensorMap tmap_qkv, const __grid_
     const uint32_t tb = __shfl_sync(0xffffffffu, tmem_base, 0);
     const int my_bh = (total_bh - (int)blockIdx.x + (int)gridDim.x - 1) / (int)gridDim.x;
     // per-warpgroup progress: (batch, head) index, block index inside it, event index inside the block, counters
-    int bi[2] = {0, 0}, qb[2] = {0, 1}, ev[2] = {0, 0}, uq[2] = {0, 0}, n_sfree[2] = {0, 0}, n_pfull[2] = {0, 0};
+    int bi[2] = {0, 0}, qb[2] = {0, 1}, ev[2] = {0, 0}, uq[2] = {0, 0}, n_pfull[2] = {0, 0};
     bool done[2] = {my_bh == 0, my_bh == 0 || nkb < 2};
     uint32_t cnt_k = 0, cnt_v = 0;       // uses of each K / V slot inside the current (batch, head), 8 bits per slot
     auto issue_s = [&](int w, int kb) {  // S_w = Q K_kb^T
@@ -157,33 +156,28 @@ attention_fwd_kernel(const __grid_constant__ CUtensorMap tmap_qkv, const __grid_
       }
       __syncwarp();
     };
+    // events of one query block: 0 = S(0); 1 + kb = { O += P(kb) V(kb), then S(kb + 1) }
     while (!(done[0] && done[1])) {
       bool progressed = false;
 #pragma unroll
       for (int w = 0; w < 2; ++w) {
         if (done[w]) continue;
         const int e = ev[w];
-        if (e <= nkb) {
-          // pass 1 block e, or (e == nkb) the first block of pass 2
-          const int kb = (e == nkb) ? 0 : e;
-          bool ready = mbar_test_wait(&k_full[kb], bi[w] & 1);
-          if (ready && e == 0) ready = mbar_test_wait(&q_full[w * 2 + (uq[w] & 1)], (uq[w] >> 1) & 1);
-          if (ready && e > 0) ready = mbar_test_wait(&s_free[w], (n_sfree[w] & 1));
+        if (e == 0) {
+          bool ready = mbar_test_wait(&k_full[0], bi[w] & 1);
+          if (ready) ready = mbar_test_wait(&q_full[w * 2 + (uq[w] & 1)], (uq[w] >> 1) & 1);
           if (!ready) continue;
-          if (e > 0) ++n_sfree[w];
           tc_fence_after();
-          issue_s(w, kb);
-          if (e == nkb) {                 // pass-2 use of K slot 0
-            cnt_k += 1u;
-            if ((cnt_k & 0xFF) == (uint32_t)nkb) { cnt_k &= ~0xFFu; if (elect_one()) umma_commit(&k_free[0]); __syncwarp(); }
-          }
-          ev[w] = e + 1;
+          issue_s(w, 0);
+          cnt_k += 1u;
+          if ((cnt_k & 0xFF) == (uint32_t)nkb) { cnt_k &= ~0xFFu; if (elect_one()) umma_commit(&k_free[0]); __syncwarp(); }
+          ev[w] = 1;
         } else {
-          // pass 2: O_w += P_w V_kb, then the next score block
-          const int kb = e - nkb - 1;
+          const int kb = e - 1;
           bool ready = mbar_test_wait(&p_full[w], n_pfull[w] & 1);
           if (ready) ready = mbar_test_wait(&v_full[kb], bi[w] & 1);
           if (ready && kb == 0 && uq[w] > 0) ready = mbar_test_wait(&o_free[w], (uq[w] - 1) & 1);
+          if (ready && kb < nkb - 1) ready = mbar_test_wait(&k_full[kb + 1], bi[w] & 1);
           if (!ready) continue;
           ++n_pfull[w];
           tc_fence_after();
@@ -192,6 +186,7 @@ attention_fwd_kernel(const __grid_constant__ CUtensorMap tmap_qkv, const __grid_
             // 16 keys per k-step: 8 TMEM columns of bf16 P, 2 groups of 8 rows x 128 B of V
 #pragma unroll
             for (int k = 0; k < 8; ++k) umma_f16_ts_lohi(to, ts + k * 8, av + k * 128, kHi, idesc_o, (kb > 0 || k > 0) ? 1u : 0u);
+            umma_commit(&pv_done[w]);                       // O is stable: a lazy rescale may touch it
             if (kb == nkb - 1) umma_commit(&o_full[w]);
           }
           __syncwarp();
@@ -202,7 +197,7 @@ attention_fwd_kernel(const __grid_constant__ CUtensorMap tmap_qkv, const __grid_
             __syncwarp();
           }
           if (kb < nkb - 1) {
-            issue_s(w, kb + 1);
+            issue_s(w, kb + 1);                             // overwrites P(kb): issued behind the MMAs that read it
             cnt_k += 1u << (8 * (kb + 1));
             if (((cnt_k >> (8 * (kb + 1))) & 0xFF) == (uint32_t)nkb) {
               cnt_k &= ~(0xFFu << (8 * (kb + 1)));
@@ -266,13 +261,19 @@ attention_fwd_kernel(const __grid_constant__ CUtensorMap tmap_qkv, const __grid_
           mbar_arrive(&q_free[pending_slot]);
           pending_slot = -1;
         }
-        // ---------------- pass 1: row maximum over all key blocks ----------------
-        float m = -INFINITY;
+        // ---------------- online softmax over the key blocks, lazy rescale ----------------
+        // m_use = exponent offset in use (raw-score units). It follows the running row maximum only when that grew by
+        // more than 8 in the log2 domain (p <= 256: harmless in bf16 P / fp32 sum and O), so the read-modify-write of
+        // the O row in tensor memory is rare after the first block. The final O / sum and lse are exact either way.
+        float m_use = -INFINITY, sum = 0.f;
         for (int kb = 0; kb < nkb; ++kb) {
           mbar_wait(&s_full[w], n_sfull & 1);
           ++n_sfull;
           tc_fence_after();
+          const bool padded = HAS_MASK && blk_pad[(bc & 1) * 4 + kb] != 0;
           uint32_t ra[32], rb[32];
+          // (a) block maximum
+          float bm = -INFINITY;
           tmem_ld_32x32b_x32(t_s, ra);
           tmem_ld_32x32b_x32(t_s + 32, rb);
           auto max_pass = [&](auto PAD) {
@@ -289,24 +290,41 @@ attention_fwd_kernel(const __grid_constant__ CUtensorMap tmap_qkv, const __grid_
                   const float4 bb = lds_f4(bias_a + (kb * 128 + c * 32 + i) * 4);
                   v0 += bb.x; v1 += bb.y; v2 += bb.z; v3 += bb.w;
                 }
-                m = fmaxf(fmaxf(m, v0), fmaxf(v1, fmaxf(v2, v3)));
+                bm = fmaxf(fmaxf(bm, v0), fmaxf(v1, fmaxf(v2, v3)));
               }
               if (c + 2 < 4) tmem_ld_32x32b_x32(t_s + (c + 2) * 32, cur);   // refill the buffer just consumed
             }
           };
-          if (HAS_MASK && blk_pad[(bc & 1) * 4 + kb]) max_pass(std::true_type{}); else max_pass(std::false_type{});
-          tc_fence_before();
-          __syncwarp();
-          if (lane == 0) mbar_arrive(&s_free[w]);
-        }
-        const float m_scaled = (m == -INFINITY) ? 0.f : m * p.scale_log2;
-        // ---------------- pass 2: p = exp2(s * scale_log2 - m_scaled), bf16 pairs in place over the scores ----------------
-        float sum = 0.f;
-        for (int kb = 0; kb < nkb; ++kb) {
-          mbar_wait(&s_full[w], n_sfull & 1);
-          ++n_sfull;
-          tc_fence_after();
-          uint32_t ra[32], rb[32];
+          if (padded) max_pass(std::true_type{}); else max_pass(std::false_type{});
+          // (b) exponent offset; rescale what has been accumulated when it has to move
+          const float m_new = fmaxf(m_use, bm);
+          if (kb == 0) {
+            m_use = m_new;
+          } else {
+            const bool need = (m_new - m_use) * p.scale_log2 > 8.f;      // (-inf) - (-inf) = NaN compares false
+            if (__any_sync(0xffffffffu, need)) {
+              mbar_wait(&pv_done[w], (uq * nkb + kb - 1) & 1);            // O holds the products of blocks < kb
+              tc_fence_after();
+              const float f = need ? ex2f((m_use - m_new) * p.scale_log2) : 1.f;
+              uint32_t o0[32], o1[32];
+              tmem_ld_32x32b_x32(t_o, o0);
+              tmem_ld_32x32b_x32(t_o + 32, o1);
+              tmem_ld_wait();
+#pragma unroll
+              for (int i = 0; i < 32; ++i) {
+                o0[i] = __float_as_uint(__uint_as_float(o0[i]) * f);
+                o1[i] = __float_as_uint(__uint_as_float(o1[i]) * f);
+              }
+              tmem_st_32x32b_x16(t_o, reinterpret_cast<const uint32_t(&)[16]>(o0[0]));
+              tmem_st_32x32b_x16(t_o + 16, reinterpret_cast<const uint32_t(&)[16]>(o0[16]));
+              tmem_st_32x32b_x16(t_o + 32, reinterpret_cast<const uint32_t(&)[16]>(o1[0]));
+              tmem_st_32x32b_x16(t_o + 48, reinterpret_cast<const uint32_t(&)[16]>(o1[16]));
+              sum *= f;
+              if (need) m_use = m_new;
+            }
+          }
+          const float m_scaled = (m_use == -INFINITY) ? 0.f : m_use * p.scale_log2;
+          // (c) p = exp2(s * scale_log2 - m_scaled), bf16 pairs in place over the scores (second read of the block)
           tmem_ld_32x32b_x32(t_s, ra);
           tmem_ld_32x32b_x32(t_s + 32, rb);
           auto exp_pass = [&](auto PAD) {
@@ -338,12 +356,13 @@ attention_fwd_kernel(const __grid_constant__ CUtensorMap tmap_qkv, const __grid_
               if (c + 2 < 4) tmem_ld_32x32b_x32(t_s + (c + 2) * 32, cur);
             }
           };
-          if (HAS_MASK && blk_pad[(bc & 1) * 4 + kb]) exp_pass(std::true_type{}); else exp_pass(std::false_type{});
+          if (padded) exp_pass(std::true_type{}); else exp_pass(std::false_type{});
           tmem_st_wait();
           tc_fence_before();
           __syncwarp();
           if (lane == 0) mbar_arrive(&p_full[w]);
         }
+        const float m = m_use;
         // ---------------- epilogue: O / sum -> bf16 -> swizzled smem (the Q stage of this block) -> TMA store ----------------
         mbar_wait(&o_full[w], uq & 1);
         tc_fence_after();
