@@ -96,15 +96,48 @@ __global__ void __launch_bounds__(kLnThreads) ln_bwd_kernel(const __nv_bfloat16*
 #pragma unroll
     for (int i = 0; i < 8; ++i) { dg[c][i] = 0.f; db[c][i] = 0.f; }
   }
-  for (int row = blockIdx.x * (kLnThreads / 32) + warp; row < M; row += warps_per_grid) {
-    const float mean = mean_in[row], rstd = rstd_in[row];
-    float xh[CHUNKS][8], gy[CHUNKS][8];
-    float s1 = 0.f, s2 = 0.f;
+  // software pipeline: the 2 x CHUNKS 16-byte loads of the NEXT row are in flight while this row is reduced (the
+  // register footprint allows one block per SM, so one row per warp in flight covers only ~60 % of HBM's
+  // latency x bandwidth product)
+  constexpr bool kPipe = CHUNKS <= 4;            // wider rows would spill
+  uint4 xn[CHUNKS], dn[CHUNKS];
+  int row = blockIdx.x * (kLnThreads / 32) + warp;
+  if (kPipe && row < M) {
 #pragma unroll
     for (int c = 0; c < CHUNKS; ++c) {
       const size_t off = (size_t)row * H + (c * 32 + lane) * 8;
-      const uint4 xu = ld_stream_v4(x + off);
-      const uint4 du = ld_stream_v4(dy + off);
+      xn[c] = ld_stream_v4(x + off);
+      dn[c] = ld_stream_v4(dy + off);
+    }
+  }
+  for (; row < M; row += warps_per_grid) {
+    const float mean = mean_in[row], rstd = rstd_in[row];
+    float xh[CHUNKS][8], gy[CHUNKS][8];
+    float s1 = 0.f, s2 = 0.f;
+    uint4 xc[CHUNKS], dc[CHUNKS];
+    if (!kPipe) {
+#pragma unroll
+      for (int c = 0; c < CHUNKS; ++c) {
+        const size_t off = (size_t)row * H + (c * 32 + lane) * 8;
+        xn[c] = ld_stream_v4(x + off);
+        dn[c] = ld_stream_v4(dy + off);
+      }
+    }
+#pragma unroll
+    for (int c = 0; c < CHUNKS; ++c) { xc[c] = xn[c]; dc[c] = dn[c]; }
+    const int nrow = row + warps_per_grid;
+    if (kPipe && nrow < M) {
+#pragma unroll
+      for (int c = 0; c < CHUNKS; ++c) {
+        const size_t off = (size_t)nrow * H + (c * 32 + lane) * 8;
+        xn[c] = ld_stream_v4(x + off);
+        dn[c] = ld_stream_v4(dy + off);
+      }
+    }
+#pragma unroll
+    for (int c = 0; c < CHUNKS; ++c) {
+      const uint4 xu = xc[c];
+      const uint4 du = dc[c];
       float xv[8], dv[8];
       float2 t;
       t = unpack_bf16x2(xu.x); xv[0] = t.x; xv[1] = t.y;
