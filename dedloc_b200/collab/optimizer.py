@@ -76,8 +76,16 @@ class CollaborativeOptimizer:
         self.local_steps_accumulated = 0
         self.last_step_time: Optional[float] = None
         self.state_lock = threading.RLock()
+        # True while this peer sits inside a global step BEFORE any parameter update (it holds state_lock there, but
+        # its parameters are stable): state downloads are served without the lock in that window (lineage healing)
+        self._params_parked = False
         self.round_counter = 0
-        self.stats = {"rounds": 0, "failed_rounds": 0, "solo_rounds": 0, "state_downloads": 0,
+        # Parameter lineage: a hash chain over (who averaged with whom, at which step). Peers with equal lineage hold
+        # bit-identical parameters (every update is deterministic given the group), so a group whose members disagree
+        # -- somebody stepped alone after a failed round -- is healed BEFORE the reduction: the minority copies the
+        # state of a majority member. (The reference heals the same situation by averaging parameters every step.)
+        self.lineage = "0" * 16
+        self.stats = {"rounds": 0, "failed_rounds": 0, "solo_rounds": 0, "state_downloads": 0, "lineage_resyncs": 0,
                       "matchmaking_s": 0.0, "averaging_host_s": 0.0}
         self.is_fused = isinstance(opt, FusedOptimizerBase)
         self._params = [p for g in opt.param_groups for p in g["params"]]
@@ -312,7 +320,7 @@ class CollaborativeOptimizer:
         mode = MODE_AUX if self.auxiliary else (MODE_CLIENT if self.client_mode else MODE_NODE)
         blob = {"weight": 0.0 if self.auxiliary else float(self.local_samples_accumulated), "mode": mode,
                 "throughput": None if self.client_mode else float(self.throughput or 1.0),
-                "step": self.local_step, "handle": None, "total": None, "device": None}
+                "step": self.local_step, "handle": None, "total": None, "device": None, "lineage": self.lineage}
         if self.is_fused and self.on_gpu:
             blob.update(handle=self.opt.buffers.handle, total=self.opt.layout.total,
                         device=self.opt.buffers.device)
@@ -321,6 +329,7 @@ class CollaborativeOptimizer:
     def _global_step(self, state: CollaborationState) -> None:
         t0 = time.perf_counter()
         with self.performance_ema.pause(), self.state_lock:
+            self._params_parked = True
             group: Optional[GroupInfo] = None
             if state.num_peers > 1:  # num_peers counts this peer's own progress record too
                 expected = state.num_peers if self.expected_group_size_from_tracker else None
@@ -344,10 +353,14 @@ class CollaborativeOptimizer:
             if not averaged and not self.auxiliary:
                 self.stats["solo_rounds"] += 1
                 self._run_solo_round()
+                self.lineage = self._mix(self.lineage, "S", self.local_step, self.endpoint)
+            elif averaged:
+                self.lineage = self._round_lineage
             self._finish_global_step()
             self.stats["averaging_host_s"] += time.perf_counter() - t1
 
     def _finish_global_step(self) -> None:
+        self._params_parked = False
         if self.is_fused and self.on_gpu:
             self.opt.buffers.acc.zero_()
         elif self._cpu_acc is not None:
@@ -395,6 +408,7 @@ class CollaborativeOptimizer:
         flat_ops.encode(codec, buf.acc, scale, buf.send, buf.aux)
 
     def _launch_fused(self, group_spec, codec) -> dict:
+        # (GPU peers serve downloads from the mapped buffer, guarded by the requester's step seqlock)
         from ..parallel.fused_allreduce import fused_allreduce
 
         opt = self.opt
@@ -429,14 +443,48 @@ class CollaborativeOptimizer:
         self._generic_opt_step()
 
     def _generic_opt_step(self) -> None:
+        self._params_parked = False
         finite = all(torch.isfinite(p.grad).all() for p in self._params if p.grad is not None)
         if finite:
             self.opt.step()
         else:
             logger.warning("non-finite gradients: optimizer update skipped at step %d", self.local_step)
 
+    @staticmethod
+    def _mix(prev: str, *parts) -> str:
+        import hashlib
+
+        h = hashlib.blake2b(prev.encode(), digest_size=8)
+        for part in parts:
+            h.update(b"|" + str(part).encode())
+        return h.hexdigest()
+
+    def _heal_lineage(self, group: GroupInfo, blobs: List[dict]) -> str:
+        """Agree on ONE lineage for the group (most common, ties by smallest endpoint) and, if ours differs, copy the
+        state of a member that has it. Donors are parked at the first barrier of this very round: their parameters do
+        not change while we copy. Returns the agreed lineage."""
+        votes: Dict[str, List[str]] = {}
+        for ep, b in zip(group.endpoints, blobs):
+            votes.setdefault(str(b.get("lineage", "")), []).append(ep)
+        agreed = min(votes, key=lambda l: (-len(votes[l]), min(votes[l])))
+        if len(votes) > 1 and self.lineage != agreed and not self.auxiliary:
+            donor = min(votes[agreed])
+            logger.warning("%s: parameters diverged from the group (lineage %s vs %s): copying the state of %s",
+                           self.endpoint, self.lineage, agreed, donor)
+            ok = False
+            try:
+                ok = self._download_from(donor, bool(self.is_fused and self.on_gpu))
+            except Exception as e:
+                logger.warning("lineage resync from %s failed: %r", donor, e)
+            if not ok:
+                raise AllreduceException("could not resynchronise parameters with the group")
+            self.stats["lineage_resyncs"] += 1
+        return agreed
+
     def _run_group_round(self, group: GroupInfo) -> None:
         blobs = list(group.gathered)
+        agreed = self._heal_lineage(group, blobs)
+        self._round_lineage = self._mix(agreed, "G", blobs[0].get("step"), *sorted(group.endpoints))
         all_gpu = all(b.get("handle") for b in blobs) and len({b.get("total") for b in blobs}) == 1
         if self.is_fused and self.on_gpu and all_gpu:
             return self._run_fused_group_round(group, blobs)
@@ -542,7 +590,7 @@ class CollaborativeOptimizer:
         if not self.allow_state_sharing:
             raise RuntimeError("this peer does not share its state")
         meta = {"local_step": self.local_step, "fused": bool(self.is_fused and self.on_gpu), "handle": None,
-                "total": None, "opt_step": getattr(self.opt, "opt_step", None)}
+                "total": None, "opt_step": getattr(self.opt, "opt_step", None), "lineage": self.lineage}
         if meta["fused"]:
             meta.update(handle=self.opt.buffers.handle, total=self.opt.layout.total)
         if payload.get("meta_only") or (meta["fused"] and payload.get("can_map")):
@@ -551,12 +599,22 @@ class CollaborativeOptimizer:
         import io
 
         def snapshot() -> bytes:
-            with self.state_lock:
-                blob = {"params": [p.detach().float().cpu() for p in self._params],
+            while True:
+                locked = self.state_lock.acquire(timeout=0.05)
+                if locked or self._params_parked:
+                    break
+            try:
+                step_before = self.local_step
+                blob = {"params": [p.detach().float().cpu().clone() for p in self._params],
                         "opt": self.opt.state_dict()}
                 bio = io.BytesIO()
                 torch.save(blob, bio)
+                if not locked and (not self._params_parked or self.local_step != step_before):
+                    raise RuntimeError("state changed while it was being copied; retry")
                 return bio.getvalue()
+            finally:
+                if locked:
+                    self.state_lock.release()
 
         meta["blob"] = await asyncio.get_event_loop().run_in_executor(None, snapshot)
         return meta
@@ -617,6 +675,7 @@ class CollaborativeOptimizer:
                     self.local_step = int(meta["local_step"])
                     if meta.get("opt_step") is not None:
                         self.opt.opt_step = int(meta["opt_step"])
+                    self.lineage = str(meta.get("lineage", self.lineage))
                     return True
                 meta = after
             return False
@@ -640,4 +699,5 @@ class CollaborativeOptimizer:
             except Exception as e:  # e.g. the donor has not created optimizer state yet
                 logger.debug("optimizer state not loaded: %r", e)
             self.local_step = int(meta["local_step"])
+            self.lineage = str(meta.get("lineage", self.lineage))
         return True

@@ -166,3 +166,37 @@ def test_dead_peer_does_not_stall_the_other():
     finally:
         c0.shutdown()
         first.shutdown()
+
+
+def test_diverged_peer_is_healed_by_lineage():
+    """A peer that stepped alone after a failed round holds different parameters at the same step number. Its lineage
+    hash differs from the group's, so at the next joint round it copies the state of a majority member before the
+    reduction and all peers are bit-identical again (the reference heals this by averaging parameters every step)."""
+    first, m0, c0 = make_peer(None, "cfg1heal", target=16)
+    d1, m1, c1 = make_peer(first, "cfg1heal", target=16)
+    d2, m2, c2 = make_peer(first, "cfg1heal", target=16)
+    peers = [(m0, c0), (m1, c1), (m2, c2)]
+    try:
+        log = []
+        threads = [threading.Thread(target=run_trainer, args=(i, m, c, 1, log)) for i, (m, c) in enumerate(peers)]
+        [t.start() for t in threads]
+        [t.join(timeout=120) for t in threads]
+        assert all(c.local_step == 1 for _, c in peers)
+        assert c0.lineage == c1.lineage == c2.lineage != "0" * 16
+        # peer 2 "stepped alone": same step number, different parameters, different lineage
+        with torch.no_grad():
+            for p in m2.parameters():
+                p.add_(0.01)
+        c2.lineage = c2._mix(c2.lineage, "S", c2.local_step, c2.endpoint)
+        threads = [threading.Thread(target=run_trainer, args=(i, m, c, 2, log)) for i, (m, c) in enumerate(peers)]
+        [t.start() for t in threads]
+        [t.join(timeout=120) for t in threads]
+        assert all(c.local_step == 2 for _, c in peers)
+        assert c2.stats["lineage_resyncs"] == 1 and c0.stats["lineage_resyncs"] == 0 and c1.stats["lineage_resyncs"] == 0
+        assert c0.lineage == c1.lineage == c2.lineage
+        assert_same_params(m0, m1, tol=1e-6)
+        assert_same_params(m0, m2, tol=1e-6)
+    finally:
+        for c, d in ((c0, first), (c1, d1), (c2, d2)):
+            c.shutdown()
+            d.shutdown()

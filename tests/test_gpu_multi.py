@@ -27,3 +27,35 @@ def test_two_gpu_collaborative_steps(compression):
     assert out["collab"]["solo_rounds"] == 0 and out["collab"]["failed_rounds"] == 0, out["collab"]
     assert out["local_step"] == 4
     assert out["gpu_launches"] > 0
+
+
+def test_late_joiner_and_peer_death(tmp_path):
+    """Elasticity on real peer memory: GPU 1 joins two steps late (state download from GPU 0 over CUDA IPC), both run
+    joint rounds with bit-identical parameters, then GPU 1 vanishes without shutting down and GPU 0 keeps stepping
+    (bounded flag waits / matchmaking timeouts, solo rounds) instead of hanging."""
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs 2 GPUs")
+    worker = os.path.join(ROOT, "tests", "elastic_worker.py")
+    first = subprocess.Popen([sys.executable, worker, "--role", "first", "--dir", str(tmp_path), "--until", "9"],
+                             cwd=ROOT, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True)
+    second = subprocess.Popen([sys.executable, worker, "--role", "second", "--dir", str(tmp_path), "--until", "6"],
+                              cwd=ROOT, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True)
+    try:
+        out2, _ = second.communicate(timeout=300)
+        out1, _ = first.communicate(timeout=300)
+    finally:
+        for p in (first, second):
+            if p.poll() is None:
+                p.kill()
+    assert first.returncode == 0, out1[-3000:]
+    assert second.returncode == 0, out2[-3000:]
+    a = json.load(open(tmp_path / "first.json"))
+    b = json.load(open(tmp_path / "second.json"))
+    assert b["joined_at"] is not None and b["joined_at"] >= 2, b          # it adopted the collaboration's step
+    assert b["stats"].get("state_downloads", 0) >= 1, b["stats"]
+    common = sorted(set(a["digests"]) & set(b["digests"]), key=int)
+    assert len(common) >= 2, (a["digests"].keys(), b["digests"].keys())
+    for s in common:                                                        # bit-identical master parameters
+        assert a["digests"][s] == b["digests"][s], (s, a["digests"][s], b["digests"][s])
+    assert a["local_step"] >= 9, a                                          # kept going after the peer died
+    assert a["stats"]["solo_rounds"] >= 1, a["stats"]
