@@ -85,6 +85,7 @@ class CollaborativeOptimizer:
         # -- somebody stepped alone after a failed round -- is healed BEFORE the reduction: the minority copies the
         # state of a majority member. (The reference heals the same situation by averaging parameters every step.)
         self.lineage = "0" * 16
+        self.lineage_depth = 0          # optimizer steps behind this lineage: ties go to the longer training history
         self.stats = {"rounds": 0, "failed_rounds": 0, "solo_rounds": 0, "state_downloads": 0, "lineage_resyncs": 0,
                       "matchmaking_s": 0.0, "averaging_host_s": 0.0}
         self.is_fused = isinstance(opt, FusedOptimizerBase)
@@ -320,7 +321,8 @@ class CollaborativeOptimizer:
         mode = MODE_AUX if self.auxiliary else (MODE_CLIENT if self.client_mode else MODE_NODE)
         blob = {"weight": 0.0 if self.auxiliary else float(self.local_samples_accumulated), "mode": mode,
                 "throughput": None if self.client_mode else float(self.throughput or 1.0),
-                "step": self.local_step, "handle": None, "total": None, "device": None, "lineage": self.lineage}
+                "step": self.local_step, "handle": None, "total": None, "device": None, "lineage": self.lineage,
+                "lineage_depth": self.lineage_depth}
         if self.is_fused and self.on_gpu:
             blob.update(handle=self.opt.buffers.handle, total=self.opt.layout.total,
                         device=self.opt.buffers.device)
@@ -354,8 +356,10 @@ class CollaborativeOptimizer:
                 self.stats["solo_rounds"] += 1
                 self._run_solo_round()
                 self.lineage = self._mix(self.lineage, "S", self.local_step, self.endpoint)
+                self.lineage_depth += 1
             elif averaged:
                 self.lineage = self._round_lineage
+                self.lineage_depth = self._agreed_depth + 1
             self._finish_global_step()
             self.stats["averaging_host_s"] += time.perf_counter() - t1
 
@@ -464,9 +468,14 @@ class CollaborativeOptimizer:
         state of a member that has it. Donors are parked at the first barrier of this very round: their parameters do
         not change while we copy. Returns the agreed lineage."""
         votes: Dict[str, List[str]] = {}
+        depth: Dict[str, int] = {}
         for ep, b in zip(group.endpoints, blobs):
-            votes.setdefault(str(b.get("lineage", "")), []).append(ep)
-        agreed = min(votes, key=lambda l: (-len(votes[l]), min(votes[l])))
+            lin = str(b.get("lineage", ""))
+            votes.setdefault(lin, []).append(ep)
+            depth[lin] = max(depth.get(lin, 0), int(b.get("lineage_depth", 0) or 0))
+        # most members; then the longest training history (a freshly started peer never wins a tie); then endpoint
+        agreed = min(votes, key=lambda l: (-len(votes[l]), -depth[l], min(votes[l])))
+        self._agreed_depth = depth[agreed]
         if len(votes) > 1 and self.lineage != agreed and not self.auxiliary:
             donor = min(votes[agreed])
             logger.warning("%s: parameters diverged from the group (lineage %s vs %s): copying the state of %s",
@@ -590,7 +599,8 @@ class CollaborativeOptimizer:
         if not self.allow_state_sharing:
             raise RuntimeError("this peer does not share its state")
         meta = {"local_step": self.local_step, "fused": bool(self.is_fused and self.on_gpu), "handle": None,
-                "total": None, "opt_step": getattr(self.opt, "opt_step", None), "lineage": self.lineage}
+                "total": None, "opt_step": getattr(self.opt, "opt_step", None), "lineage": self.lineage,
+                "lineage_depth": self.lineage_depth}
         if meta["fused"]:
             meta.update(handle=self.opt.buffers.handle, total=self.opt.layout.total)
         if payload.get("meta_only") or (meta["fused"] and payload.get("can_map")):
@@ -676,6 +686,7 @@ class CollaborativeOptimizer:
                     if meta.get("opt_step") is not None:
                         self.opt.opt_step = int(meta["opt_step"])
                     self.lineage = str(meta.get("lineage", self.lineage))
+                    self.lineage_depth = int(meta.get("lineage_depth", self.lineage_depth) or 0)
                     return True
                 meta = after
             return False
@@ -700,4 +711,5 @@ class CollaborativeOptimizer:
                 logger.debug("optimizer state not loaded: %r", e)
             self.local_step = int(meta["local_step"])
             self.lineage = str(meta.get("lineage", self.lineage))
+            self.lineage_depth = int(meta.get("lineage_depth", self.lineage_depth) or 0)
         return True

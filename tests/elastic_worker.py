@@ -25,14 +25,16 @@ def main():
     ap.add_argument("--role", required=True)
     ap.add_argument("--dir", required=True)
     ap.add_argument("--until", type=int, required=True)
+    ap.add_argument("--device", default="cuda")
     args = ap.parse_args()
     from dedloc_b200.dht import DHT
     from dedloc_b200.models.albert import AlbertConfig
     from dedloc_b200.trainers.pretrain import PeerConfig, SyntheticMLMBatches, build_albert_peer
 
     first = args.role == "first"
-    dev = torch.device("cuda", 0 if first else 1)
-    torch.cuda.set_device(dev)
+    dev = torch.device("cuda", 0 if first else 1) if args.device == "cuda" else torch.device("cpu")
+    if dev.type == "cuda":
+        torch.cuda.set_device(dev)
     port_file = os.path.join(args.dir, "port")
     prog_file = os.path.join(args.dir, "first_step")
     if first:
@@ -54,18 +56,33 @@ def main():
     t0 = time.time()
     i = 0
     joined_at = None
-    while collab.local_step < args.until and time.time() - t0 < 150:
+    # first : runs until the second peer has vanished and `--until` more collaborative steps have happened after that
+    # second: runs `--until` collaborative steps after it joined, then dies
+    other_json = os.path.join(args.dir, "second.json")
+    death_step = None
+    while time.time() - t0 < 200:
+        if first:
+            if death_step is None and os.path.exists(other_json):
+                death_step = collab.local_step
+            if death_step is not None and collab.local_step >= death_step + args.until:
+                break
+            time.sleep(0.02)          # GPU peers step every ~15 ms: do not run hundreds of steps while the other starts
+        elif joined_at is not None and collab.local_step >= joined_at + args.until:
+            break
         stepped = trainer.micro_step(batches[i % len(batches)])
         i += 1
         if not first and joined_at is None and collab.local_step > 0:
             joined_at = collab.local_step
         if stepped:
-            torch.cuda.synchronize()
-            digests[collab.local_step] = digest(trainer.opt.buffers.p32)
+            if dev.type == "cuda":
+                torch.cuda.synchronize()
+                digests[collab.local_step] = digest(trainer.opt.buffers.p32)
+            else:
+                digests[collab.local_step] = digest(torch.cat([p.detach().float().reshape(-1) for p in trainer.model.parameters()]))
             if first:
                 open(prog_file, "w").write(str(collab.local_step))
     out = {"role": args.role, "local_step": collab.local_step, "stats": {k: v for k, v in collab.stats.items() if isinstance(v, (int, float))},
-           "digests": digests, "joined_at": joined_at, "micro_steps": i}
+           "digests": digests, "joined_at": joined_at, "micro_steps": i, "death_step": death_step}
     json.dump(out, open(os.path.join(args.dir, f"{args.role}.json"), "w"))
     print(json.dumps({k: v for k, v in out.items() if k != "digests"}), flush=True)
     if first:
