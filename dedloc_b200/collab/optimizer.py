@@ -51,7 +51,7 @@ class CollaborativeOptimizer:
                  throughput: Optional[float] = None, bandwidth: Optional[float] = None,
                  listen_on: str = "127.0.0.1:*", start: bool = True, max_grad_norm: Optional[float] = None,
                  peer_key: Optional[bytes] = None, expected_group_size_from_tracker: bool = True,
-                 replicate_state: bool = True, step_slack_fraction: float = 0.5, **unused_kwargs):
+                 replicate_state: bool = True, step_slack_fraction: float = 0.75, **unused_kwargs):
         if compression is not None:  # sgd_collaborative.py:150 spells the kwarg `compression=`
             compression_type = compression
         if isinstance(compression_type, str):
