@@ -40,6 +40,7 @@ def parse_args():
     ap.add_argument("--model", default="albert-large-v2", choices=["albert-large-v2", "albert-small", "albert-tiny"])
     ap.add_argument("--ops", default="native", choices=["native", "torch"], help="linear layers: tcgen05 or torch")
     ap.add_argument("--skip-e2e", action="store_true")
+    ap.add_argument("--ddp-micro-batch", type=int, default=64, help="micro-batch cap of the --impl ddp baseline arm")
     ap.add_argument("--no-cuda-graph", action="store_true", help="run the micro-step eagerly")
     ap.add_argument("--overlap-wgrad", action="store_true", help="launch weight/bias gradient kernels on a side stream")
     return ap.parse_args()
