@@ -32,7 +32,7 @@ def parse_args():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference", "ddp"])
     ap.add_argument("--micro-batch", type=int, default=128,
-                    help="samples per device per micro-step (128: +4 % over 64 at N=1 -- larger GEMM M, fewer launches; 256 makes "
+                    help="samples per device per micro-step (128: +4 %% over 64 at N=1 -- larger GEMM M, fewer launches; 256 makes "
                          "rounds of only 2 micro-steps at N=8 and overshoots the target batch)")
     ap.add_argument("--seq-len", type=int, default=512)
     ap.add_argument("--target-batch-size", type=int, default=4096)
