@@ -5,10 +5,12 @@
 // (~6300 B/clk chip-wide), not by the tensor cores. Pairing two CTAs lets each one load ITS 128 rows of A and only
 // HALF of B (128 of the 256 columns); tcgen05.mma.cta_group::2 reads both halves across the pair: 128 FLOP/byte.
 //
-// Roles per CTA (256 threads): warp 0 TMA producer (both CTAs; transaction bytes of both land on the LEADER's
-// full barrier), warp 1 MMA issuer (leader CTA only; tcgen05.commit multicasts to both CTAs' barriers), warp 2
-// TMEM allocator (cta_group::2, both CTAs), warps 4..7 epilogue (each CTA drains its own 128 accumulator rows and
-// arrives on the leader's tmem_empty barrier). Same operand layouts / fused epilogues as gemm_tcgen05.cu.
+// Roles per CTA (352 threads, 5 smem stages): warp 0 TMA producer (both CTAs; transaction bytes of both land on the
+// LEADER's full barrier; MN-major operands through a 3-D tensor map, one request per stage and operand), warp 1 MMA
+// issuer (leader CTA only, elect.sync region with precomputed descriptor words; tcgen05.commit multicasts to both
+// CTAs' barriers), warp 2 TMEM allocator (cta_group::2, both CTAs), warps 3..10 epilogue (two per TMEM lane quadrant:
+// each CTA drains its own 128 accumulator rows, 128 columns per warp, and arrives on the leader's tmem_empty
+// barrier). Same operand layouts / fused epilogues as gemm_tcgen05.cu; K tails are zero-filled by TMA.
 #include "gemm_common.cuh"
 
 namespace dedloc {
