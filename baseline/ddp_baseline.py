@@ -1,10 +1,16 @@
-"""BASELINE.md B1: the torch DDP / NCCL (+ cuBLAS, SDPA) build of the SAME config on the same box.
+"""BASELINE.md B1 / B2: the torch DDP / NCCL (+ cuBLAS, SDPA) build of the SAME config on the same box.
 
 HF `transformers.AlbertForPreTraining` (the model class the reference instantiates, albert/run_trainer.py:64-68),
-the restated LAMB of optim/lamb.py (torch_optimizer is not installable offline), bf16 autocast,
-DistributedDataParallel with gradient accumulation under no_sync() up to the global batch of 4096, grad-norm
-clipping 1.0. None of this repo's kernels or engine is on this path. Same JSON line as bench.py's own arm with
-"impl": "ddp".
+the restated LAMB of optim/lamb.py (torch_optimizer is not installable offline), gradient accumulation up to the
+global batch of 4096, grad-norm clipping 1.0. None of this repo's kernels or engine is on this path. Same JSON line
+as bench.py's own arm with "impl": "ddp". Three variants (`--ddp-variant`):
+
+  stock      fp32 parameters + torch.autocast(bf16), DistributedDataParallel with no_sync() accumulation -- what
+             classy_vision/generic/distributed_util.py:219-244 builds (B1)
+  fp16hook   stock + DDP's fp16_compress_hook (classy_vision/tasks/classification_task.py:876-886) (B2)
+  best       the fairest torch can do without custom kernels: bf16 parameters (no autocast casts) with fp32 master
+             copies inside LAMB, SDPA attention, the micro-step captured in a CUDA graph when the HF module allows it,
+             one NCCL all-reduce of the flat bf16 gradient per optimizer step
 """
 from __future__ import annotations
 
@@ -26,42 +32,140 @@ def main_ddp(args) -> int:
     rank = int(os.environ.get("RANK", 0))
     world = int(os.environ.get("WORLD_SIZE", 1))
     local_rank = int(os.environ.get("LOCAL_RANK", 0))
+    variant = getattr(args, "ddp_variant", "stock")
     torch.cuda.set_device(local_rank)
     device = torch.device("cuda", local_rank)
     if world > 1:
         dist.init_process_group("nccl", device_id=device)
+    vocab = 32000 if getattr(args, "model", "") == "sahajbert" else 30000
     hf_cfg = transformers.AlbertConfig(
-        vocab_size=30000, embedding_size=128, hidden_size=1024, num_hidden_layers=24, num_attention_heads=16,
+        vocab_size=vocab, embedding_size=128, hidden_size=1024, num_hidden_layers=24, num_attention_heads=16,
         intermediate_size=4096, hidden_act="gelu_new", hidden_dropout_prob=0.0, attention_probs_dropout_prob=0.0,
         max_position_embeddings=512, type_vocab_size=2)
     torch.manual_seed(0)
     model = transformers.AlbertForPreTraining(hf_cfg).to(device).train()
-    opt = Lamb(albert_param_groups(model, 0.01), lr=0.00176, betas=(0.9, 0.999), eps=1e-6, weight_decay=0.01,
-               clamp_value=10000.0, debias=True)
+    seq = args.seq_len
+    notes = []
+
+    best = variant == "best"
+    masters = None
+    if best:
+        torch.backends.cuda.matmul.allow_tf32 = True
+        masters = [p.detach().clone().float().requires_grad_(True) for p in model.parameters()]
+        for m, (n, _) in zip(masters, model.named_parameters()):
+            m._dedloc_name = n
+        model = model.to(torch.bfloat16)
+        no_decay = ["bias", "LayerNorm.weight", "layer_norm.weight"]
+        named = [(n, m) for (n, _), m in zip(model.named_parameters(), masters)]
+        groups = [{"params": [m for n, m in named if not any(nd in n for nd in no_decay)], "weight_decay": 0.01},
+                  {"params": [m for n, m in named if any(nd in n for nd in no_decay)], "weight_decay": 0.0}]
+    else:
+        groups = albert_param_groups(model, 0.01)
+    opt = Lamb(groups, lr=0.00176, betas=(0.9, 0.999), eps=1e-6, weight_decay=0.01, clamp_value=10000.0, debias=True)
     sched = get_linear_schedule_with_warmup(opt, 5000, 125000)
-    ddp = DDP(model, device_ids=[local_rank]) if world > 1 else model
-    # the baseline was measured at 64 samples per micro-step (HF's eager ALBERT keeps far more activations than the
-    # native path); larger values are honoured when they are asked for explicitly
-    seq, mb = args.seq_len, min(args.micro_batch, getattr(args, "ddp_micro_batch", 64) or 64)
-    data = SyntheticMLMBatches(hf_cfg.vocab_size, seq, mb, seed=1234 + rank)
-    resident = [data.to_device(b, device) for b in data.batches]
+    if best or world == 1:
+        ddp = model
+    else:
+        ddp = DDP(model, device_ids=[local_rank])
+        if variant == "fp16hook":
+            from torch.distributed.algorithms.ddp_comm_hooks import default_hooks
+
+            ddp.register_comm_hook(None, default_hooks.fp16_compress_hook)
+
+    # micro-batch: the same as our arm when it fits, else halve until it does (and say so)
+    mb = int(getattr(args, "ddp_micro_batch", 0) or args.micro_batch)
+
+    def fwd_bwd(batch, scale, sync=True):
+        ctx = nullcontext() if (sync or ddp is model) else ddp.no_sync()
+        if best:
+            out = ddp(**batch)
+            (out.loss * scale).backward()
+        else:
+            with ctx, torch.autocast("cuda", dtype=torch.bfloat16):
+                out = ddp(**batch)
+            with ctx:
+                (out.loss * scale).backward()
+        return out.loss.detach()
+
+    while True:
+        try:
+            data = SyntheticMLMBatches(hf_cfg.vocab_size, seq, mb, seed=1234 + rank)
+            resident = [data.to_device(b, device) for b in data.batches]
+            fwd_bwd(resident[0], 1.0)
+            torch.cuda.synchronize()
+            model.zero_grad(set_to_none=True)
+            break
+        except torch.OutOfMemoryError:
+            model.zero_grad(set_to_none=True)
+            torch.cuda.empty_cache()
+            notes.append(f"micro-batch {mb} ran out of memory")
+            mb //= 2
+            if mb < 1:
+                raise
     micro_per_step = max(1, args.target_batch_size // (mb * world))
+
+    # best: CUDA-graph the micro-step when the HF module captures
+    graph, static = None, None
+    if best:
+        try:
+            static = {k: v.clone() for k, v in resident[0].items()}
+            side = torch.cuda.Stream(device)
+            side.wait_stream(torch.cuda.current_stream())
+            with torch.cuda.stream(side):
+                for _ in range(2):
+                    fwd_bwd(static, 1.0 / micro_per_step)
+            torch.cuda.current_stream().wait_stream(side)
+            torch.cuda.synchronize()
+            loss_static = torch.zeros((), device=device)
+            g = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(g):
+                loss_static.copy_(fwd_bwd(static, 1.0 / micro_per_step))
+            graph = g
+            notes.append("micro-step captured in a CUDA graph")
+        except Exception as e:  # pragma: no cover
+            graph = None
+            torch.cuda.synchronize()
+            notes.append(f"CUDA-graph capture failed ({type(e).__name__}); eager")
+        for p in model.parameters():
+            if p.grad is not None:
+                p.grad.zero_()
 
     def step(e2e: bool):
         loss_acc = torch.zeros((), device=device)
         for i in range(micro_per_step):
-            batch = data.to_device(data.next_host(), device) if e2e else resident[i % len(resident)]
-            sync = (i == micro_per_step - 1) or world == 1
-            ctx = nullcontext() if sync else ddp.no_sync()
-            with ctx, torch.autocast("cuda", dtype=torch.bfloat16):
-                out = ddp(**batch)
-            with ctx:
-                (out.loss / micro_per_step).backward()
-            loss_acc += out.loss.detach()
-        torch.nn.utils.clip_grad_norm_(model.parameters(), 1.0)
-        opt.step()
+            batch = data.next_host() if e2e else resident[i % len(resident)]
+            if graph is not None:
+                for k, v in batch.items():
+                    static[k].copy_(v, non_blocking=True)
+                graph.replay()
+                loss_acc += loss_static
+            else:
+                if e2e:
+                    batch = data.to_device(batch, device)
+                loss_acc += fwd_bwd(batch, 1.0 / micro_per_step, sync=(i == micro_per_step - 1))
+        if best:
+            grads = [p.grad for p in model.parameters()]
+            if world > 1:
+                flat = torch.cat([g.reshape(-1) for g in grads])
+                dist.all_reduce(flat)
+                flat.div_(world)
+                off = 0
+                for g in grads:
+                    g.copy_(flat[off:off + g.numel()].view_as(g))
+                    off += g.numel()
+            for m, g in zip(masters, grads):
+                m.grad = g.float()
+            torch.nn.utils.clip_grad_norm_(masters, 1.0)
+            opt.step()
+            with torch.no_grad():
+                for p, m in zip(model.parameters(), masters):
+                    p.copy_(m)
+                    p.grad.zero_()
+        else:
+            torch.nn.utils.clip_grad_norm_(model.parameters(), 1.0)
+            opt.step()
+            opt.zero_grad(set_to_none=True)
         sched.step()
-        opt.zero_grad(set_to_none=True)
         if e2e:
             return float(loss_acc.item())
 
@@ -96,10 +200,12 @@ def main_ddp(args) -> int:
             "metric": "ALBERT-large collaborative MLM samples/sec", "value": round(samples / (dev_ms / 1e3), 2),
             "unit": "samples/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
             "ms_per_step": round(dev_ms / args.steps, 3), "higher_is_better": True, "scaling": "strong",
-            "vs_baseline": None, "dtype": "bf16", "data": "synthetic", "impl": "ddp",
-            "config": {"model": "albert-large-v2 (HF transformers)", "global_batch": micro_per_step * mb * world,
+            "vs_baseline": None, "dtype": "bf16", "data": "synthetic", "impl": "ddp", "variant": variant,
+            "config": {"model": f"albert-large-v2 (HF transformers {transformers.__version__}), vocab {vocab}",
+                       "global_batch": micro_per_step * mb * world,
                        "seq_len": seq, "parallelism": f"ddp{world}", "optimizer": "LAMB (python, restated)",
-                       "micro_batch": mb},
+                       "micro_batch": mb, "attn_implementation": getattr(hf_cfg, "_attn_implementation", None),
+                       "notes": notes},
             "e2e": {"value": round(samples / (wall_ms / 1e3), 2), "unit": "samples/s"},
             "gpu_launches": 0}), flush=True)
     if world > 1:

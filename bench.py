@@ -37,10 +37,15 @@ def parse_args():
     ap.add_argument("--seq-len", type=int, default=512)
     ap.add_argument("--target-batch-size", type=int, default=4096)
     ap.add_argument("--compression", default="FLOAT16")
-    ap.add_argument("--model", default="albert-large-v2", choices=["albert-large-v2", "albert-small", "albert-tiny"])
+    ap.add_argument("--model", default="albert-large-v2",
+                    choices=["albert-large-v2", "sahajbert", "albert-small", "albert-tiny"],
+                    help="sahajbert = ALBERT-large with the 32 000-entry Bengali vocabulary (BASELINE.json config 3)")
     ap.add_argument("--ops", default="native", choices=["native", "torch"], help="linear layers: tcgen05 or torch")
     ap.add_argument("--skip-e2e", action="store_true")
-    ap.add_argument("--ddp-micro-batch", type=int, default=64, help="micro-batch cap of the --impl ddp baseline arm")
+    ap.add_argument("--ddp-micro-batch", type=int, default=0,
+                    help="micro-batch of the --impl ddp arm (0 = the same as ours, halved until it fits in memory)")
+    ap.add_argument("--ddp-variant", default="stock", choices=["stock", "fp16hook", "best"],
+                    help="--impl ddp: stock DDP + autocast, DDP + fp16_compress_hook, or the best torch-only configuration")
     ap.add_argument("--no-cuda-graph", action="store_true", help="run the micro-step eagerly")
     ap.add_argument("--overlap-wgrad", action="store_true", help="launch weight/bias gradient kernels on a side stream")
     return ap.parse_args()
@@ -100,6 +105,20 @@ def main_reference(args):
     return 0
 
 
+def committed_baseline(world: int, args):
+    """The reference publishes no throughput, so `vs_baseline` is taken against the committed
+    same-box torch DDP/NCCL line of the same config (profiles/ddp_n{N}.json, best torch-only variant)."""
+    if args.model != "albert-large-v2" or args.target_batch_size != 4096 or args.seq_len != 512:
+        return None
+    path = os.path.join(os.path.dirname(os.path.abspath(__file__)), "profiles", f"ddp_n{world}.json")
+    try:
+        rows = [json.loads(l) for l in open(path) if l.strip().startswith("{")]
+        row = max(rows, key=lambda r: r["value"])
+        return {"value": row["value"], "impl": "ddp", "variant": row.get("variant"), "file": f"profiles/ddp_n{world}.json"}
+    except Exception:
+        return None
+
+
 def main_ours(args):
     import torch
     import torch.distributed as dist
@@ -136,7 +155,8 @@ def main_ours(args):
         dht = DHT(start=True, initial_peers=[f"127.0.0.1:{port[0]}"])
 
     model_cfg = {"albert-large-v2": AlbertConfig.albert_large_v2, "albert-small": AlbertConfig.small,
-                 "albert-tiny": AlbertConfig.tiny}[args.model]()
+                 "albert-tiny": AlbertConfig.tiny,
+                 "sahajbert": lambda: AlbertConfig.albert_large_v2(vocab_size=32000)}[args.model]()
     seq = min(args.seq_len, model_cfg.max_position_embeddings)
     cfg = PeerConfig(prefix="bench", target_batch_size=args.target_batch_size, micro_batch=args.micro_batch,
                      seq_len=seq, compression=args.compression, target_group_size=max(world, 2),
@@ -215,11 +235,13 @@ def main_ours(args):
         in_sync = all(bool(torch.equal(g, gathered[0])) for g in gathered)
     if rank == 0:
         value = dev["samples"] / (dev["dev_ms"] / 1e3)
+        baseline = committed_baseline(world, args)
         out = {
             "metric": "ALBERT-large collaborative MLM samples/sec", "value": round(value, 2), "unit": "samples/s",
             "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
             "ms_per_step": round(dev["dev_ms"] / args.steps, 3), "higher_is_better": True, "scaling": "strong",
-            "vs_baseline": None, "dtype": "bf16", "data": "synthetic", "impl": "ours",
+            "vs_baseline": round(value / baseline["value"], 3) if baseline else None,
+            "baseline": baseline, "dtype": "bf16", "data": "synthetic", "impl": "ours",
             "config": {"model": args.model, "global_batch": args.target_batch_size, "seq_len": seq,
                        "parallelism": f"dedloc-dp{world}", "optimizer": "LAMB (fused in all-reduce kernel)",
                        "micro_batch": args.micro_batch, "compression": args.compression, "linear_ops": args.ops,
