@@ -99,6 +99,13 @@ extern "C" int dedloc_memcpy_async(void* dst, const void* src, long long bytes, 
   DEDLOC_CUDA_CHECK(cudaMemcpyAsync(dst, src, (size_t)bytes, cudaMemcpyDefault, (cudaStream_t)stream));
   return 0;
 }
+// Strided copy (rows of `width` bytes): pulls the interleaved chunks an owner holds out of its mapped buffer.
+extern "C" int dedloc_memcpy2d_async(void* dst, long long dpitch, const void* src, long long spitch, long long width,
+                                     long long height, void* stream) {
+  DEDLOC_CUDA_CHECK(cudaMemcpy2DAsync(dst, (size_t)dpitch, src, (size_t)spitch, (size_t)width, (size_t)height,
+                                      cudaMemcpyDefault, (cudaStream_t)stream));
+  return 0;
+}
 extern "C" int dedloc_memcpy_peer_async(void* dst, int dst_device, const void* src, int src_device,
                                         long long bytes, void* stream) {
   DEDLOC_CUDA_CHECK(cudaMemcpyPeerAsync(dst, dst_device, src, src_device, (size_t)bytes, (cudaStream_t)stream));

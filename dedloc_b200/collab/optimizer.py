@@ -51,7 +51,8 @@ class CollaborativeOptimizer:
                  throughput: Optional[float] = None, bandwidth: Optional[float] = None,
                  listen_on: str = "127.0.0.1:*", start: bool = True, max_grad_norm: Optional[float] = None,
                  peer_key: Optional[bytes] = None, expected_group_size_from_tracker: bool = True,
-                 replicate_state: bool = True, step_slack_fraction: float = 0.75, **unused_kwargs):
+                 replicate_state: bool = False, replicate_state_every: int = 8,
+                 step_slack_fraction: float = 0.75, **unused_kwargs):
         if compression is not None:  # sgd_collaborative.py:150 spells the kwarg `compression=`
             compression_type = compression
         if isinstance(compression_type, str):
@@ -67,7 +68,16 @@ class CollaborativeOptimizer:
         self.throughput = throughput if throughput is not None else bandwidth
         self.max_grad_norm = max_grad_norm
         self.expected_group_size_from_tracker = expected_group_size_from_tracker
+        # Optimizer moments live with the member that owns a chunk in a round; the fp32 master parameters are
+        # replicated (bit-identical) at all times. `replicate_state=True` pushes the moments to every member in every
+        # round (14 instead of 2 bytes per element leave the owner); the default pushes them every
+        # `replicate_state_every`-th collaborative step, which bounds what a vanished owner can take with it, and
+        # migrates them between owners whenever the group composition changes (_migrate_moments).
         self.replicate_state = replicate_state
+        self.replicate_state_every = int(replicate_state_every)
+        self._moment_owners: Optional[List[bytes]] = None   # handles of last round's owners, in owner order; None = all local
+        self._needs_resync = False                          # set when a round left this peer's state torn
+        self._state_seq = 0                                 # odd while a fused round may be writing this peer's state
         self.unused_kwargs = unused_kwargs
         assert not (client_mode and auxiliary), "an auxiliary peer must accept inbound connections"
 
@@ -87,7 +97,7 @@ class CollaborativeOptimizer:
         self.lineage = "0" * 16
         self.lineage_depth = 0          # optimizer steps behind this lineage: ties go to the longer training history
         self.stats = {"rounds": 0, "failed_rounds": 0, "solo_rounds": 0, "state_downloads": 0, "lineage_resyncs": 0,
-                      "matchmaking_s": 0.0, "averaging_host_s": 0.0}
+                      "matchmaking_s": 0.0, "averaging_host_s": 0.0, "moment_migrations": 0, "torn_rounds": 0}
         self.is_fused = isinstance(opt, FusedOptimizerBase)
         self._params = [p for g in opt.param_groups for p in g["params"]]
         self.on_gpu = bool(self._params) and self._params[0].device.type == "cuda"
@@ -226,6 +236,8 @@ class CollaborativeOptimizer:
 
     @property
     def is_synchronized(self) -> bool:
+        if self._needs_resync:
+            return False
         return self.local_step >= self.collaboration_state.optimizer_step - self.step_tolerance
 
     def is_alive(self) -> bool:
@@ -244,8 +256,9 @@ class CollaborativeOptimizer:
         batch_size = batch_size if batch_size is not None else self.batch_size_per_step
 
         if not self.is_synchronized:
-            logger.warning("%s is behind the collaboration (local step %d, global %d): downloading state",
-                           self.endpoint, self.local_step, self.collaboration_state.optimizer_step)
+            logger.warning("%s %s (local step %d, global %d): downloading state", self.endpoint,
+                           "must resynchronise after a torn round" if self._needs_resync else "is behind the collaboration",
+                           self.local_step, self.collaboration_state.optimizer_step)
             self.load_state_from_peers()
             self.zero_grad()
             return False
@@ -285,6 +298,8 @@ class CollaborativeOptimizer:
             raise RuntimeError("step_aux() is for auxiliary peers")
         if not self.is_synchronized and self.is_fused and self.on_gpu:
             self.load_state_from_peers()
+            if self._needs_resync:
+                return False          # an auxiliary peer with a torn state must not own a shard
         state = self.tracker.refresh_now()
         if not state.ready_for_step or state.num_peers - state.num_aux < 1:
             return False
@@ -322,9 +337,11 @@ class CollaborativeOptimizer:
         blob = {"weight": 0.0 if self.auxiliary else float(self.local_samples_accumulated), "mode": mode,
                 "throughput": None if self.client_mode else float(self.throughput or 1.0),
                 "step": self.local_step, "handle": None, "total": None, "device": None, "lineage": self.lineage,
-                "lineage_depth": self.lineage_depth}
+                "lineage_depth": self.lineage_depth, "host": _host_id()}
         if self.is_fused and self.on_gpu:
-            blob.update(handle=self.opt.buffers.handle, total=self.opt.layout.total,
+            handle = self.opt.buffers.handle
+            # an all-zero handle means cudaIpcGetMemHandle failed on this peer: it cannot be mapped by anybody
+            blob.update(handle=handle if any(handle) else None, total=self.opt.layout.total,
                         device=self.opt.buffers.device)
         return blob
 
@@ -352,6 +369,13 @@ class CollaborativeOptimizer:
                 except AllreduceException as e:
                     self.stats["failed_rounds"] += 1
                     logger.warning("Skipped averaging: averaging round failed with %r", e)
+            if self._needs_resync:
+                # the round died after it had begun to change this peer's state: neither a local step nor a progress
+                # report makes sense on torn parameters. step() downloads a consistent state before anything else.
+                self.stats["torn_rounds"] += 1
+                self._params_parked = False
+                self.stats["averaging_host_s"] += time.perf_counter() - t1
+                return
             if not averaged and not self.auxiliary:
                 self.stats["solo_rounds"] += 1
                 self._run_solo_round()
@@ -400,7 +424,9 @@ class CollaborativeOptimizer:
             tag = (0x20000000 | (self.round_counter & 0x1FFFFFFF))
         return tag or 1
 
-    def _encode_local(self, codec: CompressionType) -> None:
+    def _encode_local(self, codec: CompressionType, in_kernel: bool = False) -> float:
+        """Encode the accumulated gradient (mean over the local micro-steps) into the send buffer; with `in_kernel`
+        the push-based kernel does that itself from the accumulators. Returns the scale."""
         from ..ops import flat_ops
 
         buf = self.opt.buffers
@@ -409,19 +435,30 @@ class CollaborativeOptimizer:
         self._avg_ev1 = torch.cuda.Event(enable_timing=True)
         self._avg_ev0.record(torch.cuda.current_stream(buf.device))
         scale = 1.0 / max(self.local_steps_accumulated, 1)
-        flat_ops.encode(codec, buf.acc, scale, buf.send, buf.aux)
+        if not in_kernel:
+            flat_ops.encode(codec, buf.acc, scale, buf.send, buf.aux)
+        return scale
 
-    def _launch_fused(self, group_spec, codec) -> dict:
-        # (GPU peers serve downloads from the mapped buffer, guarded by the requester's step seqlock)
-        from ..parallel.fused_allreduce import fused_allreduce
+    def _launch_fused(self, group_spec, codec, replicate: bool = True, push_kernel: bool = False,
+                      scale: float = 1.0) -> dict:
+        # GPU peers serve state downloads straight from the mapped buffer; `_state_seq` is odd from before the launch
+        # until the kernel has completed, so a copy that overlaps a round is rejected by the requester (seqlock)
+        from ..parallel.fused_allreduce import fused_allreduce, fused_allreduce_v2
 
         opt = self.opt
         opt.opt_step += 1
         hyper = opt.hyper()
-        hyper.replicate_state = self.replicate_state
-        fused_allreduce(opt.buffers, group_spec, codec, hyper, xgpu_barriers=len(group_spec.bases) > 1)
-        self._avg_ev1.record(torch.cuda.current_stream(opt.buffers.device))
-        status = opt.buffers.read_status()
+        hyper.replicate_state = replicate
+        self._state_seq += 1
+        try:
+            if push_kernel:
+                fused_allreduce_v2(opt.buffers, group_spec, codec, hyper, src_f32=True, scale=scale)
+            else:
+                fused_allreduce(opt.buffers, group_spec, codec, hyper, xgpu_barriers=len(group_spec.bases) > 1)
+            self._avg_ev1.record(torch.cuda.current_stream(opt.buffers.device))
+            status = opt.buffers.read_status()
+        finally:
+            self._state_seq += 1
         self.stats["averaging_device_ms"] = self.stats.get("averaging_device_ms", 0.0) + self._avg_ev0.elapsed_time(self._avg_ev1)
         self.stats["fused_rounds"] = self.stats.get("fused_rounds", 0) + 1
         if status["code"] in (1, 2):
@@ -437,6 +474,7 @@ class CollaborativeOptimizer:
             spec = GroupSpec(bases=[buf.symm.ptr], me=0, weights=[1.0], shards=[(0, self.opt.layout.n_chunks)],
                              slots=[0], tag=self._next_tag())
             status = self._launch_fused(spec, CompressionType.NONE)
+            self._moment_owners = None      # this peer updated every chunk itself: all of its moments are current
             if status["code"] == 4:
                 logger.warning("non-finite gradients: optimizer update skipped at step %d", self.local_step)
             return
@@ -476,7 +514,10 @@ class CollaborativeOptimizer:
         # most members; then the longest training history (a freshly started peer never wins a tie); then endpoint
         agreed = min(votes, key=lambda l: (-len(votes[l]), -depth[l], min(votes[l])))
         self._agreed_depth = depth[agreed]
-        if len(votes) > 1 and self.lineage != agreed and not self.auxiliary:
+        # auxiliary peers own a share in optimizer rounds, so a stale one would push a stale shard to everybody:
+        # they are healed like everyone else
+        heal_me = not self.auxiliary or (self.is_fused and self.on_gpu)
+        if len(votes) > 1 and self.lineage != agreed and heal_me:
             donor = min(votes[agreed])
             logger.warning("%s: parameters diverged from the group (lineage %s vs %s): copying the state of %s",
                            self.endpoint, self.lineage, agreed, donor)
@@ -494,41 +535,106 @@ class CollaborativeOptimizer:
         blobs = list(group.gathered)
         agreed = self._heal_lineage(group, blobs)
         self._round_lineage = self._mix(agreed, "G", blobs[0].get("step"), *sorted(group.endpoints))
-        all_gpu = all(b.get("handle") for b in blobs) and len({b.get("total") for b in blobs}) == 1
+        from .. import lib as native
+
+        handles = [b.get("handle") for b in blobs]
+        all_gpu = (all(h and any(bytes(h)) for h in handles) and len({b.get("total") for b in blobs}) == 1
+                   and len({b.get("host") for b in blobs}) == 1      # CUDA IPC reaches GPUs of one host only
+                   and len(blobs) <= native.MAX_PEERS)
         if self.is_fused and self.on_gpu and all_gpu:
-            return self._run_fused_group_round(group, blobs)
+            try:
+                bases = [self.opt.buffers.peer_base(bytes(h)) for h in handles]
+            except Exception as e:
+                logger.warning("cannot map peer memory (%r): falling back to the socket butterfly", e)
+                bases = None
+            if bases is not None:
+                return self._run_fused_group_round(group, blobs, bases)
         return self._run_socket_group_round(group, blobs)
 
-    def _run_fused_group_round(self, group: GroupInfo, blobs: List[dict]) -> None:
-        from ..parallel.fused_allreduce import GroupSpec
+    def _run_fused_group_round(self, group: GroupInfo, blobs: List[dict], bases: List[int]) -> None:
+        import os
+
+        from ..parallel.fused_allreduce import _FLY_CODECS, GroupSpec, v2_supported
 
         opt, buf = self.opt, self.opt.buffers
         if blobs[0]["total"] != opt.layout.total:
             raise AllreduceException("peers disagree on the flat layout size")
-        try:
-            bases = [buf.peer_base(bytes(b["handle"])) for b in blobs]
-        except Exception as e:
-            raise AllreduceException(f"cannot map peer memory: {e!r}")
         shares = [0.0 if b["mode"] == MODE_CLIENT else 1.0 for b in blobs]
         weights = [float(b["weight"]) for b in blobs]
         if sum(weights) <= 0:
             raise AllreduceException("group has no gradient contributors")
-        self._encode_local(self.compression_type)
+        if sum(shares) <= 0:
+            raise AllreduceException("group has no member that can own a shard")
+        handles = [bytes(b["handle"]) for b in blobs]
+        owners = [h for h, s in zip(handles, shares) if s > 0]
         spec = GroupSpec(bases=bases, me=group.my_index, weights=weights,
                          shards=opt.layout.shard_ranges(shares), slots=list(range(len(blobs))),
                          tag=self._next_tag(group.group_id), timeout_s=self.averaging_timeout)
-        status = self._launch_fused(spec, self.compression_type)
+        push = (os.environ.get("DEDLOC_AR_KERNEL", "push") != "pull"
+                and v2_supported(opt.layout, buf.regions, spec, self.compression_type))
+        # every member derives the same answer from the agreed step, so the whole group replicates in the same rounds
+        step = int(blobs[0].get("step") or 0)
+        replicate = self.replicate_state or (self.replicate_state_every > 0 and step % self.replicate_state_every == 0)
+        if not push:
+            replicate = True      # the pull kernel's contiguous shards follow the group size: keep every replica whole
+        self._migrate_moments(handles, bases)
+        scale = self._encode_local(self.compression_type, in_kernel=push and self.compression_type in _FLY_CODECS)
+        status = self._launch_fused(spec, self.compression_type, replicate=replicate, push_kernel=push, scale=scale)
         code = status["code"]
-        if code == 0:
-            return
-        if code == 4:
-            logger.warning("non-finite averaged gradients: update skipped by the whole group")
+        if code in (0, 4):
+            self._moment_owners = None if replicate else owners
+            if code == 4:
+                logger.warning("non-finite averaged gradients: the update of %d tensor(s) was skipped by the whole "
+                               "group", status.get("nonfinite_chunks", 0))
             return
         if code == 3:
-            # pushes may be torn: force a resync on the next step()
-            self.local_step = -10 ** 6
-            raise AllreduceException("peer vanished during the all-gather; state will be re-downloaded")
+            # the round died between the first and the last update of this peer's parameters
+            self._needs_resync = True
+            raise AllreduceException("peer vanished while updates were in flight; state will be re-downloaded")
         raise AllreduceException(f"fused all-reduce aborted: {status['name']}")
+
+    def _migrate_moments(self, handles: List[bytes], bases: List[int]) -> None:
+        """Moments are current only on the member that owned a chunk in the last round (interleaved: chunk c belongs to
+        owner c mod K). Before a round whose owners may differ, pull every previous owner's chunks out of its mapped
+        buffer, as far as that owner is a member of the new group. Nobody writes moments in the new round before every
+        owner has launched its kernel (UPDATE waits for every owner's norms), and every owner launches after its own
+        pulls, so the copies read a quiescent state."""
+        prev = self._moment_owners
+        buf = self.opt.buffers
+        if prev is None or not buf.regions.m:
+            return
+        mine = buf.handle
+        owners_now = handles
+        if prev == [h for h in owners_now if h in prev] and len(prev) == len(owners_now) and mine in prev:
+            pass  # cheap common case is handled below: same owners in the same order -> nothing to do
+        from .. import lib as native
+        from ..parallel.flat import CHUNK
+
+        same = False
+        # the new owner order is only known to the caller; a conservative test: identical member list
+        if getattr(self, "_last_group_handles", None) == handles:
+            same = True
+        self._last_group_handles = list(handles)
+        if same:
+            return
+        r, K, C = buf.regions, len(prev), buf.layout.n_chunks
+        stream = torch.cuda.current_stream(buf.device)
+        pulled = 0
+        with torch.cuda.device(buf.device):
+            for k, h in enumerate(prev):
+                if h == mine or h not in handles:
+                    continue            # my own chunks are current; an absent owner's chunks stay as stale as they are
+                base = bases[handles.index(h)]
+                rows = (C - k + K - 1) // K
+                if rows <= 0:
+                    continue
+                for off in (r.m, r.v):
+                    native.check(native.lib().dedloc_memcpy2d_async(
+                        buf.symm.ptr + off + k * CHUNK * 4, K * CHUNK * 4, base + off + k * CHUNK * 4, K * CHUNK * 4,
+                        CHUNK * 4, rows, stream.cuda_stream), "moment migration")
+                pulled += 1
+        if pulled:
+            self.stats["moment_migrations"] += 1
 
     def _run_socket_group_round(self, group: GroupInfo, blobs: List[dict]) -> None:
         """Socket butterfly (CPU peers, or a mixed group): average the gradients, then step locally."""

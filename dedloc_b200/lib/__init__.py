@@ -52,6 +52,43 @@ class ARParams(C.Structure):
     ]
 
 
+AR2_MAX_STAGES = 64
+
+
+class AR2Params(C.Structure):
+    """Mirror of DedlocAR2Params (push-based, stage-pipelined all-reduce kernel)."""
+
+    _fields_ = [
+        ("P", C.c_int), ("me", C.c_int), ("mode", C.c_int), ("codec", C.c_int), ("T", C.c_int), ("K", C.c_int),
+        ("tag", C.c_uint32), ("src_f32", C.c_int), ("timeout_ns", C.c_ulonglong),
+        ("nP", C.c_int), ("nR", C.c_int), ("nU", C.c_int), ("nA", C.c_int),
+        ("NS", C.c_int), ("replicate_state", C.c_int),
+        ("Ls", C.c_longlong), ("C", C.c_longlong), ("slot_bytes", C.c_longlong), ("aux_slot_floats", C.c_longlong),
+        ("scale", C.c_float),
+        ("lr", C.c_float), ("beta1", C.c_float), ("beta2", C.c_float), ("eps", C.c_float),
+        ("bias_correction", C.c_float), ("clamp_value", C.c_float), ("momentum", C.c_float), ("trust", C.c_float),
+        ("w", C.c_float * MAX_PEERS),
+        ("owner_of_k", C.c_int * MAX_PEERS),
+        ("kidx", C.c_int * MAX_PEERS),
+        ("acc", C.c_void_p), ("send", C.c_void_p), ("aux", C.c_void_p),
+        ("p32", C.c_void_p), ("p16", C.c_void_p), ("m", C.c_void_p), ("v", C.c_void_p),
+        ("gavg", C.c_void_p), ("chunk_stats", C.c_void_p), ("chunk_tid", C.c_void_p),
+        ("tensor_cbeg", C.c_void_p), ("t_wd", C.c_void_p), ("t_lr_scale", C.c_void_p), ("t_flags", C.c_void_p),
+        ("status", C.c_void_p), ("counters", C.c_void_p),
+        ("stage_in", C.c_void_p * MAX_PEERS),
+        ("aux_in", C.c_void_p * MAX_PEERS),
+        ("delta", C.c_void_p * MAX_PEERS),
+        ("inflag", C.c_void_p * MAX_PEERS),
+        ("outflag", C.c_void_p * MAX_PEERS),
+        ("table", C.c_void_p * MAX_PEERS),
+        ("abort_word", C.c_void_p * MAX_PEERS),
+        ("out32", C.c_void_p * MAX_PEERS),
+        ("out16", C.c_void_p * MAX_PEERS),
+        ("m_all", C.c_void_p * MAX_PEERS),
+        ("v_all", C.c_void_p * MAX_PEERS),
+    ]
+
+
 class GemmArgs(C.Structure):
     """Mirror of DedlocGemmArgs."""
 
@@ -93,6 +130,8 @@ def _declare(lib: C.CDLL) -> None:
     lib.dedloc_memset_async.argtypes = [vp, i, ll, vp]
     lib.dedloc_memcpy_async.argtypes = [vp, vp, ll, vp]
     lib.dedloc_memcpy_peer_async.argtypes = [vp, i, vp, i, ll, vp]
+    lib.dedloc_memcpy2d_async.argtypes = [vp, ll, vp, ll, ll, ll, vp]
+    lib.dedloc_memcpy2d_async.restype = i
     lib.dedloc_sumsq.argtypes = [vp, i, ll, vp, i, vp, vp]
     lib.dedloc_accumulate_clip.argtypes = [vp, vp, i, ll, vp, f, i, vp]
     lib.dedloc_encode.argtypes = [i, vp, ll, f, vp, vp, vp]
@@ -100,6 +139,11 @@ def _declare(lib: C.CDLL) -> None:
     lib.dedloc_codec_aux_floats.restype = ll
     lib.dedloc_codec_payload_bytes_per_elem.argtypes = [i]
     lib.dedloc_fused_allreduce.argtypes = [C.POINTER(ARParams), vp]
+    lib.dedloc_fused_allreduce_v2.argtypes = [C.POINTER(AR2Params), i, vp, vp]
+    lib.dedloc_fused_allreduce_v2.restype = i
+    lib.dedloc_ar2_params_size.restype = i
+    lib.dedloc_ar2_max_ctas.argtypes = [i, i]
+    lib.dedloc_ar2_max_ctas.restype = i
     lib.dedloc_gemm.argtypes = [C.POINTER(GemmArgs), vp]
     lib.dedloc_layernorm_fwd.argtypes = [vp, vp, vp, vp, vp, vp, i, i, f, vp]
     lib.dedloc_layernorm_bwd.argtypes = [vp, vp, vp, vp, vp, vp, vp, vp, i, i, vp]
@@ -162,6 +206,10 @@ def load(required: bool = False) -> Optional[C.CDLL]:
                 raise NativeError(
                     f"ABI mismatch: DedlocARParams is {lib.dedloc_ar_params_size()} bytes in the library, "
                     f"{C.sizeof(ARParams)} in the binding")
+            if lib.dedloc_ar2_params_size() != C.sizeof(AR2Params):
+                raise NativeError(
+                    f"ABI mismatch: DedlocAR2Params is {lib.dedloc_ar2_params_size()} bytes in the library, "
+                    f"{C.sizeof(AR2Params)} in the binding")
             _LIB = lib
             return lib
         except OSError as e:  # e.g. libcudart missing

@@ -39,6 +39,17 @@ class RegionLayout:
     p16: int = 0
     m: int = 0
     v: int = 0
+    state_end: int = 0        # end of the regions a state download copies (p32 .. v)
+    # regions of the push-based kernel (csrc/fused_allreduce_v2.cu)
+    inflag: int = 0
+    outflag: int = 0
+    abort: int = 0
+    table2: int = 0
+    delta: int = 0
+    aux_in: int = 0
+    aux_slot_floats: int = 0
+    stage_in: int = 0
+    stage_bytes: int = 0
     total: int = 0
 
     @classmethod
@@ -63,6 +74,25 @@ class RegionLayout:
             off = _align(off + 4 * n)
             r.v = off
             off = _align(off + 4 * n)
+        r.state_end = off
+        r.inflag = off
+        off = _align(off + 4 * native.AR2_MAX_STAGES * MAX_PEERS)
+        r.outflag = off
+        off = _align(off + 4 * native.AR2_MAX_STAGES * MAX_PEERS)
+        r.abort = off
+        off = _align(off + 256)
+        r.table2 = off
+        off = _align(off + 8 * MAX_PEERS * max(n_tensors, 1) * 2)
+        r.delta = off
+        off = _align(off + 2 * n)
+        r.aux_slot_floats = max(max_aux, 1)
+        r.aux_in = off
+        off = _align(off + 4 * MAX_PEERS * r.aux_slot_floats)
+        # one staging slot per sender: P slots of ceil(C / K) chunks. Sized for fp32 payloads with up to twice as many
+        # senders as owners (client-mode members send but own nothing), plus one chunk of rounding per slot
+        r.stage_bytes = 8 * n + 4 * CHUNK * MAX_PEERS
+        r.stage_in = off
+        off = _align(off + r.stage_bytes)
         r.total = off
         return r
 
@@ -98,6 +128,8 @@ class PeerBuffers:
         self.t_lr_scale = torch.ones(layout.n_tensors, dtype=torch.float32, device=dev)
         self.t_flags = torch.zeros(layout.n_tensors, dtype=torch.int32, device=dev)
         self._status_host = torch.zeros(16, dtype=torch.int32).pin_memory()
+        self.counters = torch.zeros(3 * native.AR2_MAX_STAGES, dtype=torch.int32, device=dev)
+        self.params_dev = torch.zeros(MAX_PEERS * C.sizeof(native.AR2Params), dtype=torch.uint8, device=dev)
 
     @property
     def handle(self) -> bytes:
@@ -109,6 +141,8 @@ class PeerBuffers:
     def read_status(self) -> Dict[str, int]:
         self._status_host.copy_(self.status, non_blocking=False)
         code = int(self._status_host[0])
+        if code == 1 and int(self._status_host[1]) != 0:
+            code = 3      # the push-based kernel gave up after this member had begun to modify its state
         return {"code": code, "name": native.AR_STATUS.get(code, f"unknown_{code}"),
                 "nonfinite_chunks": int(self._status_host[2])}
 
@@ -183,3 +217,177 @@ def fused_allreduce(buf: PeerBuffers, group: GroupSpec, codec: CompressionType, 
     st = stream if stream is not None else torch.cuda.current_stream(buf.device)
     with torch.cuda.device(buf.device):
         native.check(native.lib().dedloc_fused_allreduce(C.byref(p), st.cuda_stream), "fused_allreduce")
+
+
+# ----------------------------------------------------------------------------------------------------------------
+# Push-based, stage-pipelined kernel (csrc/fused_allreduce_v2.cu)
+# ----------------------------------------------------------------------------------------------------------------
+_FLY_CODECS = (CompressionType.NONE, CompressionType.FLOAT16, CompressionType.BFLOAT16)
+_MAX_CTAS: Dict[tuple, int] = {}
+
+
+def _max_ctas(mode: int, codec: CompressionType) -> int:
+    key = (mode, int(codec), torch.cuda.current_device())
+    if key not in _MAX_CTAS:
+        _MAX_CTAS[key] = int(native.lib().dedloc_ar2_max_ctas(mode, int(codec)))
+    return _MAX_CTAS[key]
+
+
+def _role_split(total: int, mode: int, owner: bool, K: int, weights=None) -> tuple:
+    """CTAs per role (PUSH, REDUCE, UPDATE, APPLY), proportional to the bytes each role moves per element."""
+    import os
+
+    if weights is None:
+        env = os.environ.get("DEDLOC_AR2_SPLIT")
+        if env:
+            weights = [float(x) for x in env.split(",")]
+    if mode == native.AR_MEAN:
+        w = list(weights) if weights else [1.0, 1.0, 0.0, 0.0]
+        w[2] = 0.0
+        n_apply = 1                      # one CTA waits for the completion flags
+        if not owner:
+            w[1] = 0.0
+        rest = total - n_apply
+        tot = w[0] + w[1]
+        nR = max(1, int(round(rest * w[1] / tot))) if w[1] > 0 else 0
+        nP = rest - nR
+        return max(nP, 1), nR, 0, n_apply
+    w = list(weights) if weights else [6.0, 2.0 + 16.0 / K, 2.0 + 24.0 / K, 12.0]
+    if not owner:
+        w[1] = w[2] = 0.0
+    tot = sum(w)
+    nR = max(1, int(round(total * w[1] / tot))) if w[1] > 0 else 0
+    nU = max(1, int(round(total * w[2] / tot))) if w[2] > 0 else 0
+    nP = max(1, int(round(total * w[0] / tot)))
+    nA = total - nP - nR - nU
+    assert nA >= 1, (total, nP, nR, nU)
+    return nP, nR, nU, nA
+
+
+def stage_geometry(n_chunks: int, ctas: int) -> tuple:
+    """(NS, Ls): stages of Ls chunks (a multiple of 32, so 8-bit codebook blocks never straddle stages). A stage gives
+    every PUSH / APPLY CTA a few chunks; at most AR2_MAX_STAGES stages."""
+    target = max(32, (2 * ctas + 31) // 32 * 32)
+    ns = min(native.AR2_MAX_STAGES, max(1, (n_chunks + target - 1) // target))
+    ls = ((n_chunks + ns - 1) // ns + 31) // 32 * 32
+    ns = (n_chunks + ls - 1) // ls
+    return ns, ls
+
+
+def v2_supported(layout: FlatLayout, regions: RegionLayout, group: "GroupSpec", codec: CompressionType) -> bool:
+    """The push-based kernel needs >= 2 members, at least one owner and P staging slots that fit the region."""
+    P = len(group.bases)
+    K = sum(1 for b, e in group.shards if e > b)
+    if P < 2 or K < 1 or not regions.stage_in:
+        return False
+    from ..utils.compression import payload_bytes_per_elem
+
+    slot = _align(((layout.n_chunks + K - 1) // K) * CHUNK * payload_bytes_per_elem(codec))
+    return P * slot <= regions.stage_bytes
+
+
+def _fill_v2(p, buf: PeerBuffers, group: GroupSpec, codec: CompressionType, hyper: OptHyper, ctas: int,
+             src_f32: bool, scale: float, write_p16: bool, mean_out32: bool, split=None) -> None:
+    from ..utils.compression import payload_bytes_per_elem
+
+    P = len(group.bases)
+    r, layout = buf.regions, buf.layout
+    owners = [q for q in range(P) if group.shards[q][1] > group.shards[q][0]]
+    K = len(owners)
+    p.P, p.me, p.mode, p.codec, p.T, p.K = P, group.me, hyper.mode, int(codec), layout.n_tensors, K
+    p.tag = (group.tag & 0x7FFFFFFF) or 1
+    p.src_f32 = int(src_f32 and codec in _FLY_CODECS)
+    p.timeout_ns = int(group.timeout_s * 1e9)
+    p.nP, p.nR, p.nU, p.nA = _role_split(ctas, hyper.mode, group.me in owners, K, split)
+    p.NS, p.Ls = stage_geometry(layout.n_chunks, ctas)
+    p.C = layout.n_chunks
+    p.replicate_state = int(hyper.replicate_state)
+    p.slot_bytes = _align(((layout.n_chunks + K - 1) // K) * CHUNK * payload_bytes_per_elem(codec))
+    p.aux_slot_floats = r.aux_slot_floats
+    p.scale = scale
+    p.lr, p.beta1, p.beta2, p.eps = hyper.lr, hyper.beta1, hyper.beta2, hyper.eps
+    p.bias_correction, p.clamp_value = hyper.bias_correction, hyper.clamp_value
+    p.momentum, p.trust = hyper.momentum, hyper.trust
+    wsum = float(sum(group.weights))
+    for q in range(MAX_PEERS):
+        p.kidx[q] = -1
+        p.owner_of_k[q] = 0
+    for k, q in enumerate(owners):
+        p.owner_of_k[k] = q
+        p.kidx[q] = k
+    is_mean = hyper.mode == native.AR_MEAN
+    for q in range(P):
+        base = group.bases[q]
+        p.w[q] = (group.weights[q] / wsum) if wsum > 0 else 0.0
+        p.stage_in[q] = base + r.stage_in
+        p.aux_in[q] = base + r.aux_in
+        p.delta[q] = base + r.delta
+        p.inflag[q] = base + r.inflag
+        p.outflag[q] = base + r.outflag
+        p.table[q] = base + r.table2
+        p.abort_word[q] = base + r.abort
+        p.out32[q] = (base + r.p32) if (is_mean and mean_out32) else None
+        p.out16[q] = (base + r.p16) if (is_mean and write_p16) else None
+        p.m_all[q] = (base + r.m) if r.m else None
+        p.v_all[q] = (base + r.v) if r.v else None
+    own = buf.symm.ptr
+    p.acc = buf.acc.data_ptr()
+    p.send = own + r.send
+    p.aux = own + r.aux
+    p.p32 = own + r.p32
+    p.p16 = (own + r.p16) if write_p16 else None
+    p.m = (own + r.m) if r.m else None
+    p.v = (own + r.v) if r.v else None
+    p.gavg = buf.gavg.data_ptr()
+    p.chunk_stats = buf.chunk_stats.data_ptr()
+    p.chunk_tid = buf.chunk_tid.data_ptr()
+    p.tensor_cbeg = buf.tensor_cbeg.data_ptr()
+    p.t_wd = buf.t_wd.data_ptr()
+    p.t_lr_scale = buf.t_lr_scale.data_ptr()
+    p.t_flags = buf.t_flags.data_ptr()
+    p.status = buf.status.data_ptr()
+    p.counters = buf.counters.data_ptr()
+
+
+def fused_allreduce_v2(buf: PeerBuffers, group: GroupSpec, codec: CompressionType, hyper: OptHyper,
+                       stream: Optional[torch.cuda.Stream] = None, src_f32: bool = True, scale: float = 1.0,
+                       write_p16: bool = True, mean_out32: bool = True, max_ctas: int = 0, split=None) -> None:
+    """Launch the push-based kernel for this peer on `stream` (current stream by default). Asynchronous.
+
+    `group.shards` only says WHO owns a share (non-empty range = owner): ownership is interleaved, chunk c belongs to
+    the (c mod K)-th owner. With `src_f32` and an on-the-fly codec (NONE / FLOAT16 / BFLOAT16) the gradient is encoded
+    from `buf.acc * scale` inside the kernel; otherwise `buf.send` / `buf.aux` must hold the encoded payload."""
+    assert v2_supported(buf.layout, buf.regions, group, codec), "group does not fit the push-based kernel"
+    with torch.cuda.device(buf.device):
+        ctas = _max_ctas(hyper.mode, codec)
+        if max_ctas > 0:
+            ctas = min(ctas, max_ctas)
+        p = native.AR2Params()
+        _fill_v2(p, buf, group, codec, hyper, ctas, src_f32, scale, write_p16, mean_out32, split)
+        st = stream if stream is not None else torch.cuda.current_stream(buf.device)
+        native.check(native.lib().dedloc_fused_allreduce_v2(C.byref(p), 1, buf.params_dev.data_ptr(), st.cuda_stream),
+                     "fused_allreduce_v2")
+
+
+def fused_allreduce_v2_emulated(bufs: Sequence[PeerBuffers], weights: Sequence[float], shards: Sequence[tuple],
+                                codec: CompressionType, hyper: OptHyper, tag: int, src_f32: bool = True,
+                                scale: float = 1.0, write_p16: bool = True, mean_out32: bool = True,
+                                timeout_s: float = 20.0, ctas_per_rank: int = 0, split=None) -> None:
+    """All members of a group as ONE cooperative launch over buffer sets on one GPU (tests, single-GPU soak runs):
+    co-dependent ranks must not be separate launches on one device. The device code is the production code."""
+    P = len(bufs)
+    dev = bufs[0].device
+    with torch.cuda.device(dev):
+        cap = _max_ctas(hyper.mode, codec)
+        ctas = cap // P if ctas_per_rank <= 0 else min(ctas_per_rank, cap // P)
+        assert ctas >= 4, "not enough co-resident CTAs for this many emulated ranks"
+        arr = (native.AR2Params * P)()
+        bases = [b.symm.ptr for b in bufs]
+        for rnk in range(P):
+            g = GroupSpec(bases=bases, me=rnk, weights=list(weights), shards=list(shards), slots=list(range(P)),
+                          tag=tag, timeout_s=timeout_s)
+            assert v2_supported(bufs[rnk].layout, bufs[rnk].regions, g, codec)
+            _fill_v2(arr[rnk], bufs[rnk], g, codec, hyper, ctas, src_f32, scale, write_p16, mean_out32, split)
+        st = torch.cuda.current_stream(dev)
+        native.check(native.lib().dedloc_fused_allreduce_v2(arr, P, bufs[0].params_dev.data_ptr(), st.cuda_stream),
+                     "fused_allreduce_v2 (emulated ranks)")

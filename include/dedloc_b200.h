@@ -34,6 +34,8 @@ int dedloc_memset_async(void* ptr, int value, long long bytes, void* stream);
 int dedloc_memcpy_async(void* dst, const void* src, long long bytes, void* stream);
 int dedloc_memcpy_peer_async(void* dst, int dst_device, const void* src, int src_device, long long bytes,
                              void* stream);
+int dedloc_memcpy2d_async(void* dst, long long dpitch, const void* src, long long spitch, long long width,
+                          long long height, void* stream);
 
 /* ---- flat gradient path (albert/run_trainer.py:279 HF Trainer clip + hivemind grad accumulation) */
 int dedloc_sumsq(const void* x, int is_bf16, long long n, float* scratch, int scratch_floats, float* out,
@@ -89,6 +91,71 @@ typedef struct DedlocARParams {
 
 int dedloc_fused_allreduce(const DedlocARParams* params, void* stream);
 int dedloc_ar_params_size(void);
+
+/* ---- the same operation as a push-based, stage-pipelined dataflow kernel (csrc/fused_allreduce_v2.cu) -------------
+ * Ownership is interleaved (chunk c belongs to owner c % K), the vector is cut into NS stages, and the CTAs of a
+ * launch are split into four roles that run concurrently on different stages:
+ *   PUSH    encode my gradient and store every chunk into its owner's staging slot (posted NVLink writes)
+ *   REDUCE  owner: decode + weighted sum of all staged payloads; MEAN: store the average to every member;
+ *           LAMB/LARS: per-tensor partial norms, published to every member as self-validating {value, tag} words
+ *   UPDATE  owner: trust ratio from the summed norms, moments, and the update DIRECTION (fp16 u for LAMB, bf16
+ *           momentum for LARS) stored to every member's delta buffer
+ *   APPLY   every member: p32 -= scale_t * direction, bf16 mirror, optional row normalisation
+ * Stages are handed from role to role and from GPU to GPU through round-tagged flags; there is no grid-wide or
+ * cross-GPU barrier. fp32 master parameters stay replicated and bit-identical, moments live with the owner
+ * (replicate_state pushes them too). `n_ranks` > 1 runs that many emulated members as one cooperative launch on one
+ * GPU (tests). Same reference call sites as dedloc_fused_allreduce. */
+#define DEDLOC_AR2_MAX_STAGES 64
+typedef struct DedlocAR2Params {
+  int P, me, mode, codec, T, K;               /* members, my index, DEDLOC_AR_*, codec, tensors, owners */
+  uint32_t tag;                               /* non-zero, unique per round */
+  int src_f32;                                /* 1: PUSH encodes acc * scale on the fly (NONE / FLOAT16 / BFLOAT16) */
+  unsigned long long timeout_ns;
+  int nP, nR, nU, nA;                         /* CTAs per role; their sum is the grid of one member */
+  int NS;                                     /* stages */
+  int replicate_state;
+  long long Ls, C;                            /* chunks per stage (multiple of 32), chunks in the vector */
+  long long slot_bytes, aux_slot_floats;      /* staging geometry of one sender slot */
+  float scale;
+  float lr, beta1, beta2, eps, bias_correction, clamp_value, momentum, trust;
+  float w[DEDLOC_MAX_PEERS];
+  int owner_of_k[DEDLOC_MAX_PEERS];           /* member index of owner k */
+  int kidx[DEDLOC_MAX_PEERS];                 /* owner index of member q, -1 = owns nothing */
+  /* local */
+  const float* acc;                           /* fp32 gradient accumulators (src_f32) */
+  const uint8_t* send;                        /* pre-encoded payload + aux (other codecs) */
+  const float* aux;
+  float* p32;
+  uint16_t* p16;
+  float* m;
+  float* v;
+  float* gavg;
+  float* chunk_stats;
+  const int* chunk_tid;
+  const long long* tensor_cbeg;
+  const float* t_wd;
+  const float* t_lr_scale;
+  const int* t_flags;
+  uint32_t* status;                           /* [0] ARStatus [1] state was modified [2] non-finite chunks / skipped tensors */
+  uint32_t* counters;                         /* [3][DEDLOC_AR2_MAX_STAGES], zeroed by the entry point */
+  /* per member (peer memory) */
+  uint8_t* stage_in[DEDLOC_MAX_PEERS];        /* [P slots][slot_bytes] */
+  float* aux_in[DEDLOC_MAX_PEERS];            /* [P slots][aux_slot_floats] */
+  uint16_t* delta[DEDLOC_MAX_PEERS];          /* [C * chunk] update directions */
+  uint32_t* inflag[DEDLOC_MAX_PEERS];         /* [NS][MAX_PEERS] */
+  uint32_t* outflag[DEDLOC_MAX_PEERS];        /* [NS][MAX_PEERS] */
+  unsigned long long* table[DEDLOC_MAX_PEERS];/* [MAX_PEERS owners][T][2] {value, tag} words */
+  uint32_t* abort_word[DEDLOC_MAX_PEERS];
+  float* out32[DEDLOC_MAX_PEERS];             /* MEAN outputs */
+  uint16_t* out16[DEDLOC_MAX_PEERS];
+  float* m_all[DEDLOC_MAX_PEERS];             /* replicate_state targets */
+  float* v_all[DEDLOC_MAX_PEERS];
+} DedlocAR2Params;
+
+/* params: n_ranks structs in HOST memory; params_dev: device scratch of n_ranks * sizeof(DedlocAR2Params) bytes. */
+int dedloc_fused_allreduce_v2(const DedlocAR2Params* params, int n_ranks, void* params_dev, void* stream);
+int dedloc_ar2_params_size(void);
+int dedloc_ar2_max_ctas(int mode, int codec);   /* co-resident CTAs of the kernel on the current device */
 
 /* ---- tcgen05/TMEM/TMA GEMM with fused epilogues (cuBLAS calls under HF AlbertForPreTraining built at
  *      albert/run_trainer.py:64-68 and the VISSL swav_head, swav_prototypes_head.py:64-110) ----------- */

@@ -1,0 +1,18 @@
+"""Host-side planning of the push-based all-reduce kernel: stage geometry and the CTA role split."""
+
+
+def test_stage_geometry_and_role_split():
+    from dedloc_b200 import lib
+    from dedloc_b200.parallel.fused_allreduce import _role_split, stage_geometry
+
+    for n_chunks in (1, 31, 32, 33, 128, 8716, 131072, 10 ** 6):
+        for ctas in (8, 74, 148, 296):
+            ns, ls = stage_geometry(n_chunks, ctas)
+            assert 1 <= ns <= lib.AR2_MAX_STAGES and ls % 32 == 0 and ns * ls >= n_chunks > (ns - 1) * ls
+    for total in (8, 37, 74, 148, 296):
+        for mode in (0, 1, 2):
+            for owner in (True, False):
+                for K in (1, 2, 8, 16):
+                    nP, nR, nU, nA = _role_split(total, mode, owner, K)
+                    assert nP + nR + nU + nA == total and nP >= 1 and nA >= 1
+                    assert (nR >= 1) == owner and (nU >= 1) == (owner and mode != 0)
