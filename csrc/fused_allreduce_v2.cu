@@ -41,7 +41,7 @@ namespace ar2 {
 using Params = DedlocAR2Params;
 constexpr int kThreads = 256;
 constexpr int kMaxS = DEDLOC_AR2_MAX_STAGES;
-constexpr int kUnrollPush = 4;
+constexpr int kUnrollPush = 8;
 constexpr int kUnrollApply = 4;
 constexpr int kFlagStride = DEDLOC_MAX_PEERS;
 
@@ -84,8 +84,9 @@ __device__ __forceinline__ uint32_t ld_relaxed_sys_u32(const uint32_t* p) {
 }
 
 // ---- bounded waits ---------------------------------------------------------------------------------------------
+// status[1] holds the tag of the last round that modified this member's state (no reset between rounds needed)
 __device__ __noinline__ void note_abort(const Params& p) {
-  const uint32_t modified = *(volatile uint32_t*)(p.status + 1);
+  const uint32_t modified = *(volatile uint32_t*)(p.status + 1) == p.tag;
   atomicCAS(p.status, 0u, modified ? 3u : 1u);
 }
 __device__ __noinline__ void raise_abort(const Params& p) {
@@ -98,17 +99,21 @@ __device__ __forceinline__ bool saw_abort(const Params& p) {
   return true;
 }
 // One thread waits until *f == tag. false = this member gives up (timeout here, or somebody raised the abort word).
+// Polls with relaxed loads (an acquire per poll is a system-scope fence per poll, which slows every fence on the
+// chip while CTAs idle); one acquire load orders the data reads after the flag has been seen.
 __device__ bool wait_flag(const uint32_t* f, const Params& p) {
-  if (ld_acquire_sys(f) == p.tag) return true;
-  const uint64_t t0 = globaltimer_ns();
-  for (int spins = 1;; ++spins) {
-    if (ld_acquire_sys(f) == p.tag) return true;
-    if ((spins & 31) == 0) {
-      if (saw_abort(p)) return false;
-      if (globaltimer_ns() - t0 > p.timeout_ns) { raise_abort(p); return false; }
+  if (ld_relaxed_sys_u32(f) != p.tag) {
+    const uint64_t t0 = globaltimer_ns();
+    for (int spins = 1;; ++spins) {
+      if (ld_relaxed_sys_u32(f) == p.tag) break;
+      if ((spins & 31) == 0) {
+        if (saw_abort(p)) return false;
+        if (globaltimer_ns() - t0 > p.timeout_ns) { raise_abort(p); return false; }
+      }
+      __nanosleep(100);
     }
-    __nanosleep(40);
   }
+  return ld_acquire_sys(f) == p.tag;
 }
 // {float value | tag << 32}: the word validates itself, so no fence orders it against anything.
 __device__ bool wait_word(const unsigned long long* w, const Params& p, float& val) {
@@ -122,6 +127,13 @@ __device__ bool wait_word(const unsigned long long* w, const Params& p, float& v
     }
     __nanosleep(40);
   }
+}
+// optional timeline: CTA 0 of every role stamps %globaltimer at up to four points of every stage
+__device__ __forceinline__ void stamp(const Params& p, int role, int b, int s, int slot) {
+  if (p.trace != nullptr && b == 0 && threadIdx.x == 0) p.trace[((size_t)role * kMaxS + s) * 4 + slot] = globaltimer_ns();
+}
+__device__ __forceinline__ void fence_sys(const Params& p) {
+  if (!(p.debug_flags & 1)) __threadfence_system();
 }
 __device__ __forceinline__ unsigned long long pack_word(float v, uint32_t tag) {
   return (unsigned long long)__float_as_uint(v) | ((unsigned long long)tag << 32);
@@ -222,6 +234,7 @@ __device__ void role_push(const Params& p, int b) {
   for (int s = 0; s < p.NS; ++s) {
     const int s0 = (int)(s * p.Ls);
     const int s1 = (int)((s0 + p.Ls < p.C) ? s0 + p.Ls : p.C);
+    stamp(p, 0, b, s, 0);
     for (int c0 = s0 + b; c0 < s1; c0 += p.nP * kUnrollPush) {
       Raw8 raw[kUnrollPush];
 #pragma unroll
@@ -262,13 +275,21 @@ __device__ void role_push(const Params& p, int b) {
         }
       }
     }
-    __syncthreads();
-    if (tid == 0) {
-      __threadfence_system();
+    // The warps of a PUSH CTA never wait for each other: each one moves its 256-element slice of the CTA's chunks
+    // and reports the stage on its own. gpu-scope release by every warp, ONE system-scope fence by the warp that
+    // completes the stage: causality is transitive across scopes, and a system fence per CTA and stage costs
+    // 10-40 us when 147 of them run at once.
+    __syncwarp();
+    stamp(p, 0, b, s, 1);
+    if ((tid & 31) == 0) {
+      __threadfence();
+      stamp(p, 0, b, s, 2);
       const unsigned old = atomicAdd(p.counters + 0 * kMaxS + s, 1u);
-      if (old == (unsigned)p.nP - 1) {
-        __threadfence_system();
+      if (old == (unsigned)p.nP * (kThreads / 32) - 1) {
+        p.counters[0 * kMaxS + s] = 0;     // the last warp of the stage leaves the counter ready for the next round
+        fence_sys(p);
         for (int k = 0; k < K; ++k) st_release_sys(p.inflag[p.owner_of_k[k]] + s * kFlagStride + me, p.tag);
+        if (p.trace) p.trace[((size_t)0 * kMaxS + s) * 4 + 3] = globaltimer_ns();
       }
     }
   }
@@ -284,15 +305,43 @@ __device__ void role_reduce(const Params& p, int b, float* red, float* lut, int*
   int cur_cb = -1;
   const uint8_t* stage = p.stage_in[me];
   const float* auxs = p.aux_in[me];
+  // LAMB / LARS: every thread keeps running sums (sum p^2, sum u^2) over the chunks of ONE tensor; they are folded
+  // into this CTA's slot {a, b, tag} of that tensor when the tensor changes and at the end of every stage. The CTA
+  // that completes a stage adds the slots of all REDUCE CTAs, in CTA order, for the tensors that end in it.
+  float run1 = 0.f, run2 = 0.f;
+  int run_t = -1;
+  auto flush = [&]() {
+    if (run_t < 0) return;
+    const float2 r = block_sum2(run1, run2, red);
+    if (tid == 0) {
+      float4* slot = reinterpret_cast<float4*>(p.chunk_stats) + (size_t)run_t * p.nR + b;
+      float4 cur = *slot;
+      if (__float_as_uint(cur.z) != p.tag) cur = make_float4(0.f, 0.f, __uint_as_float(p.tag), 0.f);
+      cur.x += r.x;
+      cur.y += r.y;
+      *slot = cur;
+    }
+    run1 = 0.f;
+    run2 = 0.f;
+  };
   for (int s = 0; s < p.NS; ++s) {
     const int s0 = (int)(s * p.Ls);
     const int s1 = (int)((s0 + p.Ls < p.C) ? s0 + p.Ls : p.C);
     bool ok = true;
+    stamp(p, 1, b, s, 0);
     if (tid < p.P && p.w[tid] != 0.f) ok = wait_flag(p.inflag[me] + s * kFlagStride + tid, p);
     if (!__syncthreads_and((int)ok)) return;
+    stamp(p, 1, b, s, 1);
     for (int c = first_owned(s0, kme, K) + b * K; c < s1; c += p.nR * K) {
       const long long el = (long long)(c / K) * kChunk + tid * 8;
       const long long e = (long long)c * kChunk + tid * 8;
+      if constexpr (MODE != DEDLOC_AR_MEAN) {
+        const int t = p.chunk_tid[c];
+        if (t != run_t) {
+          flush();
+          run_t = t;
+        }
+      }
       if constexpr (CT::kLut) {
         const int cb = c / kCodecBlockChunks;
         if (cb != cur_cb) {
@@ -376,19 +425,23 @@ __device__ void role_reduce(const Params& p, int b, float* red, float* lut, int*
 #pragma unroll
           for (int i = 0; i < 8; ++i) { n1 = fmaf(pv[i], pv[i], n1); n2 = fmaf(acc[i], acc[i], n2); }
         }
-        const float2 r = block_sum2(n1, n2, red);
-        if (tid == 0) reinterpret_cast<float2*>(p.chunk_stats)[c] = r;
+        run1 += n1;
+        run2 += n2;
       }
     }
     // hand the stage over
+    if constexpr (MODE != DEDLOC_AR_MEAN) flush();
     __syncthreads();
+    stamp(p, 1, b, s, 2);
     if (tid == 0) {
-      if (MODE == DEDLOC_AR_MEAN) __threadfence_system(); else __threadfence();
+      __threadfence();
       const unsigned old = atomicAdd(p.counters + 1 * kMaxS + s, 1u);
       *s_last = (old == (unsigned)p.nR - 1);
       if (*s_last) {
+        p.counters[1 * kMaxS + s] = 0;
+        if (p.trace) p.trace[((size_t)1 * kMaxS + s) * 4 + 3] = globaltimer_ns();
         if (MODE == DEDLOC_AR_MEAN) {
-          __threadfence_system();
+          fence_sys(p);
           for (int q = 0; q < p.P; ++q) st_release_sys(p.outflag[q] + s * kFlagStride + kme, p.tag);
         } else {
           __threadfence();
@@ -405,10 +458,13 @@ __device__ void role_reduce(const Params& p, int b, float* red, float* lut, int*
           if (te > s0 && te <= s1) {
             const int tb = (int)p.tensor_cbeg[t];
             float a = 0.f, bsum = 0.f;
-            for (int c = first_owned(tb, kme, K) + lane * K; c < te; c += 32 * K) {
-              const float2 st = __ldcg(reinterpret_cast<const float2*>(p.chunk_stats) + c);
-              a += st.x;
-              bsum += st.y;
+            (void)tb;
+            for (int i = lane; i < p.nR; i += 32) {
+              const float4 st = __ldcg(reinterpret_cast<const float4*>(p.chunk_stats) + (size_t)t * p.nR + i);
+              if (__float_as_uint(st.z) == p.tag) {   // CTAs that saw no chunk of this tensor have a stale slot
+                a += st.x;
+                bsum += st.y;
+              }
             }
             a = warp_sum(a);
             bsum = warp_sum(bsum);
@@ -437,6 +493,7 @@ __device__ void role_update(const Params& p, int b, float* red) {
   for (int s = 0; s < p.NS; ++s) {
     const int s0 = (int)(s * p.Ls);
     const int s1c = (int)((s0 + p.Ls < p.C) ? s0 + p.Ls : p.C);
+    stamp(p, 2, b, s, 0);
     for (int c = first_owned(s0, kme, K) + b * K; c < s1c; c += p.nU * K) {
       const int t = p.chunk_tid[c];
       if (t != cur_t) {
@@ -446,7 +503,7 @@ __device__ void role_update(const Params& p, int b, float* red) {
       const int tf = p.t_flags[t];
       if ((tf & DEDLOC_TF_FROZEN) || !isfinite(s1) || !isfinite(s2)) continue;   // APPLY uses scale 0 for this tensor
       if (!marked) {
-        if (tid == 0) atomicExch(p.status + 1, 1u);
+        if (tid == 0) atomicExch(p.status + 1, p.tag);
         marked = true;
       }
       const long long e = (long long)c * kChunk + tid * 8;
@@ -504,12 +561,16 @@ __device__ void role_update(const Params& p, int b, float* red) {
       }
     }
     __syncthreads();
+    stamp(p, 2, b, s, 1);
     if (tid == 0) {
-      __threadfence_system();
+      __threadfence();
+      stamp(p, 2, b, s, 2);
       const unsigned old = atomicAdd(p.counters + 2 * kMaxS + s, 1u);
       if (old == (unsigned)p.nU - 1) {
-        __threadfence_system();
+        p.counters[2 * kMaxS + s] = 0;
+        fence_sys(p);
         for (int q = 0; q < p.P; ++q) st_release_sys(p.outflag[q] + s * kFlagStride + kme, p.tag);
+        if (p.trace) p.trace[((size_t)2 * kMaxS + s) * 4 + 3] = globaltimer_ns();
       }
     }
   }
@@ -523,8 +584,10 @@ __device__ void role_apply(const Params& p, int b, float* red) {
     // nothing to apply: the averages were stored straight into the outputs; wait until all of them have landed
     for (int s = 0; s < p.NS; ++s) {
       bool ok = true;
+      stamp(p, 3, b, s, 0);
       if (tid < K) ok = wait_flag(p.outflag[me] + s * kFlagStride + tid, p);
       if (!__syncthreads_and((int)ok)) return;
+      stamp(p, 3, b, s, 1);
     }
     return;
   } else {
@@ -536,8 +599,10 @@ __device__ void role_apply(const Params& p, int b, float* red) {
       const int s0 = (int)(s * p.Ls);
       const int s1 = (int)((s0 + p.Ls < p.C) ? s0 + p.Ls : p.C);
       bool ok = true;
+      stamp(p, 3, b, s, 0);
       if (tid < K) ok = wait_flag(p.outflag[me] + s * kFlagStride + tid, p);
       if (!__syncthreads_and((int)ok)) return;
+      stamp(p, 3, b, s, 1);
       for (int c0 = s0 + b; c0 < s1; c0 += p.nA * kUnrollApply) {
         float sc[kUnrollApply];
         int fl[kUnrollApply];
@@ -586,7 +651,7 @@ __device__ void role_apply(const Params& p, int b, float* red) {
         for (int j = 0; j < kUnrollApply; ++j) {
           if (sc[j] != 0.f) {
             if (!marked) {
-              if (tid == 0) atomicExch(p.status + 1, 1u);
+              if (tid == 0) atomicExch(p.status + 1, p.tag);
               marked = true;
             }
             const long long e = (long long)(c0 + j * p.nA) * kChunk + tid * 8;
@@ -625,6 +690,7 @@ __device__ void role_apply(const Params& p, int b, float* red) {
           }
         }
       }
+      stamp(p, 3, b, s, 2);
     }
     if (skipped && tid == 0) {
       atomicAdd(p.status + 2, skipped);
@@ -634,24 +700,11 @@ __device__ void role_apply(const Params& p, int b, float* red) {
 }
 
 template <int CODEC, int MODE>
-__global__ void __launch_bounds__(kThreads, 2) ar2_kernel(const Params* __restrict__ pa, int ctas_per_rank) {
-  __shared__ Params sp;
-  __shared__ float red[64];
-  __shared__ float lut[CodecTraits<CODEC>::kLut ? DEDLOC_MAX_PEERS * 256 : 1];
-  __shared__ int s_last;
-  const int rank = blockIdx.x / ctas_per_rank;
-  const int b = blockIdx.x % ctas_per_rank;
-  {
-    const uint32_t* src = reinterpret_cast<const uint32_t*>(pa + rank);
-    uint32_t* dst = reinterpret_cast<uint32_t*>(&sp);
-    for (int i = threadIdx.x; i < (int)(sizeof(Params) / 4); i += kThreads) dst[i] = src[i];
-  }
-  __syncthreads();
-  const Params& p = sp;
+__device__ __forceinline__ void run_role(const Params& p, int b, float* red, float* lut, int* s_last) {
   if (b < p.nP) {
     role_push<CODEC>(p, b);
   } else if (b < p.nP + p.nR) {
-    role_reduce<CODEC, MODE>(p, b - p.nP, red, lut, &s_last);
+    role_reduce<CODEC, MODE>(p, b - p.nP, red, lut, s_last);
   } else if (b < p.nP + p.nR + p.nU) {
     if constexpr (MODE != DEDLOC_AR_MEAN) role_update<MODE>(p, b - p.nP - p.nR, red);
   } else {
@@ -659,33 +712,71 @@ __global__ void __launch_bounds__(kThreads, 2) ar2_kernel(const Params* __restri
   }
 }
 
+// Production: one member per launch, its parameters by value (no copy, no memset precedes the launch).
+template <int CODEC, int MODE>
+__global__ void __launch_bounds__(kThreads, 2) ar2_kernel(const __grid_constant__ Params p) {
+  __shared__ float red[64];
+  __shared__ float lut[CodecTraits<CODEC>::kLut ? DEDLOC_MAX_PEERS * 256 : 1];
+  __shared__ int s_last;
+  run_role<CODEC, MODE>(p, blockIdx.x, red, lut, &s_last);
+}
+
+// Tests: several members in one cooperative launch on one GPU; every CTA copies its member's parameters to smem.
+template <int CODEC, int MODE>
+__global__ void __launch_bounds__(kThreads, 2) ar2_kernel_ranks(const Params* __restrict__ pa, int ctas_per_rank) {
+  __shared__ Params sp;
+  __shared__ float red[64];
+  __shared__ float lut[CodecTraits<CODEC>::kLut ? DEDLOC_MAX_PEERS * 256 : 1];
+  __shared__ int s_last;
+  const int rank = blockIdx.x / ctas_per_rank;
+  {
+    const uint32_t* src = reinterpret_cast<const uint32_t*>(pa + rank);
+    uint32_t* dst = reinterpret_cast<uint32_t*>(&sp);
+    for (int i = threadIdx.x; i < (int)(sizeof(Params) / 4); i += kThreads) dst[i] = src[i];
+  }
+  __syncthreads();
+  run_role<CODEC, MODE>(sp, blockIdx.x % ctas_per_rank, red, lut, &s_last);
+}
+
 template <int CODEC, int MODE>
 static int max_ctas() {
-  int dev = 0, sms = 0, occ = 0;
+  int dev = 0, sms = 0, occ = 0, occ_r = 0;
   if (cudaGetDevice(&dev) != cudaSuccess) return 0;
   if (cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess) return 0;
   if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, ar2_kernel<CODEC, MODE>, kThreads, 0) != cudaSuccess) return 0;
+  if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ_r, ar2_kernel_ranks<CODEC, MODE>, kThreads, 0) != cudaSuccess) return 0;
+  if (occ_r < occ) occ = occ_r;
   return sms * (occ > 2 ? 2 : occ);
 }
 
 template <int CODEC, int MODE>
-static int launch(const Params* dev_params, int n_ranks, int ctas_per_rank, cudaStream_t st) {
+static int launch(const Params* host_params, const Params* dev_params, int n_ranks, int ctas_per_rank, cudaStream_t st) {
   const int cap = max_ctas<CODEC, MODE>();
   DEDLOC_REQUIRE(n_ranks * ctas_per_rank <= cap, "fused_allreduce_v2: %d CTAs requested, %d can be co-resident",
                  n_ranks * ctas_per_rank, cap);
-  void* args[] = {(void*)&dev_params, (void*)&ctas_per_rank};
-  DEDLOC_CUDA_CHECK(cudaLaunchCooperativeKernel((const void*)ar2_kernel<CODEC, MODE>, dim3(n_ranks * ctas_per_rank),
-                                                dim3(kThreads), args, 0, st));
+  // a cooperative launch only for its co-residency guarantee (CTAs of different roles wait on each other)
+  if (n_ranks == 1) {
+    void* args[] = {(void*)host_params};
+    DEDLOC_CUDA_CHECK(cudaLaunchCooperativeKernel((const void*)ar2_kernel<CODEC, MODE>, dim3(ctas_per_rank),
+                                                  dim3(kThreads), args, 0, st));
+  } else {
+    DEDLOC_CUDA_CHECK(cudaMemcpyAsync((void*)dev_params, host_params, (size_t)n_ranks * sizeof(Params),
+                                      cudaMemcpyHostToDevice, st));
+    void* args[] = {(void*)&dev_params, (void*)&ctas_per_rank};
+    DEDLOC_CUDA_CHECK(cudaLaunchCooperativeKernel((const void*)ar2_kernel_ranks<CODEC, MODE>,
+                                                  dim3(n_ranks * ctas_per_rank), dim3(kThreads), args, 0, st));
+  }
   count_launch();
   return 0;
 }
 
 template <int MODE>
-static int dispatch(int codec, const Params* dev_params, int n_ranks, int ctas, cudaStream_t st, bool query, int* out) {
+static int dispatch(int codec, const Params* host_params, const Params* dev_params, int n_ranks, int ctas,
+                    cudaStream_t st, bool query, int* out) {
 #define DEDLOC_AR2_CASE(C)                                                   \
   case C:                                                                    \
     if (query) { *out = max_ctas<C, MODE>(); return 0; }                     \
-    return launch<C, MODE>(dev_params, n_ranks, ctas, st);
+    return launch<C, MODE>(host_params, dev_params, n_ranks, ctas, st);
   switch (codec) {
     DEDLOC_AR2_CASE(CODEC_NONE)
     DEDLOC_AR2_CASE(CODEC_FLOAT16)
@@ -700,12 +791,12 @@ static int dispatch(int codec, const Params* dev_params, int n_ranks, int ctas, 
   return DEDLOC_EINVAL;
 }
 
-static int dispatch_mode(int mode, int codec, const Params* dev_params, int n_ranks, int ctas, cudaStream_t st,
-                         bool query, int* out) {
+static int dispatch_mode(int mode, int codec, const Params* host_params, const Params* dev_params, int n_ranks,
+                         int ctas, cudaStream_t st, bool query, int* out) {
   switch (mode) {
-    case DEDLOC_AR_MEAN: return dispatch<DEDLOC_AR_MEAN>(codec, dev_params, n_ranks, ctas, st, query, out);
-    case DEDLOC_AR_LAMB: return dispatch<DEDLOC_AR_LAMB>(codec, dev_params, n_ranks, ctas, st, query, out);
-    case DEDLOC_AR_LARS: return dispatch<DEDLOC_AR_LARS>(codec, dev_params, n_ranks, ctas, st, query, out);
+    case DEDLOC_AR_MEAN: return dispatch<DEDLOC_AR_MEAN>(codec, host_params, dev_params, n_ranks, ctas, st, query, out);
+    case DEDLOC_AR_LAMB: return dispatch<DEDLOC_AR_LAMB>(codec, host_params, dev_params, n_ranks, ctas, st, query, out);
+    case DEDLOC_AR_LARS: return dispatch<DEDLOC_AR_LARS>(codec, host_params, dev_params, n_ranks, ctas, st, query, out);
   }
   set_last_error("fused_allreduce_v2: unknown mode %d", mode);
   return DEDLOC_EINVAL;
@@ -717,7 +808,8 @@ static int dispatch_mode(int mode, int codec, const Params* dev_params, int n_ra
 using namespace dedloc;
 
 extern "C" int dedloc_fused_allreduce_v2(const DedlocAR2Params* params, int n_ranks, void* params_dev, void* stream) {
-  DEDLOC_REQUIRE(params != nullptr && params_dev != nullptr && n_ranks >= 1 && n_ranks <= DEDLOC_MAX_PEERS,
+  DEDLOC_REQUIRE(params != nullptr && (params_dev != nullptr || n_ranks == 1) && n_ranks >= 1 &&
+                     n_ranks <= DEDLOC_MAX_PEERS,
                  "fused_allreduce_v2: bad arguments");
   const DedlocAR2Params& p0 = params[0];
   const int ctas = p0.nP + p0.nR + p0.nU + p0.nA;
@@ -746,17 +838,18 @@ extern "C" int dedloc_fused_allreduce_v2(const DedlocAR2Params* params, int n_ra
     DEDLOC_REQUIRE(p.status && p.counters, "fused_allreduce_v2: status / counters are required");
     DEDLOC_REQUIRE(p.w[p.me] == 0.f || (p.src_f32 ? p.acc != nullptr : p.send != nullptr),
                    "fused_allreduce_v2: a contributing member needs its gradient source");
-    DEDLOC_CUDA_CHECK(cudaMemsetAsync(p.status, 0, 4 * sizeof(uint32_t), st));
-    DEDLOC_CUDA_CHECK(cudaMemsetAsync(p.counters, 0, 3 * DEDLOC_AR2_MAX_STAGES * sizeof(uint32_t), st));
   }
-  DEDLOC_CUDA_CHECK(cudaMemcpyAsync(params_dev, params, (size_t)n_ranks * sizeof(DedlocAR2Params), cudaMemcpyHostToDevice, st));
-  return ar2::dispatch_mode(p0.mode, p0.codec, (const DedlocAR2Params*)params_dev, n_ranks, ctas, st, false, nullptr);
+  // No memset precedes the launch: the stage counters reset themselves (the CTA that completes a stage zeroes its
+  // counter) and the status words are only written on the rare paths (abort, skipped tensors). The caller keeps both
+  // zero otherwise: it clears them after reading a non-zero status (PeerBuffers.read_status).
+  return ar2::dispatch_mode(p0.mode, p0.codec, params, (const DedlocAR2Params*)params_dev, n_ranks, ctas, st, false,
+                            nullptr);
 }
 
 extern "C" int dedloc_ar2_params_size(void) { return (int)sizeof(DedlocAR2Params); }
 
 extern "C" int dedloc_ar2_max_ctas(int mode, int codec) {
   int out = 0;
-  if (ar2::dispatch_mode(mode, codec, nullptr, 0, 0, nullptr, true, &out) != 0) return 0;
+  if (ar2::dispatch_mode(mode, codec, nullptr, nullptr, 0, 0, nullptr, true, &out) != 0) return 0;
   return out;
 }

@@ -72,6 +72,32 @@ class Matchmaking:
     def group_key(self) -> str:
         return f"{self.prefix}_averaging.0b{self.group_bits}"
 
+    # ---------------------------------------------------------------- group bits (the "shuffle around")
+    def num_group_bits(self, num_peers: Optional[int]) -> int:
+        """How many key bits split `num_peers` into buckets of about target_group_size."""
+        if not num_peers or num_peers <= self.target_group_size:
+            return 0
+        import math
+
+        return max(0, math.ceil(math.log2(num_peers / self.target_group_size)))
+
+    def rederive_group_bits(self, group: Optional["GroupInfo"], num_peers: Optional[int]) -> str:
+        """After a round, every member moves to a bucket chosen by hash(group id, its index in the group): members of
+        one group scatter over the buckets, so the next round mixes different peers (hivemind re-derives the bits from
+        the group id for the same reason; contributor_notebook.ipynb cell 3 describes the effect). A peer that found
+        nobody draws its bits at random."""
+        import hashlib
+
+        nbits = self.num_group_bits(num_peers)
+        if nbits == 0:
+            self.group_bits = ""
+        elif group is None:
+            self.group_bits = format(random.getrandbits(nbits), f"0{nbits}b")
+        else:
+            h = hashlib.sha256(group.group_id + group.my_index.to_bytes(4, "little")).digest()
+            self.group_bits = format(int.from_bytes(h[:4], "little") % (1 << nbits), f"0{nbits}b")
+        return self.group_bits
+
     # ---------------------------------------------------------------- leader side
     async def rpc_join_group(self, peer_host: str, payload) -> dict:
         """Long-poll: returns when the round begins (or the request is rejected / the group disbanded)."""
@@ -117,7 +143,16 @@ class Matchmaking:
                 if not self.client_mode:
                     await self.dht.node.store(self.group_key, self.declared_expiration, self.declared_expiration,
                                               subkey=self.endpoint)
-                return await self._search(deadline)
+                found = await self._search(deadline)
+                if found is None and self.group_bits and get_dht_time() < deadline:
+                    # nobody else landed in this bucket: try once more under the common key
+                    self.group_bits = ""
+                    self.declared_expiration = get_dht_time() + self.averaging_expiration
+                    if not self.client_mode:
+                        await self.dht.node.store(self.group_key, self.declared_expiration, self.declared_expiration,
+                                                  subkey=self.endpoint)
+                    found = await self._search(deadline)
+                return found
             finally:
                 self.looking = False
                 if self.assembled is not None and not self.assembled.done():

@@ -38,6 +38,25 @@ logger = logging.getLogger(__name__)
 MODE_NODE, MODE_CLIENT, MODE_AUX = 0, 1, 2
 
 
+def _host_id() -> str:
+    """Identifies the machine: CUDA-IPC peer memory only reaches GPUs of the same host (same boot)."""
+    global _HOST_ID
+    if _HOST_ID is None:
+        import socket
+
+        boot = ""
+        try:
+            with open("/proc/sys/kernel/random/boot_id") as f:
+                boot = f.read().strip()
+        except OSError:
+            pass
+        _HOST_ID = f"{socket.gethostname()}/{boot}"
+    return _HOST_ID
+
+
+_HOST_ID: Optional[str] = None
+
+
 class CollaborativeOptimizer:
     def __init__(self, opt: torch.optim.Optimizer, *, dht: DHT, prefix: str, target_batch_size: int,
                  batch_size_per_step: Optional[int] = None, scheduler=None, min_refresh_period: float = 0.5,
@@ -75,6 +94,8 @@ class CollaborativeOptimizer:
         # migrates them between owners whenever the group composition changes (_migrate_moments).
         self.replicate_state = replicate_state
         self.replicate_state_every = int(replicate_state_every)
+        self.average_diverged_parameters = bool(unused_kwargs.pop("average_diverged_parameters", True))
+        self._pending_param_average = False
         self._moment_owners: Optional[List[bytes]] = None   # handles of last round's owners, in owner order; None = all local
         self._needs_resync = False                          # set when a round left this peer's state torn
         self._state_seq = 0                                 # odd while a fused round may be writing this peer's state
@@ -337,7 +358,8 @@ class CollaborativeOptimizer:
         blob = {"weight": 0.0 if self.auxiliary else float(self.local_samples_accumulated), "mode": mode,
                 "throughput": None if self.client_mode else float(self.throughput or 1.0),
                 "step": self.local_step, "handle": None, "total": None, "device": None, "lineage": self.lineage,
-                "lineage_depth": self.lineage_depth, "host": _host_id()}
+                "lineage_depth": self.lineage_depth, "host": _host_id(),
+                "n_avg_tensors": 0 if (self.is_fused and self.on_gpu) else len(self._averaged_tensors())}
         if self.is_fused and self.on_gpu:
             handle = self.opt.buffers.handle
             # an all-zero handle means cudaIpcGetMemHandle failed on this peer: it cannot be mapped by anybody
@@ -361,6 +383,8 @@ class CollaborativeOptimizer:
             t1 = time.perf_counter()
             self.stats["matchmaking_s"] += t1 - t0
             self.stats["rounds"] += 1
+            # next round's bucket: members of one group scatter, so large collaborations reshuffle every round
+            self._matchmaking.rederive_group_bits(group, state.num_peers)
             averaged = False
             if group is not None and group.group_size > 1:
                 try:
@@ -502,28 +526,49 @@ class CollaborativeOptimizer:
         return h.hexdigest()
 
     def _heal_lineage(self, group: GroupInfo, blobs: List[dict]) -> str:
-        """Agree on ONE lineage for the group (most common, ties by smallest endpoint) and, if ours differs, copy the
-        state of a member that has it. Donors are parked at the first barrier of this very round: their parameters do
-        not change while we copy. Returns the agreed lineage."""
+        """Agree on ONE lineage for the group. Returns it; sets `_pending_param_average` when the members have to
+        average their parameters first.
+
+        * Members that trained in different groups of the previous round (target_group_size < number of peers: the
+          reshuffle of contributor_notebook.ipynb cell 3) or stepped alone after a failed round are at the SAME step
+          with different lineages: nobody's step is thrown away -- the group averages parameters (and, off the GPU,
+          optimizer statistics) before it averages gradients, which is what hivemind's TrainingAverager does in
+          every round.
+        * Members at different steps: the ones behind copy the state of a member of the most advanced lineage
+          (most members, then longest history). Donors are members of this very round: nothing in it modifies their
+          state before every member has launched, so their parameters do not change while we copy."""
+        lins = [str(b.get("lineage", "")) for b in blobs]
+        depths = [int(b.get("lineage_depth", 0) or 0) for b in blobs]
+        steps = [int(b.get("step") or 0) for b in blobs]
+        # auxiliary peers take whatever the trainers agree on
+        voters = [i for i, b in enumerate(blobs) if b.get("mode") != MODE_AUX] or list(range(len(blobs)))
+        distinct = sorted({lins[i] for i in voters})
+        self._pending_param_average = False
+        if len(distinct) > 1 and self.average_diverged_parameters and len({steps[i] for i in voters}) == 1:
+            self._pending_param_average = True
+            self._agreed_depth = max(depths[i] for i in voters)
+            return self._mix("A", *distinct)
         votes: Dict[str, List[str]] = {}
         depth: Dict[str, int] = {}
-        for ep, b in zip(group.endpoints, blobs):
-            lin = str(b.get("lineage", ""))
-            votes.setdefault(lin, []).append(ep)
-            depth[lin] = max(depth.get(lin, 0), int(b.get("lineage_depth", 0) or 0))
+        top = max(steps[i] for i in voters)
+        for i in voters:
+            if steps[i] < top and len(distinct) > 1:
+                continue                                   # a member that is behind does not get to vote
+            votes.setdefault(lins[i], []).append(group.endpoints[i])
+            depth[lins[i]] = max(depth.get(lins[i], 0), depths[i])
         # most members; then the longest training history (a freshly started peer never wins a tie); then endpoint
         agreed = min(votes, key=lambda l: (-len(votes[l]), -depth[l], min(votes[l])))
         self._agreed_depth = depth[agreed]
-        # auxiliary peers own a share in optimizer rounds, so a stale one would push a stale shard to everybody:
-        # they are healed like everyone else
+        # auxiliary GPU peers own a share in optimizer rounds, so a stale one would push a stale shard to everybody:
+        # they are healed like everyone else; a CPU auxiliary peer only relays and keeps no parameters worth healing
         heal_me = not self.auxiliary or (self.is_fused and self.on_gpu)
-        if len(votes) > 1 and self.lineage != agreed and heal_me:
+        if self.lineage != agreed and heal_me and (len(distinct) > 1 or self.auxiliary):
             donor = min(votes[agreed])
             logger.warning("%s: parameters diverged from the group (lineage %s vs %s): copying the state of %s",
                            self.endpoint, self.lineage, agreed, donor)
             ok = False
             try:
-                ok = self._download_from(donor, bool(self.is_fused and self.on_gpu))
+                ok = self._download_from(donor, bool(self.is_fused and self.on_gpu), in_round=True)
             except Exception as e:
                 logger.warning("lineage resync from %s failed: %r", donor, e)
             if not ok:
@@ -541,15 +586,79 @@ class CollaborativeOptimizer:
         all_gpu = (all(h and any(bytes(h)) for h in handles) and len({b.get("total") for b in blobs}) == 1
                    and len({b.get("host") for b in blobs}) == 1      # CUDA IPC reaches GPUs of one host only
                    and len(blobs) <= native.MAX_PEERS)
+        bases = None
         if self.is_fused and self.on_gpu and all_gpu:
             try:
                 bases = [self.opt.buffers.peer_base(bytes(h)) for h in handles]
             except Exception as e:
                 logger.warning("cannot map peer memory (%r): falling back to the socket butterfly", e)
                 bases = None
-            if bases is not None:
-                return self._run_fused_group_round(group, blobs, bases)
+        if self._pending_param_average:
+            self._average_parameters(group, blobs, bases)
+            self.lineage, self.lineage_depth = agreed, self._agreed_depth
+            self.stats["parameter_averagings"] = self.stats.get("parameter_averagings", 0) + 1
+        if bases is not None:
+            return self._run_fused_group_round(group, blobs, bases)
         return self._run_socket_group_round(group, blobs)
+
+    # ---- parameter averaging (H4): merges the work of groups that stepped side by side -----------------------------
+    def _averaged_tensors(self) -> List[torch.Tensor]:
+        """Parameters, then every floating-point optimizer statistic, in a fixed order (generic / CPU path)."""
+        out = [p.data for p in self._params]
+        for p in self._params:
+            st = self.opt.state.get(p, {}) if hasattr(self.opt, "state") else {}
+            for key in sorted(st):
+                v = st[key]
+                if isinstance(v, torch.Tensor) and v.is_floating_point() and v.shape == p.shape:
+                    out.append(v)
+        return out
+
+    def _average_parameters(self, group: GroupInfo, blobs: List[dict], bases: Optional[List[int]]) -> None:
+        weights = [0.0 if b.get("mode") == MODE_AUX else 1.0 for b in blobs]
+        if bases is not None:
+            from ..parallel.fused_allreduce import GroupSpec, fused_average_parameters, v2_supported
+
+            opt, buf = self.opt, self.opt.buffers
+            shares = [0.0 if b["mode"] == MODE_CLIENT else 1.0 for b in blobs]
+            base_tag = (int.from_bytes(group.group_id[4:8], "little") & 0x3FFFFFF0) or 16
+            spec = GroupSpec(bases=bases, me=group.my_index, weights=weights, shards=opt.layout.shard_ranges(shares),
+                             slots=list(range(len(blobs))), tag=base_tag, timeout_s=self.averaging_timeout)
+            if not v2_supported(opt.layout, buf.regions, spec, CompressionType.NONE):
+                raise AllreduceException("parameter averaging needs the push-based kernel")
+            self._state_seq += 1
+            try:
+                fused_average_parameters(buf, spec)
+                status = buf.read_status()
+            finally:
+                self._state_seq += 1
+            if status["code"] != 0:
+                if status["code"] == 3:
+                    self._needs_resync = True
+                raise AllreduceException(f"parameter averaging aborted: {status['name']}")
+            return
+        from ..parallel.flat import FlatLayout
+
+        if self.is_fused and self.on_gpu:
+            raise AllreduceException("parameter averaging between GPU and CPU peers is not supported")
+        tensors = self._averaged_tensors()
+        counts = {int(b.get("n_avg_tensors") or 0) for b in blobs if b.get("mode") != MODE_AUX}
+        if len(counts) > 1:
+            tensors = [p.data for p in self._params]        # somebody has no optimizer statistics yet: parameters only
+        layout = FlatLayout([t.shape for t in tensors])
+        flat = layout.pack([t.float() for t in tensors], dtype=torch.float32, device="cpu")
+        throughputs = [b["throughput"] if b["mode"] != MODE_CLIENT else None for b in blobs]
+        try:
+            averaged = self.dht.run_coroutine(
+                lambda dht, node: self._cpu_averager.allreduce(group, flat, weights, throughputs, phase="params"))
+        except AllreduceException:
+            raise
+        except Exception as e:
+            raise AllreduceException(repr(e))
+        if self.auxiliary:
+            return
+        with torch.no_grad():
+            for t, src in zip(tensors, layout.views(averaged)):
+                t.copy_(src.to(t.dtype))
 
     def _run_fused_group_round(self, group: GroupInfo, blobs: List[dict], bases: List[int]) -> None:
         import os
@@ -577,7 +686,7 @@ class CollaborativeOptimizer:
         replicate = self.replicate_state or (self.replicate_state_every > 0 and step % self.replicate_state_every == 0)
         if not push:
             replicate = True      # the pull kernel's contiguous shards follow the group size: keep every replica whole
-        self._migrate_moments(handles, bases)
+        self._migrate_moments(handles, bases, None if replicate else owners)
         scale = self._encode_local(self.compression_type, in_kernel=push and self.compression_type in _FLY_CODECS)
         status = self._launch_fused(spec, self.compression_type, replicate=replicate, push_kernel=push, scale=scale)
         code = status["code"]
@@ -593,30 +702,20 @@ class CollaborativeOptimizer:
             raise AllreduceException("peer vanished while updates were in flight; state will be re-downloaded")
         raise AllreduceException(f"fused all-reduce aborted: {status['name']}")
 
-    def _migrate_moments(self, handles: List[bytes], bases: List[int]) -> None:
+    def _migrate_moments(self, handles: List[bytes], bases: List[int], new_owners: Optional[List[bytes]] = None) -> None:
         """Moments are current only on the member that owned a chunk in the last round (interleaved: chunk c belongs to
-        owner c mod K). Before a round whose owners may differ, pull every previous owner's chunks out of its mapped
-        buffer, as far as that owner is a member of the new group. Nobody writes moments in the new round before every
-        owner has launched its kernel (UPDATE waits for every owner's norms), and every owner launches after its own
+        owner c mod K). Before a round whose owners differ, pull every previous owner's chunks out of its mapped buffer,
+        as far as that owner is a member of the new group. Nobody writes moments in the new round before every owner
+        has launched its kernel (UPDATE waits for every owner's norm words), and every owner launches after its own
         pulls, so the copies read a quiescent state."""
         prev = self._moment_owners
         buf = self.opt.buffers
-        if prev is None or not buf.regions.m:
-            return
-        mine = buf.handle
-        owners_now = handles
-        if prev == [h for h in owners_now if h in prev] and len(prev) == len(owners_now) and mine in prev:
-            pass  # cheap common case is handled below: same owners in the same order -> nothing to do
+        if prev is None or not buf.regions.m or (new_owners is not None and new_owners == prev):
+            return        # everything is local, or the same owners in the same order keep their chunks
         from .. import lib as native
         from ..parallel.flat import CHUNK
 
-        same = False
-        # the new owner order is only known to the caller; a conservative test: identical member list
-        if getattr(self, "_last_group_handles", None) == handles:
-            same = True
-        self._last_group_handles = list(handles)
-        if same:
-            return
+        mine = buf.handle
         r, K, C = buf.regions, len(prev), buf.layout.n_chunks
         stream = torch.cuda.current_stream(buf.device)
         pulled = 0
@@ -706,28 +805,30 @@ class CollaborativeOptimizer:
             raise RuntimeError("this peer does not share its state")
         meta = {"local_step": self.local_step, "fused": bool(self.is_fused and self.on_gpu), "handle": None,
                 "total": None, "opt_step": getattr(self.opt, "opt_step", None), "lineage": self.lineage,
-                "lineage_depth": self.lineage_depth}
+                "lineage_depth": self.lineage_depth, "seq": self._state_seq, "host": _host_id(),
+                "torn": bool(self._needs_resync),
+                "moment_owners": None if self._moment_owners is None else list(self._moment_owners)}
+        if self._needs_resync:
+            raise RuntimeError("this peer's own state is torn; ask somebody else")
         if meta["fused"]:
             meta.update(handle=self.opt.buffers.handle, total=self.opt.layout.total)
         if payload.get("meta_only") or (meta["fused"] and payload.get("can_map")):
             return meta
-        # host path: serialise parameters + optimizer state under the state lock (consistent snapshot)
-        import io
+        # host path: parameters + optimizer state as raw tensor bytes (never pickled: the receiver may be anybody)
+        from ..utils.serialization import pack_state
 
-        def snapshot() -> bytes:
+        def snapshot():
             while True:
                 locked = self.state_lock.acquire(timeout=0.05)
                 if locked or self._params_parked:
                     break
             try:
                 step_before = self.local_step
-                blob = {"params": [p.detach().float().cpu().clone() for p in self._params],
-                        "opt": self.opt.state_dict()}
-                bio = io.BytesIO()
-                torch.save(blob, bio)
+                blob = pack_state({"params": [p.detach().float().cpu().clone() for p in self._params],
+                                   "opt": self.opt.state_dict()})
                 if not locked and (not self._params_parked or self.local_step != step_before):
                     raise RuntimeError("state changed while it was being copied; retry")
-                return bio.getvalue()
+                return blob
             finally:
                 if locked:
                     self.state_lock.release()
@@ -762,17 +863,28 @@ class CollaborativeOptimizer:
             logger.warning("could not load state from any of %d peers", len(donors))
         else:
             logger.info("no peers share state yet; keeping the local state")
-        # nobody to learn from: adopt the collaboration's step so that we are not "behind" forever
+        # nobody to learn from: adopt the collaboration's step so that we are not "behind" forever. A torn state that
+        # nobody can replace is kept (its parameters are finite and close to every other replica); training goes on
+        # and the lineage check heals the difference as soon as a consistent peer is in reach.
         self.local_step = max(self.local_step, self.collaboration_state.optimizer_step)
+        if self._needs_resync:
+            self._needs_resync = False
+            self.lineage = self._mix(self.lineage, "T", self.local_step, self.endpoint)
         return False
 
     def _call(self, endpoint: str, method: str, payload: dict, timeout: float):
         return asyncio.run_coroutine_threadsafe(self._client.call(endpoint, method, payload, timeout),
                                                 self.dht.loop).result()
 
-    def _download_from(self, endpoint: str, can_map: bool) -> bool:
+    def _download_from(self, endpoint: str, can_map: bool, in_round: bool = False) -> bool:
+        """`in_round`: the donor is a member of the round this peer is about to join (lineage healing). Its kernel may
+        already be waiting for us -- nothing in that round modifies anybody's state before every member has launched
+        (every member either sends a gradient or owns a share) -- so an odd sequence number is fine as long as it
+        does not move."""
         meta = self._call(endpoint, "download_state", {"can_map": can_map}, self.averaging_timeout)
-        if meta.get("fused") and can_map and meta.get("handle") and meta["total"] == self.opt.layout.total:
+        handle = meta.get("handle")
+        mappable = bool(handle) and any(bytes(handle)) and meta.get("host") == _host_id()
+        if meta.get("fused") and can_map and mappable and meta["total"] == self.opt.layout.total:
             # NVLink path: map the donor's symmetric buffer and copy master params, bf16 mirror and moments
             buf = self.opt.buffers
             r = buf.regions
@@ -783,24 +895,37 @@ class CollaborativeOptimizer:
                 stream = torch.cuda.current_stream(buf.device)
                 with torch.cuda.device(buf.device):
                     native.check(native.lib().dedloc_memcpy_async(buf.symm.ptr + r.p32, base + r.p32,
-                                                                  r.total - r.p32, stream.cuda_stream),
+                                                                  r.state_end - r.p32, stream.cuda_stream),
                                  "state copy")
+                    self._overlay_moments(meta, buf, stream)
                 stream.synchronize()
                 after = self._call(endpoint, "download_state", {"meta_only": True}, self.averaging_timeout)
-                if after["local_step"] == meta["local_step"]:   # donor did not step while we were copying
+                # seqlock: the donor's sequence number is odd while one of its rounds may be writing, and moves on
+                # with every round; both reads must show the same even value (and the same step)
+                quiet = (after.get("seq") == meta.get("seq") and after.get("opt_step") == meta.get("opt_step")
+                         and (in_round or int(meta.get("seq") or 0) % 2 == 0))
+                if after["local_step"] == meta["local_step"] and quiet:
                     self.local_step = int(meta["local_step"])
                     if meta.get("opt_step") is not None:
                         self.opt.opt_step = int(meta["opt_step"])
                     self.lineage = str(meta.get("lineage", self.lineage))
                     self.lineage_depth = int(meta.get("lineage_depth", self.lineage_depth) or 0)
+                    self._moment_owners = None
+                    self._needs_resync = False
                     return True
                 meta = after
             return False
         if "blob" not in meta:
             meta = self._call(endpoint, "download_state", {"can_map": False}, self.averaging_timeout * 4)
-        import io
+        from ..utils.serialization import unpack_state
 
-        blob = torch.load(io.BytesIO(meta["blob"]), map_location="cpu", weights_only=False)
+        blob = unpack_state(meta["blob"])
+        if not isinstance(blob, dict) or not isinstance(blob.get("params"), list):
+            raise ValueError("malformed state message")
+        if len(blob["params"]) != len(self._params) or any(
+                not isinstance(src, torch.Tensor) or tuple(src.shape) != tuple(p.shape) or not src.is_floating_point()
+                for src, p in zip(blob["params"], self._params)):
+            raise ValueError("the donor's parameters do not match this model")
         with self.state_lock, torch.no_grad():
             if self.is_fused and self.on_gpu:
                 views32 = self.opt.layout.views(self.opt.buffers.p32)
@@ -818,4 +943,36 @@ class CollaborativeOptimizer:
             self.local_step = int(meta["local_step"])
             self.lineage = str(meta.get("lineage", self.lineage))
             self.lineage_depth = int(meta.get("lineage_depth", self.lineage_depth) or 0)
+            self._moment_owners = None
+            self._needs_resync = False
         return True
+
+    def _overlay_moments(self, meta: dict, buf, stream) -> None:
+        """The donor's moments are current only for the chunks it owned in its last round; the other owners of that
+        round hold the rest. Pull their chunks too where their buffers can be mapped (same host, still alive)."""
+        owners = meta.get("moment_owners")
+        if not owners or not buf.regions.m:
+            return
+        from .. import lib as native
+        from ..parallel.flat import CHUNK
+
+        r, K, C = buf.regions, len(owners), buf.layout.n_chunks
+        donor = bytes(meta["handle"])
+        for k, h in enumerate(owners):
+            h = bytes(h)
+            if h == donor:
+                continue
+            rows = (C - k + K - 1) // K
+            if rows <= 0:
+                continue
+            src_is_me = h == buf.handle
+            try:
+                base = buf.symm.ptr if src_is_me else buf.peer_base(h)
+            except Exception:
+                continue          # that owner is gone: its chunks keep the donor's (older) values
+            if src_is_me:
+                continue          # my own stale copy is no better than the donor's
+            for off in (r.m, r.v):
+                native.check(native.lib().dedloc_memcpy2d_async(
+                    buf.symm.ptr + off + k * CHUNK * 4, K * CHUNK * 4, base + off + k * CHUNK * 4, K * CHUNK * 4,
+                    CHUNK * 4, rows, stream.cuda_stream), "moment overlay")

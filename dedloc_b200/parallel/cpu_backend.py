@@ -64,6 +64,7 @@ class _RoundState:
         self.received: Dict[int, torch.Tensor] = {}
         self.remaining = set(range(group.group_size)) - {group.my_index}
         self.done = asyncio.get_event_loop().create_future()
+        self.codec: Optional[CompressionType] = None       # codec of this round's deltas (None = the averager's)
 
     def add(self, sender: int, decoded: torch.Tensor, weight: float) -> None:
         if sender not in self.remaining:
@@ -88,7 +89,8 @@ class CPUAverager:
             server.handlers["allreduce_part"] = self.rpc_allreduce_part
 
     async def rpc_allreduce_part(self, peer_host: str, payload) -> bytes:
-        gid, sender = bytes(payload["group_id"]), payload["sender"]
+        # a group may run several reductions in one round (parameters, then gradients): the phase is part of the key
+        gid, sender = bytes(payload["group_id"]) + str(payload.get("phase") or "").encode(), payload["sender"]
         enc = comp.from_bytes(payload["data"])
         decoded = comp.decode(enc)
         deadline = asyncio.get_event_loop().time() + self.timeout
@@ -100,21 +102,27 @@ class CPUAverager:
         state.add(sender, decoded, state.weights[sender])
         average = await asyncio.wait_for(asyncio.shield(state.done), self.timeout)
         delta = average - decoded
-        return comp.to_bytes(comp.encode(delta, self._delta_codec()))
+        return comp.to_bytes(comp.encode(delta, state.codec if state.codec is not None else self._delta_codec()))
 
     def _delta_codec(self) -> CompressionType:
         return self.compression
 
     async def allreduce(self, group: GroupInfo, flat: torch.Tensor, weights: List[float],
-                        throughputs: List[Optional[float]]) -> torch.Tensor:
-        """flat: padded fp32 vector (multiple of CHUNK). Returns the weighted average (same shape)."""
+                        throughputs: List[Optional[float]], phase: str = "",
+                        compression: Optional[CompressionType] = None) -> torch.Tensor:
+        """flat: padded fp32 vector (multiple of CHUNK). Returns the weighted average (same shape). `phase` tells
+        apart several reductions of one group; `compression` overrides the wire codec (parameters travel lossless)."""
+        if phase == "params" and compression is None:
+            compression = CompressionType.NONE
+        codec = self.compression if compression is None else CompressionType(compression)
         assert flat.dtype == torch.float32 and flat.numel() % CHUNK == 0
         P, me = group.group_size, group.my_index
         counts = load_balance_peers(flat.numel() // CHUNK, throughputs)
         parts = [(b * CHUNK, e * CHUNK) for b, e in parts_from_counts(counts)]
-        gid = group.group_id
+        gid = group.group_id + phase.encode()
         mb, me_ = parts[me]
         state = _RoundState(group, weights, flat[mb:me_], weights[me])
+        state.codec = codec
         if not state.remaining and not state.done.done():
             state.done.set_result(state.acc / max(state.total_weight, 1e-30))
         self.rounds[gid] = state
@@ -124,10 +132,11 @@ class CPUAverager:
                 b, e = parts[j]
                 if e == b:
                     return
-                enc = comp.encode(flat[b:e], self.compression)
+                enc = comp.encode(flat[b:e], codec)
                 sent = comp.decode(enc)  # what the owner will see from us
                 raw = await self.client.call(group.endpoints[j], "allreduce_part",
-                                             {"group_id": gid, "sender": me, "data": comp.to_bytes(enc)},
+                                             {"group_id": group.group_id, "phase": phase, "sender": me,
+                                              "data": comp.to_bytes(enc)},
                                              timeout=self.timeout)
                 delta = comp.decode(comp.from_bytes(raw))
                 out[b:e] = sent + delta

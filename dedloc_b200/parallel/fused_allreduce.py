@@ -9,6 +9,7 @@ averaging round (members, weights, shard ownership) as agreed by matchmaking (co
 from __future__ import annotations
 
 import ctypes as C
+import os
 from dataclasses import dataclass, field
 from typing import Dict, List, Optional, Sequence
 
@@ -118,7 +119,11 @@ class PeerBuffers:
         # local (never addressed by peers)
         self.acc = torch.zeros(n, dtype=torch.float32, device=dev)       # gradient accumulators (H3 step 2)
         self.gavg = torch.zeros(n, dtype=torch.float32, device=dev)      # averaged gradient of my shard
-        self.chunk_stats = torch.zeros(layout.n_chunks * 2, dtype=torch.float32, device=dev)
+        # per-chunk partial norms: [chunk][2] for the pull kernel, [chunk][8 warps][2] for the push kernel
+        # partial norms: [chunk][2] for the pull kernel; [tensor][REDUCE CTA]{a, b, tag, -} for the push kernel
+        self.chunk_stats = torch.zeros(max(layout.n_chunks * 2, layout.n_tensors * 4 * 304), dtype=torch.float32,
+                                       device=dev)
+        self._v2_cache: Dict[tuple, object] = {}
         self.status = torch.zeros(16, dtype=torch.int32, device=dev)
         self.norm_scratch = torch.zeros(2048, dtype=torch.float32, device=dev)
         self.normsq = torch.zeros(1, dtype=torch.float32, device=dev)
@@ -129,6 +134,7 @@ class PeerBuffers:
         self.t_flags = torch.zeros(layout.n_tensors, dtype=torch.int32, device=dev)
         self._status_host = torch.zeros(16, dtype=torch.int32).pin_memory()
         self.counters = torch.zeros(3 * native.AR2_MAX_STAGES, dtype=torch.int32, device=dev)
+        self.last_tag = 0          # tag of the last push-kernel launch (status[1] holds it once state was modified)
         self.params_dev = torch.zeros(MAX_PEERS * C.sizeof(native.AR2Params), dtype=torch.uint8, device=dev)
 
     @property
@@ -141,8 +147,13 @@ class PeerBuffers:
     def read_status(self) -> Dict[str, int]:
         self._status_host.copy_(self.status, non_blocking=False)
         code = int(self._status_host[0])
-        if code == 1 and int(self._status_host[1]) != 0:
+        if code == 1 and self.last_tag and (int(self._status_host[1]) & 0xFFFFFFFF) == self.last_tag:
             code = 3      # the push-based kernel gave up after this member had begun to modify its state
+        if code != 0 or int(self._status_host[2]) != 0:
+            # the push-based kernel is launched without a memset: leave status and stage counters clean for the next
+            # round (a round that was abandoned half-way leaves counters behind)
+            self.status[0:4].zero_()
+            self.counters.zero_()
         return {"code": code, "name": native.AR_STATUS.get(code, f"unknown_{code}"),
                 "nonfinite_chunks": int(self._status_host[2])}
 
@@ -264,11 +275,18 @@ def _role_split(total: int, mode: int, owner: bool, K: int, weights=None) -> tup
     return nP, nR, nU, nA
 
 
-def stage_geometry(n_chunks: int, ctas: int) -> tuple:
-    """(NS, Ls): stages of Ls chunks (a multiple of 32, so 8-bit codebook blocks never straddle stages). A stage gives
-    every PUSH / APPLY CTA a few chunks; at most AR2_MAX_STAGES stages."""
-    target = max(32, (2 * ctas + 31) // 32 * 32)
+def stage_geometry(n_chunks: int, ctas: int, bytes_per_elem: int = 2) -> tuple:
+    """(NS, Ls): stages of Ls chunks (a multiple of 32, so 8-bit codebook blocks never straddle stages). Every stage
+    hand-over costs a system-scope fence and a flag round trip (~10 us), so a stage carries at least
+    DEDLOC_AR2_STAGE_MB (default 4) MB of payload and at least two chunks per CTA; at most AR2_MAX_STAGES stages."""
+    import os
+
+    stage_mb = float(os.environ.get("DEDLOC_AR2_STAGE_MB", "4"))
+    by_bytes = int(stage_mb * 2 ** 20 / (CHUNK * bytes_per_elem))
+    target = max(32, (max(2 * ctas, by_bytes) + 31) // 32 * 32)
     ns = min(native.AR2_MAX_STAGES, max(1, (n_chunks + target - 1) // target))
+    if os.environ.get("DEDLOC_AR2_STAGES"):
+        ns = max(1, min(native.AR2_MAX_STAGES, int(os.environ["DEDLOC_AR2_STAGES"])))
     ls = ((n_chunks + ns - 1) // ns + 31) // 32 * 32
     ns = (n_chunks + ls - 1) // ls
     return ns, ls
@@ -299,7 +317,8 @@ def _fill_v2(p, buf: PeerBuffers, group: GroupSpec, codec: CompressionType, hype
     p.src_f32 = int(src_f32 and codec in _FLY_CODECS)
     p.timeout_ns = int(group.timeout_s * 1e9)
     p.nP, p.nR, p.nU, p.nA = _role_split(ctas, hyper.mode, group.me in owners, K, split)
-    p.NS, p.Ls = stage_geometry(layout.n_chunks, ctas)
+    p.NS, p.Ls = stage_geometry(layout.n_chunks, ctas, payload_bytes_per_elem(codec))
+    buf.last_tag = int(p.tag)
     p.C = layout.n_chunks
     p.replicate_state = int(hyper.replicate_state)
     p.slot_bytes = _align(((layout.n_chunks + K - 1) // K) * CHUNK * payload_bytes_per_elem(codec))
@@ -347,11 +366,14 @@ def _fill_v2(p, buf: PeerBuffers, group: GroupSpec, codec: CompressionType, hype
     p.t_flags = buf.t_flags.data_ptr()
     p.status = buf.status.data_ptr()
     p.counters = buf.counters.data_ptr()
+    p.trace = None
+    p.debug_flags = 0
 
 
 def fused_allreduce_v2(buf: PeerBuffers, group: GroupSpec, codec: CompressionType, hyper: OptHyper,
                        stream: Optional[torch.cuda.Stream] = None, src_f32: bool = True, scale: float = 1.0,
-                       write_p16: bool = True, mean_out32: bool = True, max_ctas: int = 0, split=None) -> None:
+                       write_p16: bool = True, mean_out32: bool = True, max_ctas: int = 0, split=None,
+                       trace: Optional[torch.Tensor] = None, debug_flags: int = 0) -> None:
     """Launch the push-based kernel for this peer on `stream` (current stream by default). Asynchronous.
 
     `group.shards` only says WHO owns a share (non-empty range = owner): ownership is interleaved, chunk c belongs to
@@ -362,8 +384,31 @@ def fused_allreduce_v2(buf: PeerBuffers, group: GroupSpec, codec: CompressionTyp
         ctas = _max_ctas(hyper.mode, codec)
         if max_ctas > 0:
             ctas = min(ctas, max_ctas)
-        p = native.AR2Params()
-        _fill_v2(p, buf, group, codec, hyper, ctas, src_f32, scale, write_p16, mean_out32, split)
+        # filling ~200 ctypes fields costs ~50 us of Python per call: the structure of a group that meets again is kept
+        key = (tuple(group.bases), group.me, tuple(group.weights), tuple(e > b for b, e in group.shards), int(codec),
+               hyper.mode, ctas, bool(src_f32), bool(write_p16), bool(mean_out32), None if split is None else tuple(split),
+               os.environ.get("DEDLOC_AR2_STAGES"), os.environ.get("DEDLOC_AR2_STAGE_MB"), os.environ.get("DEDLOC_AR2_SPLIT"))
+        p = buf._v2_cache.get(key)
+        if p is None:
+            if len(buf._v2_cache) > 64:
+                buf._v2_cache.clear()
+            p = native.AR2Params()
+            _fill_v2(p, buf, group, codec, hyper, ctas, src_f32, scale, write_p16, mean_out32, split)
+            buf._v2_cache[key] = p
+        else:
+            p.tag = (group.tag & 0x7FFFFFFF) or 1
+            buf.last_tag = int(p.tag)
+            p.timeout_ns = int(group.timeout_s * 1e9)
+            p.replicate_state = int(hyper.replicate_state)
+            p.scale = scale
+            p.lr, p.beta1, p.beta2, p.eps = hyper.lr, hyper.beta1, hyper.beta2, hyper.eps
+            p.bias_correction, p.clamp_value = hyper.bias_correction, hyper.clamp_value
+            p.momentum, p.trust = hyper.momentum, hyper.trust
+            p.trace = None
+        if trace is not None:       # int64 [4 roles, AR2_MAX_STAGES, 4] on this device: per-stage %globaltimer stamps
+            assert trace.numel() >= 4 * native.AR2_MAX_STAGES * 4 and trace.dtype == torch.int64
+            p.trace = trace.data_ptr()
+        p.debug_flags = debug_flags
         st = stream if stream is not None else torch.cuda.current_stream(buf.device)
         native.check(native.lib().dedloc_fused_allreduce_v2(C.byref(p), 1, buf.params_dev.data_ptr(), st.cuda_stream),
                      "fused_allreduce_v2")
@@ -391,3 +436,20 @@ def fused_allreduce_v2_emulated(bufs: Sequence[PeerBuffers], weights: Sequence[f
         st = torch.cuda.current_stream(dev)
         native.check(native.lib().dedloc_fused_allreduce_v2(arr, P, bufs[0].params_dev.data_ptr(), st.cuda_stream),
                      "fused_allreduce_v2 (emulated ranks)")
+
+
+def fused_average_parameters(buf: PeerBuffers, group: GroupSpec, stream: Optional[torch.cuda.Stream] = None) -> None:
+    """Weighted mean of the members' fp32 master parameters, in place, with the bf16 mirror refreshed (MEAN mode of the
+    push-based kernel, lossless fp32 payload): merges the work of groups that stepped side by side (the
+    reference averages parameters in every round). In place is safe: an owner stores the average of a chunk into a
+    member's parameters only after that member's PUSH of the stage has been flagged complete."""
+    codec = CompressionType.NONE
+    assert v2_supported(buf.layout, buf.regions, group, codec)
+    with torch.cuda.device(buf.device):
+        p = native.AR2Params()
+        _fill_v2(p, buf, group, codec, OptHyper(mode=native.AR_MEAN), _max_ctas(native.AR_MEAN, codec), True, 1.0,
+                 True, True)
+        p.acc = buf.symm.ptr + buf.regions.p32          # the "gradient" of this reduction is the parameter vector
+        st = stream if stream is not None else torch.cuda.current_stream(buf.device)
+        native.check(native.lib().dedloc_fused_allreduce_v2(C.byref(p), 1, buf.params_dev.data_ptr(), st.cuda_stream),
+                     "fused_average_parameters")

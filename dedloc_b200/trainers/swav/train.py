@@ -121,7 +121,8 @@ class SelfSupervisionTask:
         cands = [link] if os.path.exists(link) else sorted(glob.glob(os.path.join(ck.DIR, "model_*.torch")),
                                                            key=os.path.getmtime)
         if cands:
-            state = torch.load(cands[-1], map_location="cpu", weights_only=False)
+            # the VISSL-shaped checkpoint is tensors and plain containers only: never unpickle arbitrary objects
+            state = torch.load(cands[-1], map_location="cpu", weights_only=True)
             self.set_classy_state(state["classy_state_dict"])
             logger.info(f"Resumed from {cands[-1]} at iteration {self.iteration}")
 

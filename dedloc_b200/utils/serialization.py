@@ -30,7 +30,8 @@ def pack_state(obj: Any, _depth: int = 0) -> Any:
         t = obj.detach().cpu().contiguous()
         if t.dtype not in _NAMES:
             raise ValueError(f"unsupported tensor dtype {t.dtype}")
-        raw = t.view(torch.uint8).numpy().tobytes() if t.dtype != torch.bool else t.to(torch.uint8).numpy().tobytes()
+        flat = t.reshape(-1)
+        raw = flat.view(torch.uint8).numpy().tobytes() if t.dtype != torch.bool else flat.to(torch.uint8).numpy().tobytes()
         return {"__tensor__": _NAMES[t.dtype], "shape": list(t.shape), "data": raw}
     if isinstance(obj, dict):
         return {"__dict__": [[pack_state(k, _depth + 1), pack_state(v, _depth + 1)] for k, v in obj.items()]}
@@ -61,6 +62,8 @@ def unpack_state(obj: Any, max_tensor_bytes: int = 1 << 34, _depth: int = 0) -> 
             itemsize = 1 if dtype == torch.bool else torch.empty((), dtype=dtype).element_size()
             if numel * itemsize != len(data) or len(data) > max_tensor_bytes:
                 raise ValueError("tensor byte count does not match its shape")
+            if numel == 0:
+                return torch.zeros(shape, dtype=dtype)
             flat = torch.frombuffer(bytearray(data), dtype=torch.uint8)
             if dtype == torch.bool:
                 return flat.to(torch.bool).reshape(shape)

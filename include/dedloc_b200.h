@@ -150,6 +150,9 @@ typedef struct DedlocAR2Params {
   uint16_t* out16[DEDLOC_MAX_PEERS];
   float* m_all[DEDLOC_MAX_PEERS];             /* replicate_state targets */
   float* v_all[DEDLOC_MAX_PEERS];
+  unsigned long long* trace;                  /* optional [4 roles][MAX_STAGES][4] %globaltimer stamps of CTA 0 of each role */
+  int debug_flags;                            /* diagnostics only; 1 = omit the system-scope fences (results undefined) */
+  int reserved;
 } DedlocAR2Params;
 
 /* params: n_ranks structs in HOST memory; params_dev: device scratch of n_ranks * sizeof(DedlocAR2Params) bytes. */
