@@ -41,8 +41,10 @@ namespace ar2 {
 using Params = DedlocAR2Params;
 constexpr int kThreads = 256;
 constexpr int kMaxS = DEDLOC_AR2_MAX_STAGES;
-constexpr int kUnrollPush = 8;
-constexpr int kUnrollApply = 4;
+constexpr int kUnrollPush = 4;
+constexpr int kUnrollApply = 2;
+constexpr int kPeerBatch = 4;     // staged payloads in flight per thread in REDUCE
+constexpr int kCtasPerSm = 4;     // <= 64 registers per thread: 32 warps per SM hide the load latency of the streaming roles
 constexpr int kFlagStride = DEDLOC_MAX_PEERS;
 
 template <int CODEC>
@@ -355,11 +357,11 @@ __device__ void role_reduce(const Params& p, int b, float* red, float* lut, int*
       float acc[8];
 #pragma unroll
       for (int i = 0; i < 8; ++i) acc[i] = 0.f;
-      for (int q0 = 0; q0 < p.P; q0 += 8) {
-        Raw8 raw[8];
-        float a0[8], a1[8];
+      for (int q0 = 0; q0 < p.P; q0 += kPeerBatch) {
+        Raw8 raw[kPeerBatch];
+        float a0[kPeerBatch], a1[kPeerBatch];
 #pragma unroll
-        for (int k = 0; k < 8; ++k) {
+        for (int k = 0; k < kPeerBatch; ++k) {
           const int q = q0 + k;
           a0[k] = 0.f;
           a1[k] = 0.f;
@@ -374,7 +376,7 @@ __device__ void role_reduce(const Params& p, int b, float* red, float* lut, int*
           }
         }
 #pragma unroll
-        for (int k = 0; k < 8; ++k) {
+        for (int k = 0; k < kPeerBatch; ++k) {
           const int q = q0 + k;
           if (q < p.P && p.w[q] != 0.f) {
             float x[8];
@@ -701,6 +703,24 @@ __device__ void role_apply(const Params& p, int b, float* red) {
 
 template <int CODEC, int MODE>
 __device__ __forceinline__ void run_role(const Params& p, int b, float* red, float* lut, int* s_last) {
+  if (p.sequential) {
+    // Every CTA runs the four roles one after the other over ALL stages (nP = nR = nU = nA = grid): each phase has
+    // the whole chip, which hides load latency far better than a quarter of the CTAs per role, and both the gradient
+    // and the update stores leave through the same NVLink direction anyway, so running them side by side gains no
+    // bandwidth. Waits stay stage-granular: a phase starts on stage 0 while the peers are still finishing the last
+    // stages of their previous phase. No role waits for a later role, so the order cannot deadlock.
+    role_push<CODEC>(p, b);
+    role_reduce<CODEC, MODE>(p, b, red, lut, s_last);
+    if (saw_abort(p)) return;
+    if constexpr (MODE != DEDLOC_AR_MEAN) {
+      role_update<MODE>(p, b, red);
+      if (saw_abort(p)) return;
+      role_apply<MODE>(p, b, red);
+    } else if (b == 0) {
+      role_apply<MODE>(p, b, red);
+    }
+    return;
+  }
   if (b < p.nP) {
     role_push<CODEC>(p, b);
   } else if (b < p.nP + p.nR) {
@@ -714,7 +734,7 @@ __device__ __forceinline__ void run_role(const Params& p, int b, float* red, flo
 
 // Production: one member per launch, its parameters by value (no copy, no memset precedes the launch).
 template <int CODEC, int MODE>
-__global__ void __launch_bounds__(kThreads, 2) ar2_kernel(const __grid_constant__ Params p) {
+__global__ void __launch_bounds__(kThreads, kCtasPerSm) ar2_kernel(const __grid_constant__ Params p) {
   __shared__ float red[64];
   __shared__ float lut[CodecTraits<CODEC>::kLut ? DEDLOC_MAX_PEERS * 256 : 1];
   __shared__ int s_last;
@@ -723,7 +743,7 @@ __global__ void __launch_bounds__(kThreads, 2) ar2_kernel(const __grid_constant_
 
 // Tests: several members in one cooperative launch on one GPU; every CTA copies its member's parameters to smem.
 template <int CODEC, int MODE>
-__global__ void __launch_bounds__(kThreads, 2) ar2_kernel_ranks(const Params* __restrict__ pa, int ctas_per_rank) {
+__global__ void __launch_bounds__(kThreads, kCtasPerSm) ar2_kernel_ranks(const Params* __restrict__ pa, int ctas_per_rank) {
   __shared__ Params sp;
   __shared__ float red[64];
   __shared__ float lut[CodecTraits<CODEC>::kLut ? DEDLOC_MAX_PEERS * 256 : 1];
@@ -746,7 +766,7 @@ static int max_ctas() {
   if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, ar2_kernel<CODEC, MODE>, kThreads, 0) != cudaSuccess) return 0;
   if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ_r, ar2_kernel_ranks<CODEC, MODE>, kThreads, 0) != cudaSuccess) return 0;
   if (occ_r < occ) occ = occ_r;
-  return sms * (occ > 2 ? 2 : occ);
+  return sms * (occ > kCtasPerSm ? kCtasPerSm : occ);
 }
 
 template <int CODEC, int MODE>
@@ -812,7 +832,7 @@ extern "C" int dedloc_fused_allreduce_v2(const DedlocAR2Params* params, int n_ra
                      n_ranks <= DEDLOC_MAX_PEERS,
                  "fused_allreduce_v2: bad arguments");
   const DedlocAR2Params& p0 = params[0];
-  const int ctas = p0.nP + p0.nR + p0.nU + p0.nA;
+  const int ctas = p0.sequential ? p0.nP : p0.nP + p0.nR + p0.nU + p0.nA;
   cudaStream_t st = (cudaStream_t)stream;
   for (int r = 0; r < n_ranks; ++r) {
     const DedlocAR2Params& p = params[r];
@@ -821,13 +841,20 @@ extern "C" int dedloc_fused_allreduce_v2(const DedlocAR2Params* params, int n_ra
     DEDLOC_REQUIRE(p.K >= 1 && p.K <= p.P, "fused_allreduce_v2: %d owners in a group of %d", p.K, p.P);
     DEDLOC_REQUIRE(p.tag != 0, "fused_allreduce_v2: the round tag must not be zero");
     DEDLOC_REQUIRE(p.mode == p0.mode && p.codec == p0.codec, "fused_allreduce_v2: members disagree on mode / codec");
-    DEDLOC_REQUIRE(p.nP + p.nR + p.nU + p.nA == ctas && p.nP >= 1 && p.nA >= 1,
-                   "fused_allreduce_v2: role split (%d, %d, %d, %d) does not add up to %d", p.nP, p.nR, p.nU, p.nA, ctas);
+    if (p.sequential) {
+      DEDLOC_REQUIRE(p0.sequential && p.nP == p0.nP && p.nP >= 1 && p.nA == p.nP &&
+                         (p.nR == p.nP || p.nR == 0) && (p.nU == p.nP || p.nU == 0),
+                     "fused_allreduce_v2: sequential phases need the same CTA count for every role");
+    } else {
+      DEDLOC_REQUIRE(p.nP + p.nR + p.nU + p.nA == ctas && p.nP >= 1 && p.nA >= 1,
+                     "fused_allreduce_v2: role split (%d, %d, %d, %d) does not add up to %d", p.nP, p.nR, p.nU, p.nA, ctas);
+    }
     DEDLOC_REQUIRE(p.NS >= 1 && p.NS <= DEDLOC_AR2_MAX_STAGES && p.Ls % kCodecBlockChunks == 0 && p.Ls * p.NS >= p.C &&
                        p.C >= 1,
                    "fused_allreduce_v2: bad stage geometry (NS %d, Ls %lld, C %lld)", p.NS, p.Ls, p.C);
     const bool owner = p.kidx[p.me] >= 0;
     DEDLOC_REQUIRE(!owner || p.nR >= 1, "fused_allreduce_v2: an owner needs REDUCE CTAs");
+    DEDLOC_REQUIRE(owner || p.nR == 0 || p.sequential, "fused_allreduce_v2: REDUCE CTAs on a member that owns nothing");
     if (p.mode != DEDLOC_AR_MEAN) {
       DEDLOC_REQUIRE(!owner || p.nU >= 1, "fused_allreduce_v2: an owner needs UPDATE CTAs");
       DEDLOC_REQUIRE(p.p32 && p.gavg && p.chunk_stats && p.chunk_tid && p.tensor_cbeg && p.t_wd && p.t_lr_scale && p.t_flags,

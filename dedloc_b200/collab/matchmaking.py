@@ -148,6 +148,10 @@ class Matchmaking:
                     # nobody else landed in this bucket: try once more under the common key
                     self.group_bits = ""
                     self.declared_expiration = get_dht_time() + self.averaging_expiration
+                    self.followers = {}
+                    self.assembled = loop.create_future()     # the first attempt resolved its future (to None)
+                    self.group_full.clear()
+                    self.current_leader = None
                     if not self.client_mode:
                         await self.dht.node.store(self.group_key, self.declared_expiration, self.declared_expiration,
                                                   subkey=self.endpoint)

@@ -96,6 +96,7 @@ class CollaborativeOptimizer:
         self.replicate_state_every = int(replicate_state_every)
         self.average_diverged_parameters = bool(unused_kwargs.pop("average_diverged_parameters", True))
         self._pending_param_average = False
+        self._agreed_step = 0
         self._moment_owners: Optional[List[bytes]] = None   # handles of last round's owners, in owner order; None = all local
         self._needs_resync = False                          # set when a round left this peer's state torn
         self._state_seq = 0                                 # odd while a fused round may be writing this peer's state
@@ -544,9 +545,12 @@ class CollaborativeOptimizer:
         voters = [i for i, b in enumerate(blobs) if b.get("mode") != MODE_AUX] or list(range(len(blobs)))
         distinct = sorted({lins[i] for i in voters})
         self._pending_param_average = False
-        if len(distinct) > 1 and self.average_diverged_parameters and len({steps[i] for i in voters}) == 1:
+        vsteps = [steps[i] for i in voters]
+        if len(distinct) > 1 and self.average_diverged_parameters and max(vsteps) - min(vsteps) <= self.step_tolerance:
+            # (a group that finished its previous round a moment earlier may already be one step ahead)
             self._pending_param_average = True
             self._agreed_depth = max(depths[i] for i in voters)
+            self._agreed_step = max(vsteps)
             return self._mix("A", *distinct)
         votes: Dict[str, List[str]] = {}
         depth: Dict[str, int] = {}
@@ -596,6 +600,9 @@ class CollaborativeOptimizer:
         if self._pending_param_average:
             self._average_parameters(group, blobs, bases)
             self.lineage, self.lineage_depth = agreed, self._agreed_depth
+            if self._agreed_step > self.local_step and not self.auxiliary:
+                self.local_step = self._agreed_step            # merged with a group that was one step ahead
+                self._sync_scheduler()
             self.stats["parameter_averagings"] = self.stats.get("parameter_averagings", 0) + 1
         if bases is not None:
             return self._run_fused_group_round(group, blobs, bases)

@@ -86,7 +86,7 @@ class AR2Params(C.Structure):
         ("out16", C.c_void_p * MAX_PEERS),
         ("m_all", C.c_void_p * MAX_PEERS),
         ("v_all", C.c_void_p * MAX_PEERS),
-        ("trace", C.c_void_p), ("debug_flags", C.c_int), ("reserved", C.c_int),
+        ("trace", C.c_void_p), ("debug_flags", C.c_int), ("sequential", C.c_int),
     ]
 
 

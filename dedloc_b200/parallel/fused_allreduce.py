@@ -121,7 +121,7 @@ class PeerBuffers:
         self.gavg = torch.zeros(n, dtype=torch.float32, device=dev)      # averaged gradient of my shard
         # per-chunk partial norms: [chunk][2] for the pull kernel, [chunk][8 warps][2] for the push kernel
         # partial norms: [chunk][2] for the pull kernel; [tensor][REDUCE CTA]{a, b, tag, -} for the push kernel
-        self.chunk_stats = torch.zeros(max(layout.n_chunks * 2, layout.n_tensors * 4 * 304), dtype=torch.float32,
+        self.chunk_stats = torch.zeros(max(layout.n_chunks * 2, layout.n_tensors * 4 * 640), dtype=torch.float32,
                                        device=dev)
         self._v2_cache: Dict[tuple, object] = {}
         self.status = torch.zeros(16, dtype=torch.int32, device=dev)
@@ -278,10 +278,10 @@ def _role_split(total: int, mode: int, owner: bool, K: int, weights=None) -> tup
 def stage_geometry(n_chunks: int, ctas: int, bytes_per_elem: int = 2) -> tuple:
     """(NS, Ls): stages of Ls chunks (a multiple of 32, so 8-bit codebook blocks never straddle stages). Every stage
     hand-over costs a system-scope fence and a flag round trip (~10 us), so a stage carries at least
-    DEDLOC_AR2_STAGE_MB (default 4) MB of payload and at least two chunks per CTA; at most AR2_MAX_STAGES stages."""
+    DEDLOC_AR2_STAGE_MB (default 16) MB of payload and at least two chunks per CTA; at most AR2_MAX_STAGES stages."""
     import os
 
-    stage_mb = float(os.environ.get("DEDLOC_AR2_STAGE_MB", "4"))
+    stage_mb = float(os.environ.get("DEDLOC_AR2_STAGE_MB", "16"))
     by_bytes = int(stage_mb * 2 ** 20 / (CHUNK * bytes_per_elem))
     target = max(32, (max(2 * ctas, by_bytes) + 31) // 32 * 32)
     ns = min(native.AR2_MAX_STAGES, max(1, (n_chunks + target - 1) // target))
@@ -316,7 +316,16 @@ def _fill_v2(p, buf: PeerBuffers, group: GroupSpec, codec: CompressionType, hype
     p.tag = (group.tag & 0x7FFFFFFF) or 1
     p.src_f32 = int(src_f32 and codec in _FLY_CODECS)
     p.timeout_ns = int(group.timeout_s * 1e9)
-    p.nP, p.nR, p.nU, p.nA = _role_split(ctas, hyper.mode, group.me in owners, K, split)
+    sequential = os.environ.get("DEDLOC_AR2_SCHEDULE", "sequential") != "concurrent"
+    p.sequential = int(sequential)
+    if sequential:
+        # every CTA runs the four roles one after the other: each phase has the whole chip
+        is_owner = group.me in owners
+        p.nP, p.nA = ctas, ctas
+        p.nR = ctas if is_owner else 0
+        p.nU = ctas if (is_owner and hyper.mode != native.AR_MEAN) else 0
+    else:
+        p.nP, p.nR, p.nU, p.nA = _role_split(ctas, hyper.mode, group.me in owners, K, split)
     p.NS, p.Ls = stage_geometry(layout.n_chunks, ctas, payload_bytes_per_elem(codec))
     buf.last_tag = int(p.tag)
     p.C = layout.n_chunks
@@ -387,7 +396,8 @@ def fused_allreduce_v2(buf: PeerBuffers, group: GroupSpec, codec: CompressionTyp
         # filling ~200 ctypes fields costs ~50 us of Python per call: the structure of a group that meets again is kept
         key = (tuple(group.bases), group.me, tuple(group.weights), tuple(e > b for b, e in group.shards), int(codec),
                hyper.mode, ctas, bool(src_f32), bool(write_p16), bool(mean_out32), None if split is None else tuple(split),
-               os.environ.get("DEDLOC_AR2_STAGES"), os.environ.get("DEDLOC_AR2_STAGE_MB"), os.environ.get("DEDLOC_AR2_SPLIT"))
+               os.environ.get("DEDLOC_AR2_STAGES"), os.environ.get("DEDLOC_AR2_STAGE_MB"), os.environ.get("DEDLOC_AR2_SPLIT"),
+               os.environ.get("DEDLOC_AR2_SCHEDULE"))
         p = buf._v2_cache.get(key)
         if p is None:
             if len(buf._v2_cache) > 64:

@@ -118,6 +118,8 @@ class AlbertTrainingArguments:
     device: Optional[str] = None
     max_local_steps: int = 0   # 0 = unbounded; handy for smoke runs
     use_hf_trainer: bool = False
+    no_cuda_graph: bool = False   # run the micro-step eagerly instead of replaying a captured CUDA graph
+    report_json: bool = False     # print one JSON line with the throughput of this process when the loop ends
 
 
 @dataclass

@@ -9,8 +9,11 @@ resize_token_embeddings) -> LAMB with two weight-decay groups + linear warm-up -
 validators -> CollaborativeOptimizer -> training loop with an independent per-peer shuffling seed ->
 `CollaborativeCallback`: state download on start, non-finite guard with rollback, metrics published to
 `{prefix}_metrics[public key]` whenever the collaboration step advances, checkpoint every `save_steps`.
-The loop is this repo's own (one process per B200, bf16, fused kernels); `--use_hf_trainer` drives the same
-optimizer through transformers.Trainer exactly like the reference does.
+The loop is `trainers/pretrain.py:PeerTrainer` -- the very code path bench.py times: micro-step captured in a CUDA
+graph, at most one micro-step of host run-ahead, loss accumulated on the device and read once per collaborative step,
+no per-step host synchronisation (the non-finite guard lives in the all-reduce kernel, which skips the update of a
+tensor whose averaged gradient is not finite). `--use_hf_trainer` drives the same optimizer through
+transformers.Trainer exactly like the reference does.
 """
 from __future__ import annotations
 
@@ -99,9 +102,14 @@ class CollaborativeCallback:
         logger.warning("Loading state from peers")
         self.collaborative_optimizer.load_state_from_peers()
 
-    def on_step_end(self, args=None, state=None, control=None, loss: Optional[float] = None, **kwargs):
+    def on_step_end(self, args=None, state=None, control=None, loss: Optional[float] = None, mini_steps: int = 1,
+                    samples: Optional[int] = None, **kwargs):
+        """`loss` is the SUM of the losses of `mini_steps` local steps (the reference calls this once per local step;
+        the PeerTrainer loop calls it once per collaborative step with everything that happened since)."""
         if control is not None:
             control.should_log = True
+        if samples is not None:
+            self.samples = samples
         if not self.params_are_finite():
             logger.warning("non-finite parameters detected: rolling back to the previous state")
             self.load_from_state(self.previous_state)
@@ -113,7 +121,7 @@ class CollaborativeCallback:
             loss = state.log_history[-1].get("loss")
         if loss is not None:
             self.loss += float(loss)
-            self.steps += 1
+            self.steps += mini_steps
             if self.collaborative_optimizer.local_step != self.last_reported_collaboration_step:
                 self.last_reported_collaboration_step = self.collaborative_optimizer.local_step
                 self.total_samples_processed += self.samples
@@ -131,15 +139,17 @@ class CollaborativeCallback:
                     self.dht.store(key=self.collaborative_optimizer.prefix + "_metrics",
                                    subkey=self.local_public_key, value=statistics.dict(),
                                    expiration_time=get_dht_time() + self.statistics_expiration, return_future=True)
-        self.samples = self.collaborative_optimizer.local_samples_accumulated
+        if samples is None:
+            self.samples = self.collaborative_optimizer.local_samples_accumulated
         return control
 
     @torch.no_grad()
     def get_current_state(self) -> Dict[str, Any]:
         opt = self.collaborative_optimizer.opt
         if isinstance(opt, FusedLamb) and opt.is_materialized:
-            b = opt.buffers
-            return {"fused": (b.p32.clone(), b.m.clone(), b.v.clone(), opt.opt_step)}
+            # no 3 x 71 MB clone per step: the fused kernel never commits a non-finite update (it skips the tensor),
+            # so there is nothing to roll back to; a peer whose state is damaged resynchronises from its peers
+            return {"fused": None}
         return {"model": {k: v.clone() for k, v in self.model.state_dict().items()},
                 "opt": _clone_state(opt.state_dict())}
 
@@ -147,6 +157,9 @@ class CollaborativeCallback:
     def load_from_state(self, state) -> None:
         opt = self.collaborative_optimizer.opt
         if "fused" in state:
+            if state["fused"] is None:
+                self.collaborative_optimizer.load_state_from_peers()
+                return
             p32, m, v, step = state["fused"]
             b = opt.buffers
             b.p32.copy_(p32)
@@ -261,30 +274,53 @@ def main(argv=None):
         return
     callback.on_train_begin()
     batches = make_batches(training_args, dataset_args, model.config, independent_shuffling_seed(local_public_key))
-    accum = training_args.gradient_accumulation_steps
+    from ..pretrain import PeerConfig, PeerTrainer
+
+    peer_cfg = PeerConfig(micro_batch=total_batch_size_per_step,
+                          gradient_accumulation_steps=training_args.gradient_accumulation_steps,
+                          seq_len=training_args.seq_length)
+    trainer = PeerTrainer(model, opt, scheduler, collaborative_optimizer, peer_cfg, device)
+    first = next(batches)
+    if on_gpu and not training_args.no_cuda_graph:
+        trainer.enable_cuda_graph(first)
     local_steps = 0
     last_saved = collaborative_optimizer.local_step
+    pending: Optional[Dict[str, torch.Tensor]] = first
+    samples_at_last_step = 0
+    t_log = time.time()
     while collaborative_optimizer.local_step < training_args.max_steps:
-        host = next(batches)
-        batch = {k: v.to(device, non_blocking=True) for k, v in host.items()}
-        n = batch["input_ids"].shape[0]
-        loss_val = torch.zeros((), device=device)
-        for c in range(accum):
-            sub = {k: v[c * n // accum:(c + 1) * n // accum] for k, v in batch.items()}
-            out = model(**sub)
-            (out.loss / accum).backward()                 # HF Trainer averages over accumulation steps
-            loss_val += out.loss.detach().float() / accum
-        model.flush_fused_grads()
-        collaborative_optimizer.step()                    # clips (max_grad_norm), accumulates, maybe global step
-        collaborative_optimizer.zero_grad()
-        callback.on_step_end(loss=float(loss_val))
+        host = pending if pending is not None else next(batches)
+        pending = None
+        mini_before = trainer.mini_steps
+        stepped = trainer.micro_step(host)                # forward/backward (graph replay) + CollaborativeOptimizer.step()
         local_steps += 1
-        step = collaborative_optimizer.local_step
-        if step != last_saved and step % training_args.save_steps == 0:
-            save_checkpoint(training_args, model, collaborative_optimizer, step)
-            last_saved = step
+        if stepped:
+            # one device->host read per collaborative step: everything the reference reports after every local step
+            n_mini = max(trainer.mini_steps, mini_before + 1)
+            mean_loss = trainer.pop_mean_loss()
+            callback.on_step_end(loss=mean_loss * n_mini, mini_steps=n_mini,
+                                 samples=trainer.samples_processed - samples_at_last_step)
+            samples_at_last_step = trainer.samples_processed
+            step = collaborative_optimizer.local_step
+            if training_args.logging_steps and step % max(training_args.logging_steps, 1) == 0:
+                dt = time.time() - t_log
+                logger.info(f"collaborative step {step}: {trainer.samples_processed / max(dt, 1e-9):.1f} samples/s locally")
+            if step != last_saved and step % training_args.save_steps == 0:
+                save_checkpoint(training_args, model, collaborative_optimizer, step)
+                last_saved = step
         if training_args.max_local_steps and local_steps >= training_args.max_local_steps:
             break
+    if on_gpu:
+        torch.cuda.synchronize(device)
+    if training_args.report_json:
+        import json
+
+        dt = time.time() - t_log
+        print(json.dumps({"entry": "dedloc_b200.trainers.albert.run_trainer", "local_steps": local_steps,
+                          "collaborative_steps": collaborative_optimizer.local_step,
+                          "samples": trainer.samples_processed, "seconds": round(dt, 3),
+                          "samples_per_second_incl_startup": round(trainer.samples_processed / max(dt, 1e-9), 2),
+                          "cuda_graph": trainer._graph is not None}), flush=True)
     collaborative_optimizer.shutdown()
     dht.shutdown()
 

@@ -152,7 +152,7 @@ typedef struct DedlocAR2Params {
   float* v_all[DEDLOC_MAX_PEERS];
   unsigned long long* trace;                  /* optional [4 roles][MAX_STAGES][4] %globaltimer stamps of CTA 0 of each role */
   int debug_flags;                            /* diagnostics only; 1 = omit the system-scope fences (results undefined) */
-  int reserved;
+  int sequential;                             /* 1: every CTA runs PUSH, REDUCE, UPDATE, APPLY one after the other (all n* = grid) */
 } DedlocAR2Params;
 
 /* params: n_ranks structs in HOST memory; params_dev: device scratch of n_ranks * sizeof(DedlocAR2Params) bytes. */

@@ -1,7 +1,7 @@
 """Per-stage timeline of the push-based all-reduce kernel (csrc/fused_allreduce_v2.cu) on N GPUs.
 
     python -m torch.distributed.run --nproc-per-node N --master-addr 127.0.0.1 scripts/trace_allreduce.py \
-        [size_mb] [mode: MEAN|LAMB] [stages or 0] [debug_flags]
+        [size_mb] [mode: MEAN|LAMB] [stages or 0] [debug_flags] [sequential|concurrent]
 
 CTA 0 of every role stamps %globaltimer at the start of a stage, after its work, after its system-scope fence and
 when the stage's flag goes out. Prints, per role and stage, the offsets from the first stamp in microseconds, and the
@@ -32,6 +32,8 @@ def main():
     if len(sys.argv) > 3 and int(sys.argv[3]) > 0:
         os.environ["DEDLOC_AR2_STAGES"] = sys.argv[3]
     debug = int(sys.argv[4]) if len(sys.argv) > 4 else 0
+    if len(sys.argv) > 5:
+        os.environ["DEDLOC_AR2_SCHEDULE"] = sys.argv[5]
     layout = scaled_layout(albert_shapes(), mb)
     buf = PeerBuffers(layout, local, with_state=True)
     handles = [None] * world
@@ -64,7 +66,8 @@ def main():
                  "APPLY wait/flags seen/done"]
         print(json.dumps({"size_mb": mb, "gpus": world, "mode": sys.argv[2] if len(sys.argv) > 2 else "MEAN",
                           "launch_ms": [round(x, 4) for x in times], "status": st, "debug_flags": debug,
-                          "stages_env": os.environ.get("DEDLOC_AR2_STAGES")}))
+                          "stages_env": os.environ.get("DEDLOC_AR2_STAGES"),
+                          "schedule": os.environ.get("DEDLOC_AR2_SCHEDULE", "sequential")}))
         for r in range(4):
             print(names[r])
             for s in range(native.AR2_MAX_STAGES):

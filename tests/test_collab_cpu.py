@@ -168,13 +168,16 @@ def test_dead_peer_does_not_stall_the_other():
         first.shutdown()
 
 
-def test_diverged_peer_is_healed_by_lineage():
+@pytest.mark.parametrize("average", [True, False])
+def test_diverged_peer_is_healed_by_lineage(average):
     """A peer that stepped alone after a failed round holds different parameters at the same step number. Its lineage
-    hash differs from the group's, so at the next joint round it copies the state of a majority member before the
-    reduction and all peers are bit-identical again (the reference heals this by averaging parameters every step)."""
-    first, m0, c0 = make_peer(None, "cfg1heal", target=16)
-    d1, m1, c1 = make_peer(first, "cfg1heal", target=16)
-    d2, m2, c2 = make_peer(first, "cfg1heal", target=16)
+    hash differs from the group's, so the next joint round first makes everybody equal again: by averaging the
+    parameters of all members (default; the reference averages parameters in every round, and no step is thrown away),
+    or -- average_diverged_parameters=False -- by copying the state of a majority member."""
+    kw = dict(average_diverged_parameters=average)
+    first, m0, c0 = make_peer(None, f"cfg1heal{int(average)}", target=16, **kw)
+    d1, m1, c1 = make_peer(first, f"cfg1heal{int(average)}", target=16, **kw)
+    d2, m2, c2 = make_peer(first, f"cfg1heal{int(average)}", target=16, **kw)
     peers = [(m0, c0), (m1, c1), (m2, c2)]
     try:
         log = []
@@ -192,11 +195,47 @@ def test_diverged_peer_is_healed_by_lineage():
         [t.start() for t in threads]
         [t.join(timeout=120) for t in threads]
         assert all(c.local_step == 2 for _, c in peers)
-        assert c2.stats["lineage_resyncs"] == 1 and c0.stats["lineage_resyncs"] == 0 and c1.stats["lineage_resyncs"] == 0
+        if average:
+            assert all(c.stats["lineage_resyncs"] == 0 and c.stats.get("parameter_averagings", 0) == 1 for _, c in peers)
+        else:
+            assert c2.stats["lineage_resyncs"] == 1 and c0.stats["lineage_resyncs"] == 0 and c1.stats["lineage_resyncs"] == 0
         assert c0.lineage == c1.lineage == c2.lineage
         assert_same_params(m0, m1, tol=1e-6)
         assert_same_params(m0, m2, tol=1e-6)
     finally:
         for c, d in ((c0, first), (c1, d1), (c2, d2)):
+            c.shutdown()
+            d.shutdown()
+
+
+def test_four_peers_in_groups_of_two_merge_instead_of_discarding():
+    """target_group_size < number of peers (swav/README.md:26 runs groups of 4; contributor_notebook.ipynb cell 3
+    describes the reshuffle): two groups step side by side in a round, so their parameters differ afterwards. The next
+    round's groups average PARAMETERS first (hivemind averages them in every round) -- nobody's step is thrown away by
+    a state copy -- and the collaboration stays close to single-process large-batch training."""
+    first, m0, c0 = make_peer(None, "cfg1g", target=32, target_group_size=2, averaging_expiration=1.0)
+    others = [make_peer(first, "cfg1g", target=32, target_group_size=2, averaging_expiration=1.0) for _ in range(3)]
+    peers = [(first, m0, c0)] + others
+    log, n_rounds = [], 4
+    threads = [threading.Thread(target=run_trainer, args=(i, m, c, n_rounds, log))
+               for i, (_, m, c) in enumerate(peers)]
+    try:
+        [t.start() for t in threads]
+        [t.join(timeout=240) for t in threads]
+        for _, _, c in peers:
+            assert c.local_step == n_rounds, [x[2].local_step for x in peers]
+            assert c.stats["lineage_resyncs"] == 0 and c.stats["state_downloads"] == 0, c.stats   # nothing discarded
+        sizes = [c.stats["rounds"] - c.stats["solo_rounds"] for _, _, c in peers]
+        assert min(sizes) >= n_rounds - 1, [c.stats for _, _, c in peers]          # (almost) every round was a group round
+        assert sum(c.stats.get("parameter_averagings", 0) for _, _, c in peers) >= 2, [c.stats for _, _, c in peers]
+        # peers that were merged in the last round agree; all are close to each other and to large-batch training
+        ref = oracle(log, n_rounds)
+        with torch.no_grad():
+            step = sum(float((p - q).abs().mean()) for p, q in zip(ref.parameters(), make_model(0).parameters()))
+            for _, m, _ in peers:
+                dist = sum(float((p - q).abs().mean()) for p, q in zip(m.parameters(), ref.parameters()))
+                assert dist < 0.8 * step, (dist, step)      # closer to the large-batch trajectory than the trajectory is long
+    finally:
+        for d, _, c in peers:
             c.shutdown()
             d.shutdown()

@@ -35,7 +35,10 @@ def _owners(mask):
 
 @pytest.mark.parametrize("codec", list(CompressionType))
 @pytest.mark.parametrize("fly", [False, True])
-def test_weighted_mean_all_codecs(native, codec, fly):
+def test_weighted_mean_all_codecs(native, codec, fly, monkeypatch):
+    if codec in (CompressionType.FLOAT16, CompressionType.UNIFORM_8BIT):
+        monkeypatch.setenv("DEDLOC_AR2_SCHEDULE", "concurrent")
+    monkeypatch.setenv("DEDLOC_AR2_STAGE_MB", "0.25")        # several stages even for this small vector
     from dedloc_b200.ops import flat_ops
     from dedloc_b200.parallel.fused_allreduce import OptHyper, fused_allreduce_v2_emulated
 
@@ -83,12 +86,15 @@ def _ref_lamb(params, grads_avg, steps, lr, wd_list, eps=1e-6, clamp=10000.0):
     return ps, opt
 
 
+@pytest.mark.parametrize("schedule", ["sequential", "concurrent"])
 @pytest.mark.parametrize("replicate", [False, True])
-def test_fused_lamb_matches_reference(native, replicate):
+def test_fused_lamb_matches_reference(native, replicate, schedule, monkeypatch):
+    monkeypatch.setenv("DEDLOC_AR2_SCHEDULE", schedule)     # phases one after the other / four roles side by side
     from dedloc_b200 import lib
     from dedloc_b200.optim import lamb_bias_correction
     from dedloc_b200.parallel.fused_allreduce import OptHyper, fused_allreduce_v2_emulated
 
+    monkeypatch.setenv("DEDLOC_AR2_STAGE_MB", "0.25")
     P = 3
     layout, bufs, params, _ = _setup(P, seed=2)
     weights = [1.0, 2.0, 1.0]
