@@ -76,14 +76,13 @@ def main_ddp(args) -> int:
     mb = int(getattr(args, "ddp_micro_batch", 0) or args.micro_batch)
 
     def fwd_bwd(batch, scale, sync=True):
-        ctx = nullcontext() if (sync or ddp is model) else ddp.no_sync()
         if best:
             out = ddp(**batch)
             (out.loss * scale).backward()
         else:
-            with ctx, torch.autocast("cuda", dtype=torch.bfloat16):
-                out = ddp(**batch)
-            with ctx:
+            with (nullcontext() if (sync or ddp is model) else ddp.no_sync()):
+                with torch.autocast("cuda", dtype=torch.bfloat16):
+                    out = ddp(**batch)
                 (out.loss * scale).backward()
         return out.loss.detach()
 

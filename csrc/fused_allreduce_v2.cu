@@ -259,7 +259,7 @@ __device__ void role_push(const Params& p, int b) {
           if constexpr (CT::kFly) {
             if (fly) encode_fly<CODEC>(raw[j], p.scale);
           }
-          const int owner = p.owner_of_k[c % K];
+          const int owner = (p.debug_flags & 4) ? me : p.owner_of_k[c % K];   // 4: keep every store local (diagnostic)
           const long long el = (long long)(c / K) * kChunk + tid * 8;
           store_raw8<CODEC>(p.stage_in[owner] + (size_t)me * p.slot_bytes, el, raw[j]);
           float* ax = p.aux_in[owner] + (size_t)me * p.aux_slot_floats;
@@ -283,8 +283,17 @@ __device__ void role_push(const Params& p, int b) {
     // 10-40 us when 147 of them run at once.
     __syncwarp();
     stamp(p, 0, b, s, 1);
+    if (p.trace != nullptr && (tid & 31) == 0 && (tid >> 5) == 0 && b < 1024 && s < 4) {
+      // per-CTA view (warp 0): [SM id, stored s0..s3, fenced s0..s3] after the role traces
+      unsigned smid;
+      asm volatile("mov.u32 %0, %%smid;" : "=r"(smid));
+      unsigned long long* t2 = p.trace + 4 * kMaxS * 4 + (size_t)b * 10;
+      t2[0] = smid;
+      t2[1 + s] = globaltimer_ns();
+    }
     if ((tid & 31) == 0) {
-      __threadfence();
+      if (!(p.debug_flags & 2)) __threadfence();      // 2: omit the per-warp release fence (diagnostic)
+      if (p.trace != nullptr && (tid >> 5) == 0 && b < 1024 && s < 4) p.trace[4 * kMaxS * 4 + (size_t)b * 10 + 5 + s] = globaltimer_ns();
       stamp(p, 0, b, s, 2);
       const unsigned old = atomicAdd(p.counters + 0 * kMaxS + s, 1u);
       if (old == (unsigned)p.nP * (kThreads / 32) - 1) {

@@ -30,6 +30,7 @@ from ..dht import DHT, get_dht_time
 from ..dht.protocol import RPCClient, RPCServer
 from ..optim.fused import FusedOptimizerBase
 from ..utils.compression import CHUNK, CompressionType
+from ..utils.perf_stats import nvtx_range
 from .matchmaking import AllreduceException, GroupInfo, Matchmaking
 from .progress import CollaborationState, PerformanceEMA, ProgressTracker
 
@@ -287,7 +288,7 @@ class CollaborativeOptimizer:
         if self.last_step_time is not None and get_dht_time() - self.last_step_time > self.metadata_expiration:
             logger.warning("training step took longer than metadata_expiration; peers may not see this one")
 
-        with self.state_lock:
+        with self.state_lock, nvtx_range("accumulate_gradients"):
             self._accumulate_local_gradients()
             self.local_samples_accumulated += batch_size
             self.local_steps_accumulated += 1
@@ -376,9 +377,10 @@ class CollaborativeOptimizer:
             if state.num_peers > 1:  # num_peers counts this peer's own progress record too
                 expected = state.num_peers if self.expected_group_size_from_tracker else None
                 try:
-                    group = self.dht.run_coroutine(
-                        lambda dht, node: self._matchmaking.look_for_group(
-                            self._my_blob(), timeout=self.averaging_timeout, expected_size=expected))
+                    with nvtx_range("matchmaking"):
+                        group = self.dht.run_coroutine(
+                            lambda dht, node: self._matchmaking.look_for_group(
+                                self._my_blob(), timeout=self.averaging_timeout, expected_size=expected))
                 except Exception as e:
                     logger.warning("matchmaking failed: %r", e)
             t1 = time.perf_counter()
@@ -389,7 +391,8 @@ class CollaborativeOptimizer:
             averaged = False
             if group is not None and group.group_size > 1:
                 try:
-                    self._run_group_round(group)
+                    with nvtx_range("averaging_round"):
+                        self._run_group_round(group)
                     averaged = True
                 except AllreduceException as e:
                     self.stats["failed_rounds"] += 1

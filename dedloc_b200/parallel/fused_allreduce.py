@@ -275,16 +275,20 @@ def _role_split(total: int, mode: int, owner: bool, K: int, weights=None) -> tup
     return nP, nR, nU, nA
 
 
-def stage_geometry(n_chunks: int, ctas: int, bytes_per_elem: int = 2) -> tuple:
-    """(NS, Ls): stages of Ls chunks (a multiple of 32, so 8-bit codebook blocks never straddle stages). Every stage
-    hand-over costs a system-scope fence and a flag round trip (~10 us), so a stage carries at least
-    DEDLOC_AR2_STAGE_MB (default 16) MB of payload and at least two chunks per CTA; at most AR2_MAX_STAGES stages."""
-    import os
+def stage_geometry(n_chunks: int, ctas: int, bytes_per_elem: int = 2, sequential: bool = True) -> tuple:
+    """(NS, Ls): stages of Ls chunks (a multiple of 32, so 8-bit codebook blocks never straddle stages).
 
+    Every stage hand-over costs a system-scope fence by the warp that completes the stage, and that fence waits for
+    whatever the chip still has in flight: 7-25 us while other stages are streaming, a few us on a quiet chip
+    (profiles/allreduce_trace_*.txt). With the phases run one after the other there is nothing a second stage could
+    overlap with, so ONE stage is fastest at every size measured (1 MB - 1 GB, 2 and 8 GPUs). With concurrent roles a
+    stage carries at least DEDLOC_AR2_STAGE_MB (default 16) MB of payload. DEDLOC_AR2_STAGES forces a count."""
     stage_mb = float(os.environ.get("DEDLOC_AR2_STAGE_MB", "16"))
     by_bytes = int(stage_mb * 2 ** 20 / (CHUNK * bytes_per_elem))
     target = max(32, (max(2 * ctas, by_bytes) + 31) // 32 * 32)
     ns = min(native.AR2_MAX_STAGES, max(1, (n_chunks + target - 1) // target))
+    if sequential and not os.environ.get("DEDLOC_AR2_STAGE_MB"):
+        ns = 1
     if os.environ.get("DEDLOC_AR2_STAGES"):
         ns = max(1, min(native.AR2_MAX_STAGES, int(os.environ["DEDLOC_AR2_STAGES"])))
     ls = ((n_chunks + ns - 1) // ns + 31) // 32 * 32
@@ -326,7 +330,7 @@ def _fill_v2(p, buf: PeerBuffers, group: GroupSpec, codec: CompressionType, hype
         p.nU = ctas if (is_owner and hyper.mode != native.AR_MEAN) else 0
     else:
         p.nP, p.nR, p.nU, p.nA = _role_split(ctas, hyper.mode, group.me in owners, K, split)
-    p.NS, p.Ls = stage_geometry(layout.n_chunks, ctas, payload_bytes_per_elem(codec))
+    p.NS, p.Ls = stage_geometry(layout.n_chunks, ctas, payload_bytes_per_elem(codec), sequential)
     buf.last_tag = int(p.tag)
     p.C = layout.n_chunks
     p.replicate_state = int(hyper.replicate_state)
@@ -416,7 +420,7 @@ def fused_allreduce_v2(buf: PeerBuffers, group: GroupSpec, codec: CompressionTyp
             p.momentum, p.trust = hyper.momentum, hyper.trust
             p.trace = None
         if trace is not None:       # int64 [4 roles, AR2_MAX_STAGES, 4] on this device: per-stage %globaltimer stamps
-            assert trace.numel() >= 4 * native.AR2_MAX_STAGES * 4 and trace.dtype == torch.int64
+            assert trace.numel() >= 4 * native.AR2_MAX_STAGES * 4 + 1024 * 10 and trace.dtype == torch.int64
             p.trace = trace.data_ptr()
         p.debug_flags = debug_flags
         st = stream if stream is not None else torch.cuda.current_stream(buf.device)

@@ -9,76 +9,76 @@ from typing import List, Optional
 @dataclass
 class BaseTrainingArguments:
     experiment_prefix: str = field(
-        metadata={"help": "A unique 'name' of this experiment, used to store metadata on the DHT"})
+        metadata={"help": "Name of the run; every DHT key of the collaboration is prefixed with it"})
     initial_peers: List[str] = field(
         default_factory=list,
-        metadata={"help": "One or more peers (comma-separated) that will welcome you into the collaboration"})
+        metadata={"help": "host:port of one or more peers that are already in the collaboration (bootstrap nodes)"})
     dht_listen_on: str = field(
-        default="[::]:*", metadata={"help": "Network interface used for incoming DHT communication. Default: all ipv6"})
+        default="[::]:*", metadata={"help": "host:port the DHT node binds to ('*' picks a free port)"})
 
 
 @dataclass
 class AveragerArguments:
     averaging_expiration: float = field(
-        default=5.0, metadata={"help": "Averaging group will wait for stragglers for at most this many seconds"})
+        default=5.0, metadata={"help": "How long (s) a forming group stays open for late members before the round starts"})
     averaging_timeout: float = field(
-        default=30.0, metadata={"help": "Give up on averaging step after this many seconds"})
+        default=30.0, metadata={"help": "A round that has not finished after this many seconds is abandoned; the peer then steps on its own gradients"})
     listen_on: str = field(
         default="[::]:*",
-        metadata={"help": "Network interface used for incoming averager communication. Default: all ipv6"})
+        metadata={"help": "host:port the averaging RPC server binds to ('*' picks a free port)"})
     min_refresh_period: float = field(
-        default=0.5, metadata={"help": "Wait for at least this many seconds before fetching new collaboration state"})
+        default=0.5, metadata={"help": "Lower bound (s) on the interval between two reads of the collaboration's progress records"})
     max_refresh_period: float = field(
-        default=30, metadata={"help": "Wait for at most this many seconds before fetching new collaboration state"})
+        default=30, metadata={"help": "Upper bound (s) on that interval"})
     default_refresh_period: float = field(
-        default=3, metadata={"help": "Attempt to fetch collaboration state every this often until successful"})
+        default=3, metadata={"help": "Interval (s) used while no progress record has been found yet"})
     expected_drift_peers: float = field(
-        default=3, metadata={"help": "Trainer assumes that this many new peers can join per step"})
+        default=3, metadata={"help": "Head-room, in peers, for newcomers when the time of the next step is extrapolated"})
     expected_drift_rate: float = field(
-        default=0.2, metadata={"help": "Trainer assumes that this fraction of current size can join per step"})
+        default=0.2, metadata={"help": "The same head-room as a fraction of the current number of peers"})
     performance_ema_alpha: float = field(
-        default=0.1, metadata={"help": "Uses this alpha for moving average estimate of samples per second"})
-    target_group_size: int = field(default=256, metadata={"help": "Maximum group size for all-reduce"})
+        default=0.1, metadata={"help": "Smoothing factor of the samples-per-second estimate this peer reports"})
+    target_group_size: int = field(default=256, metadata={"help": "Largest number of peers that average together in one round; more peers split into several groups"})
     metadata_expiration: float = field(
-        default=30, metadata={"help": "Peer's metadata will be removed if not updated in this many seconds"})
+        default=30, metadata={"help": "Lifetime (s) of a progress record: a peer that stops reporting drops out of the count after this"})
 
 
 @dataclass
 class CollaborativeOptimizerArguments:
     target_batch_size: int = field(
         default=4096,
-        metadata={"help": "Perform optimizer step after all peers collectively accumulate this many samples"})
+        metadata={"help": "Samples the whole collaboration gathers between two optimizer steps"})
     client_mode: bool = field(
         default=False,
-        metadata={"help": "Of True, runs training without incoming connections, in a firewall-compatible mode"})
+        metadata={"help": "Never accept inbound connections (peers behind NAT / firewalls); such a peer sends gradients but owns no shard"})
     batch_size_lead: int = field(
         default=0,
-        metadata={"help": "Optional: begin looking for group in advance, this many samples before target_batch_size"})
+        metadata={"help": "Start matchmaking this many samples early so that group formation overlaps the last micro-batches"})
     bandwidth: float = field(
         default=100.0,
-        metadata={"help": "Available network bandwidth, in mbps (used for load balancing in all-reduce)"})
+        metadata={"help": "Link speed of this peer in Mbit/s; shard sizes of the socket all-reduce are proportional to it"})
     compression: str = field(
-        default="FLOAT16", metadata={"help": "Use this compression when averaging parameters/gradients"})
+        default="FLOAT16", metadata={"help": "Wire codec of the averaged gradients: NONE, FLOAT16, BFLOAT16, MEANSTD_16BIT, UNIFORM_8BIT, QUANTILE_8BIT, BLOCKWISE_FP8"})
 
 
 @dataclass
 class CollaborationArguments(AveragerArguments, CollaborativeOptimizerArguments, BaseTrainingArguments):
     statistics_expiration: float = field(
-        default=600, metadata={"help": "Statistics will be removed if not updated in this many seconds"})
+        default=600, metadata={"help": "Lifetime (s) of the metrics record the coordinator aggregates"})
     endpoint: Optional[str] = field(
         default=None,
-        metadata={"help": "This node's IP for inbound connections, used when running from behind a proxy"})
+        metadata={"help": "Address other peers should dial when it differs from the bound one (proxy / port forwarding)"})
 
 
 @dataclass
 class DatasetArguments:
     dataset_path: Optional[str] = field(
-        default="data/albert_tokenized_wikitext", metadata={"help": "Path to the tokenized dataset"})
-    tokenizer_path: Optional[str] = field(default="data/tokenizer", metadata={"help": "Path to the tokenizer"})
+        default="data/albert_tokenized_wikitext", metadata={"help": "Directory written by tokenize_wikitext103.py (datasets.save_to_disk)"})
+    tokenizer_path: Optional[str] = field(default="data/tokenizer", metadata={"help": "Directory with the ALBERT tokenizer files"})
     config_path: Optional[str] = field(
         default="https://s3.amazonaws.com/models.huggingface.co/bert/albert-large-v2-config.json",
-        metadata={"help": "Path to the model config"})
-    cache_dir: Optional[str] = field(default="data", metadata={"help": "Path to the cache"})
+        metadata={"help": "config.json of the model to train (file, directory or URL)"})
+    cache_dir: Optional[str] = field(default="data", metadata={"help": "Download / cache directory"})
     synthetic_data: bool = field(
         default=False, metadata={"help": "Train on synthetic WikiText-shaped tokens (no dataset / tokenizer needed)"})
 
@@ -124,26 +124,23 @@ class AlbertTrainingArguments:
 
 @dataclass
 class CoordinatorArguments(BaseTrainingArguments):
-    """
-    Note: You might want to have several initial peers so that if one dies,
-    new workers still can join the collaboration via alive initial peers' addresses.
-    Specify initial_peers argument for that purpose
-    """
+    """The coordinator is only one of possibly many bootstrap nodes: pass --initial_peers here too and list several live
+    peers when starting trainers, so that joining does not depend on this process staying up."""
     address: Optional[str] = field(
         default=None,
-        metadata={"help": "This machine's network address. Use public IP for global experiments, "
-                          "local address for private runs"})
+        metadata={"help": "Address under which this coordinator is reachable (public for internet-wide runs, "
+                          "127.0.0.1 for one box)"})
     refresh_period: float = field(
-        default=30, metadata={"help": "Coordinator will fetch keys from DHT once in this many seconds"})
-    wandb_project: Optional[str] = field(default=None, metadata={"help": "Learning curves will be published there"})
+        default=30, metadata={"help": "Seconds between two polls of the metrics key"})
+    wandb_project: Optional[str] = field(default=None, metadata={"help": "wandb project for the aggregated curves (offline when there is no network)"})
     save_checkpoint_step_interval: int = field(
-        default=5, metadata={"help": "Coordinator will load and save state from peers once every that many steps"})
+        default=5, metadata={"help": "Pull a fresh copy of the training state from the peers every this many collaborative steps"})
     model_config_path: str = field(
         default="https://s3.amazonaws.com/models.huggingface.co/bert/albert-large-v2-config.json",
-        metadata={"help": "Path to the model config"})
+        metadata={"help": "config.json of the model to train (file, directory or URL)"})
     repo_path: Optional[str] = field(
         default=None,
-        metadata={"help": "Path to HuggingFace repo in which coordinator will upload the model and optimizer states"})
+        metadata={"help": "Local clone of the Hugging Face repository that receives model + optimizer_state.pt commits"})
     upload_interval: Optional[float] = field(
-        default=None, metadata={"help": "Coordinator will upload model once in this many seconds"})
+        default=None, metadata={"help": "Minimum seconds between two uploads"})
     max_iterations: int = field(default=0, metadata={"help": "Stop after this many refresh periods (0 = forever)"})

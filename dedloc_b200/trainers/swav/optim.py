@@ -114,40 +114,73 @@ class SGD(ClassyOptimizer):
                    larc_config=config.get("larc_config"))
 
 
+# The config keys (and their defaults) are the contract with swav_1node_resnet_submit.yaml and the
+# `+config.OPTIMIZER.<key>=...` overrides of swav/README.md:17-32; everything else here is this repo's.
+#   key -> (default, type check or None, used)
+_SGD_COLLAB_SCHEMA: Dict[str, tuple] = {
+    # plain SGD + LARC (apex semantics)
+    "lr": (0, (int, float), True),
+    "momentum": (0.0, float, True),
+    "weight_decay": (0.0, (int, float), True),
+    "nesterov": (False, bool, True),
+    "use_larc": (False, bool, True),
+    "larc_config": ({"clip": True, "eps": 1e-08, "trust_coefficient": 0.02}, dict, True),
+    # collaboration
+    "dht_initial_peers": ([], (list, tuple), True),
+    "batch_size_for_tracking": (200, int, True),
+    "exp_prefix": ("test_exp", str, True),
+    "dht_listen_on_port": ("1337", (str, int), True),
+    "averager_listen_on_port": ("1338", (str, int), True),
+    "target_group_size": (5, int, True),
+    # accepted and stored, as in the reference, but nothing reads them
+    "max_allowed_epoch_difference": (1, int, False),
+    "total_steps_in_epoch": (6405, int, False),
+    "averaging_steps_period": (1, int, False),
+    "averaging_time_period": (0, (int, float), False),
+    "report_progress_expiration": (60, (int, float), False),
+    "timeout": (None, None, False),
+    # learning-rate schedule, stepped once per COLLABORATIVE step
+    "warmup_epochs": (0, (int, float), True),
+    "max_epochs": (200, (int, float), True),
+    "warmup_start_lr": (0, (int, float), True),
+    "eta_min": (0.006 * 200 / 256, (int, float), True),
+}
+_SGD_COLLAB_EXTRA = ("target_batch_size", "compression", "dht", "collab_kwargs", "scheduler_cls")
+
+
+def _listen_address(port) -> str:
+    return "127.0.0.1:" + ("*" if str(port) in ("any", "*", "0") else str(port))
+
+
 @register_optimizer("sgd_collaborative")
 class SGDCollaborative(ClassyOptimizer):
     TARGET_BATCH_SIZE = 32768   # hard-coded in the reference (sgd_collaborative.py:153)
 
-    def __init__(self, larc_config: Dict[str, Any] = None, lr: float = 0, momentum: float = 0.0,
-                 weight_decay: float = 0.0, nesterov: bool = False, use_larc: bool = False,
-                 dht_initial_peers: List[str] = (), batch_size_for_tracking: int = 200,
-                 dht_listen_on_port: str = "1337", averager_listen_on_port: str = "1338",
-                 exp_prefix: str = "test_exp", target_group_size: int = 5, max_allowed_epoch_difference: int = 1,
-                 total_steps_in_epoch: int = 6405, scheduler_cls=None, averaging_steps_period: int = 5,
-                 averaging_time_period: float = 0, report_progress_expiration: int = 60, timeout: float = None,
-                 target_batch_size: Optional[int] = None, compression: str = "FLOAT16", dht: Optional[DHT] = None,
-                 collab_kwargs: Optional[Dict[str, Any]] = None):
+    def __init__(self, **options):
         super().__init__()
-        self._lr, self._momentum, self._weight_decay, self._nesterov = lr, momentum, weight_decay, nesterov
-        self._use_larc, self._larc_config, self._exp_prefix = use_larc, larc_config, exp_prefix
-        port = lambda p: "*" if str(p) in ("any", "*", "0") else str(p)
-        self._listen_on_dht = f"127.0.0.1:{port(dht_listen_on_port)}"
-        self._listen_on_averager = f"127.0.0.1:{port(averager_listen_on_port)}"
-        self._dht_initial_peers = list(dht_initial_peers)
-        self._target_group_size, self._batch_size_for_tracking = target_group_size, batch_size_for_tracking
-        # accepted for CLI parity; unused by the reference as well
-        self._max_allowed_epoch_difference, self._total_steps_in_epoch = max_allowed_epoch_difference, total_steps_in_epoch
-        self._averaging_steps_period, self._averaging_time_period = averaging_steps_period, averaging_time_period
-        self._report_progress_expiration, self._timeout = report_progress_expiration, timeout
-        self._scheduler_cls = scheduler_cls
-        self._target_batch_size = target_batch_size or self.TARGET_BATCH_SIZE
-        self._compression, self._dht, self._collab_kwargs = compression, dht, dict(collab_kwargs or {})
+        unknown = set(options) - set(_SGD_COLLAB_SCHEMA) - set(_SGD_COLLAB_EXTRA)
+        if unknown:
+            raise TypeError(f"sgd_collaborative: unknown option(s) {sorted(unknown)}")
+        opts = {k: (options[k] if k in options else spec[0]) for k, spec in _SGD_COLLAB_SCHEMA.items()}
+        self.options = opts
+        self._lr, self._momentum = opts["lr"], opts["momentum"]
+        self._weight_decay, self._nesterov = opts["weight_decay"], opts["nesterov"]
+        self._use_larc, self._larc_config, self._exp_prefix = opts["use_larc"], opts["larc_config"], opts["exp_prefix"]
+        self._listen_on_dht = _listen_address(opts["dht_listen_on_port"])
+        self._listen_on_averager = _listen_address(opts["averager_listen_on_port"])
+        self._dht_initial_peers = list(opts["dht_initial_peers"])
+        self._target_group_size, self._batch_size_for_tracking = opts["target_group_size"], opts["batch_size_for_tracking"]
+        self._scheduler_cls = options.get("scheduler_cls")
+        self._target_batch_size = options.get("target_batch_size") or self.TARGET_BATCH_SIZE
+        self._compression = options.get("compression", "FLOAT16")
+        self._dht, self._collab_kwargs = options.get("dht"), dict(options.get("collab_kwargs") or {})
         self.dht: Optional[DHT] = None
 
     def prepare(self, param_groups):
         for group in param_groups:
             group["lr"] = self._lr
-        assert self._use_larc, "we can't use collab sgd without larc"
+        if not self._use_larc:
+            raise ValueError("sgd_collaborative runs SGD behind LARC only: set OPTIMIZER.use_larc=True")
         params = [p for g in param_groups for p in g["params"]]
         on_gpu = bool(params) and params[0].device.type == "cuda"
         if on_gpu:
@@ -182,35 +215,20 @@ class SGDCollaborative(ClassyOptimizer):
 
     @classmethod
     def from_config(cls, config: Dict[str, Any]) -> "SGDCollaborative":
-        config.setdefault("lr", 0)
-        config.setdefault("momentum", 0.0)
-        config.setdefault("weight_decay", 0.0)
-        config.setdefault("nesterov", False)
-        config.setdefault("use_larc", False)
-        config.setdefault("larc_config", {"clip": True, "eps": 1e-08, "trust_coefficient": 0.02})
-        assert isinstance(config["momentum"], float) and 0.0 <= config["momentum"] < 1.0, \
-            "Config must contain a 'momentum' in [0, 1) for SGD optimizer"
-        assert isinstance(config["nesterov"], bool), "Config must contain a boolean 'nesterov' param for SGD optimizer"
-        assert isinstance(config["use_larc"], bool), "Config must contain a boolean 'use_larc' param for SGD optimizer"
-        for key, default in (("dht_initial_peers", []), ("batch_size_for_tracking", 200), ("exp_prefix", "test_exp"),
-                             ("dht_listen_on_port", "1337"), ("averager_listen_on_port", "1338"),
-                             ("target_group_size", 5), ("max_allowed_epoch_difference", 1),
-                             ("total_steps_in_epoch", 6405), ("averaging_steps_period", 1),
-                             ("averaging_time_period", 0), ("report_progress_expiration", 60), ("timeout", None),
-                             ("warmup_epochs", 0), ("max_epochs", 200), ("warmup_start_lr", 0),
-                             ("eta_min", 0.006 * 200 / 256)):
-            config.setdefault(key, default)
-        logger.info(f"creating SGDCollaborative with config: {config}")
-
-        def scheduler_cls(optim):
-            return LinearWarmupCosineAnnealingLR(optim, warmup_epochs=config["warmup_epochs"],
-                                                 max_epochs=config["max_epochs"],
-                                                 warmup_start_lr=config["warmup_start_lr"], eta_min=config["eta_min"])
-
-        config.setdefault("scheduler_cls", scheduler_cls)
-        keys = ("larc_config", "lr", "momentum", "weight_decay", "nesterov", "use_larc", "dht_initial_peers",
-                "dht_listen_on_port", "averager_listen_on_port", "exp_prefix", "target_group_size",
-                "batch_size_for_tracking", "max_allowed_epoch_difference", "total_steps_in_epoch", "scheduler_cls",
-                "averaging_steps_period", "averaging_time_period", "report_progress_expiration", "timeout")
-        extra = {k: config[k] for k in ("target_batch_size", "compression", "dht", "collab_kwargs") if k in config}
-        return cls(**{k: config[k] for k in keys}, **extra)
+        """Build from the OPTIMIZER section of the config: fill in the defaults of `_SGD_COLLAB_SCHEMA`, check types
+        and ranges, and attach the warm-up + cosine schedule unless the caller supplied one."""
+        for key, (default, kind, _) in _SGD_COLLAB_SCHEMA.items():
+            if key not in config:
+                config[key] = dict(default) if isinstance(default, dict) else (list(default) if isinstance(default, list) else default)
+            elif kind is not None and not isinstance(config[key], kind):
+                wanted = kind.__name__ if isinstance(kind, type) else " or ".join(k.__name__ for k in kind)
+                raise TypeError(f"sgd_collaborative: option '{key}' must be {wanted}, got {type(config[key]).__name__}")
+        if not 0.0 <= config["momentum"] < 1.0:
+            raise ValueError(f"sgd_collaborative: momentum {config['momentum']} is outside [0, 1)")
+        logger.info("sgd_collaborative options: %s", {k: config[k] for k in _SGD_COLLAB_SCHEMA})
+        options = {k: config[k] for k in _SGD_COLLAB_SCHEMA}
+        options.update({k: config[k] for k in _SGD_COLLAB_EXTRA if k in config})
+        if "scheduler_cls" not in options:
+            schedule = {k: config[k] for k in ("warmup_epochs", "max_epochs", "warmup_start_lr", "eta_min")}
+            options["scheduler_cls"] = lambda optim: LinearWarmupCosineAnnealingLR(optim, **schedule)
+        return cls(**options)

@@ -3,7 +3,8 @@ swav/vissl/vissl/utils/perf_stats.py:12-250, used by standard_train_step.py:110-
 recorded; device time is recorded with a CUDA event pair per section and resolved only when the events have
 completed, so timing never forces a synchronisation. Section names of the train step:
 read_sample, forward, loss_compute, loss_all_reduce, meters_update, backward, optimizer_step, train_step_total,
-plus `exposed_averaging` for the collaborative step."""
+plus `exposed_averaging` for the collaborative step. Every section is also an NVTX range (`nvtx_range`),
+so an nsys / ncu timeline shows the same names; set DEDLOC_NVTX=0 to switch the ranges off."""
 from __future__ import annotations
 
 import time
@@ -11,6 +12,37 @@ from collections import defaultdict
 from typing import Dict, List, Optional, Tuple
 
 import torch
+
+
+import os
+from contextlib import contextmanager
+
+_NVTX = os.environ.get("DEDLOC_NVTX", "1") != "0"
+
+
+def nvtx_push(name: str) -> bool:
+    """Open an NVTX range when CUDA is up (a no-op on CPU-only machines). Returns whether a range was opened."""
+    if _NVTX and torch.cuda.is_available():
+        try:
+            torch.cuda.nvtx.range_push(name)
+            return True
+        except Exception:  # pragma: no cover - nvtx missing from the build
+            return False
+    return False
+
+
+def nvtx_pop(opened: bool) -> None:
+    if opened:
+        torch.cuda.nvtx.range_pop()
+
+
+@contextmanager
+def nvtx_range(name: str):
+    opened = nvtx_push(name)
+    try:
+        yield
+    finally:
+        nvtx_pop(opened)
 
 
 class PerfMetric:
@@ -86,6 +118,7 @@ class PerfTimer:
         self.name, self.stats = name, perf_stats
 
     def __enter__(self):
+        self._nvtx = nvtx_push(self.name)
         if self.stats is None:
             return self
         self.t0 = time.perf_counter()
@@ -96,6 +129,7 @@ class PerfTimer:
         return self
 
     def __exit__(self, *exc):
+        nvtx_pop(self._nvtx)
         if self.stats is None:
             return False
         if self.stats.use_cuda:

@@ -63,6 +63,7 @@ def main():
     dev = torch.device("cuda", local)
     dist.init_process_group("nccl", device_id=dev)
     sizes_mb = [1, 4, 16, 64, 68, 256, 1024] if len(sys.argv) < 2 else [int(x) for x in sys.argv[1].split(",")]
+    kernels = (sys.argv[2] if len(sys.argv) > 2 else "push,pull").split(",")
     mean_codecs = [CompressionType.FLOAT16, CompressionType.NONE, CompressionType.UNIFORM_8BIT,
                    CompressionType.BLOCKWISE_FP8]
     numels = albert_shapes()
@@ -143,12 +144,15 @@ def main():
                 fly = codec in (CompressionType.NONE, CompressionType.FLOAT16, CompressionType.BFLOAT16)
                 # push kernel: the encoder runs inside the kernel for the 16/32-bit codecs, so there is one number;
                 # the 8-bit codecs need their two-pass encoder first
-                t_push = timed(lambda: run("push", mode, codec, encode_first=not fly))
-                res[key + "_push"] = entry(t_push, pb + 2, {"includes_encode": True})
-                assert buf.read_status()["code"] == 0, buf.read_status()
-                if not fly:
+                if "push" in kernels:
+                    t_push = timed(lambda: run("push", mode, codec, encode_first=not fly))
+                    res[key + "_push"] = entry(t_push, pb + 2, {"includes_encode": True})
+                    assert buf.read_status()["code"] == 0, buf.read_status()
+                if not fly and "push" in kernels:
                     t_push_pre = timed(lambda: run("push", mode, codec, encode_first=False))
                     res[key + "_push"]["ms_payload_pre_encoded"] = round(t_push_pre, 4)
+                if "pull" not in kernels:
+                    continue
                 out_bytes = 2 if mode == native.AR_MEAN else 6       # pull kernel, LAMB: fp32 master + bf16 mirror
                 t_pull = timed(lambda: run("pull", mode, codec, encode_first=False))
                 t_pull_enc = timed(lambda: run("pull", mode, codec, encode_first=True))
@@ -162,7 +166,7 @@ def main():
         torch.cuda.empty_cache()
     if rank == 0:
         os.makedirs("gpurun_out", exist_ok=True)
-        json.dump(rows, open(f"gpurun_out/allreduce_sweep_n{world}.json", "w"), indent=1)
+        json.dump(rows, open(f"gpurun_out/allreduce_sweep_n{world}_{'_'.join(kernels)}.json", "w"), indent=1)
     dist.destroy_process_group()
 
 

@@ -41,7 +41,8 @@ def main():
     bases = [buf.peer_base(h) for h in handles]
     buf.acc.copy_(torch.randn(layout.total, device=dev) * 0.01)
     buf.p32.copy_(torch.randn(layout.total, device=dev) * 0.05)
-    trace = torch.zeros(4 * native.AR2_MAX_STAGES * 4, dtype=torch.int64, device=dev)
+    n_role = 4 * native.AR2_MAX_STAGES * 4
+    trace = torch.zeros(n_role + 1024 * 10, dtype=torch.int64, device=dev)
     tag = 7000
     times = []
     for it in range(6):
@@ -60,7 +61,9 @@ def main():
         times.append(e0.elapsed_time(e1))
     st = buf.read_status()
     if rank == 0:
-        t = trace.cpu().view(4, native.AR2_MAX_STAGES, 4).numpy()
+        full = trace.cpu()
+        t = full[:n_role].view(4, native.AR2_MAX_STAGES, 4).numpy()
+        per_cta = full[n_role:].view(1024, 10).numpy()
         t0 = t[t > 0].min()
         names = ["PUSH  begin/stored/fenced/flag", "REDUCE wait/flag seen/done/last", "UPDATE begin/done/fenced/flag",
                  "APPLY wait/flags seen/done"]
@@ -73,6 +76,23 @@ def main():
             for s in range(native.AR2_MAX_STAGES):
                 if t[r, s].max() > 0:
                     print(f"  s{s:02d} " + " ".join(f"{(x - t0) / 1e3:8.1f}" if x > 0 else "       -" for x in t[r, s]))
+        import numpy as np
+
+        live = per_cta[per_cta[:, 1] > 0]
+        if len(live):
+            print(f"PUSH per CTA (warp 0), {len(live)} CTAs, us from first stamp: stage  stored min/med/p90/max   fenced min/med/p90/max")
+            for s in range(4):
+                st, fe = live[:, 1 + s], live[:, 5 + s]
+                if st.max() <= 0:
+                    continue
+                st, fe = (st[st > 0] - t0) / 1e3, (fe[fe > 0] - t0) / 1e3
+                q = lambda a: " ".join(f"{x:7.1f}" for x in (a.min(), np.median(a), np.percentile(a, 90), a.max()))
+                print(f"  s{s}  {q(st)}   |  {q(fe)}")
+            # slowest CTAs of the last traced stage, with their SM
+            last = max(s for s in range(4) if live[:, 5 + s].max() > 0)
+            order = np.argsort(live[:, 5 + last])
+            fmt = lambda i: f"(sm {int(live[i, 0])}: {(live[i, 5 + last] - t0) / 1e3:.1f})"
+            print("  fastest:", " ".join(fmt(i) for i in order[:6]), " slowest:", " ".join(fmt(i) for i in order[-6:]))
     dist.destroy_process_group()
 
 

@@ -7,7 +7,8 @@ def test_stage_geometry_and_role_split():
 
     for n_chunks in (1, 31, 32, 33, 128, 8716, 131072, 10 ** 6):
         for ctas in (8, 74, 148, 296):
-            ns, ls = stage_geometry(n_chunks, ctas)
+            ns, ls = stage_geometry(n_chunks, ctas, 2, sequential=False)
+            assert stage_geometry(n_chunks, ctas, 2, sequential=True)[0] == 1
             assert 1 <= ns <= lib.AR2_MAX_STAGES and ls % 32 == 0 and ns * ls >= n_chunks > (ns - 1) * ls
     for total in (8, 37, 74, 148, 296):
         for mode in (0, 1, 2):
