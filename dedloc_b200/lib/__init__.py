@@ -90,6 +90,18 @@ class AR2Params(C.Structure):
     ]
 
 
+class NvlsParams(C.Structure):
+    """Mirror of DedlocNvlsParams."""
+
+    _fields_ = [
+        ("mc_base", C.c_void_p), ("uc_base", C.c_void_p), ("n", C.c_longlong),
+        ("off_flags", C.c_longlong), ("off_payload", C.c_longlong), ("off_result", C.c_longlong),
+        ("P", C.c_int), ("me", C.c_int), ("round", C.c_uint32), ("ctas", C.c_int),
+        ("payload_is_bf16", C.c_int), ("reserved", C.c_int), ("timeout_ns", C.c_ulonglong),
+        ("status", C.c_void_p), ("out16", C.c_void_p), ("out32", C.c_void_p),
+    ]
+
+
 class GemmArgs(C.Structure):
     """Mirror of DedlocGemmArgs."""
 
@@ -145,6 +157,9 @@ def _declare(lib: C.CDLL) -> None:
     lib.dedloc_ar2_params_size.restype = i
     lib.dedloc_ar2_max_ctas.argtypes = [i, i]
     lib.dedloc_ar2_max_ctas.restype = i
+    lib.dedloc_nvls_allreduce_mean.argtypes = [C.POINTER(NvlsParams), vp]
+    lib.dedloc_nvls_allreduce_mean.restype = i
+    lib.dedloc_nvls_params_size.restype = i
     lib.dedloc_gemm.argtypes = [C.POINTER(GemmArgs), vp]
     lib.dedloc_layernorm_fwd.argtypes = [vp, vp, vp, vp, vp, vp, i, i, f, vp]
     lib.dedloc_layernorm_bwd.argtypes = [vp, vp, vp, vp, vp, vp, vp, vp, i, i, vp]

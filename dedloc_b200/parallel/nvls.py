@@ -189,7 +189,7 @@ class NvlsWindow:
             self.size = (need + gran - 1) // gran * gran
             self.handle = _ck(cu.cuMemCreate(self.size, _alloc_prop(device), 0), "cuMemCreate")
             self.ptr = _map_rw(self.handle, self.size, device)
-            _ck(cu.cuMemsetD8(self.ptr, 0, self.size), "cuMemsetD8")
+            _ck(cu.cuMemsetD8(cu.CUdeviceptr(self.ptr), 0, self.size), "cuMemsetD8")
         self.off_flags, self.off_payload, self.off_result = 0, self.FLAG_BYTES, self.FLAG_BYTES + 2 * self.n
         self.key = f"win-{os.getpid()}-{id(self):x}"
         fd = _ck(cu.cuMemExportToShareableHandle(
@@ -238,3 +238,71 @@ class NvlsGroup:
             arrive(leader, "bound-" + group_key, self.P, timeout)
             self.mc_ptr = _map_rw(self.mc, size, dev)
         self.round = 0        # the barrier counters in the flag page only ever grow
+
+
+# --------------------------------------------------------------------------------------------------- the operation
+class NvlsAllreduce:
+    """Weighted mean of a flat fp32 vector across a group, reduced inside the NVSwitch (csrc/nvls_allreduce.cu).
+
+    One instance per peer and vector length. `group()` builds (once per composition) the multicast object;
+    `allreduce()` encodes `src * weight` as fp16 / bf16 into the window and launches the kernel. The result lands in
+    the window as bf16 and, if asked, in `out16` / `out32`."""
+
+    def __init__(self, n_elems: int, device: int, server: Optional[FdServer] = None):
+        import torch
+
+        from .. import lib as native
+
+        self.native = native
+        self.server = server or FdServer()
+        self.window = NvlsWindow(n_elems, device, self.server)
+        self.device, self.n = device, int(n_elems)
+        self._groups: Dict[str, NvlsGroup] = {}
+        self.status = torch.zeros(16, dtype=torch.int32, device=f"cuda:{device}")
+        self.payload16 = self.window.tensor(self.window.off_payload, 2 * self.n, torch.uint8)
+        self.result = self.window.tensor(self.window.off_result, self.n, torch.bfloat16)
+        self._aux = torch.zeros(1, dtype=torch.float32, device=f"cuda:{device}")
+        props = torch.cuda.get_device_properties(device)
+        self.ctas = props.multi_processor_count * 4
+
+    @property
+    def sock(self) -> str:
+        return self.server.path
+
+    def group(self, socks: Sequence[str], me: int, salt: str = "", timeout: float = 30.0) -> NvlsGroup:
+        """`socks`: the members' FdServer paths in group order; `salt` tells apart several windows of the same peers
+        (every member must pass the same string)."""
+        import hashlib
+
+        key = hashlib.sha1(("|".join(socks) + "#" + salt).encode()).hexdigest()[:16]
+        g = self._groups.get(key)
+        if g is None:
+            g = self._groups[key] = NvlsGroup(self.window, list(socks), me, key, timeout)
+        return g
+
+    def allreduce(self, src, weight: float, group: NvlsGroup, out16=None, out32=None, bf16_payload: bool = False,
+                  timeout_s: float = 20.0, stream=None) -> None:
+        """result = sum over members of (src_i * weight_i); pass normalised weights for a weighted mean."""
+        import ctypes as C
+
+        import torch
+
+        from ..ops import flat_ops
+        from ..utils.compression import CompressionType
+
+        native = self.native
+        codec = CompressionType.BFLOAT16 if bf16_payload else CompressionType.FLOAT16
+        with torch.cuda.device(self.device):
+            flat_ops.encode(codec, src, float(weight), self.payload16, self._aux)
+            group.round += 1
+            p = native.NvlsParams()
+            p.mc_base, p.uc_base, p.n = group.mc_ptr, self.window.ptr, self.n
+            p.off_flags, p.off_payload, p.off_result = self.window.off_flags, self.window.off_payload, self.window.off_result
+            p.P, p.me, p.round, p.ctas = group.P, group.me, group.round, self.ctas
+            p.payload_is_bf16 = int(bf16_payload)
+            p.timeout_ns = int(timeout_s * 1e9)
+            p.status = self.status.data_ptr()
+            p.out16 = out16.data_ptr() if out16 is not None else None
+            p.out32 = out32.data_ptr() if out32 is not None else None
+            st = stream if stream is not None else torch.cuda.current_stream(self.device)
+            native.check(native.lib().dedloc_nvls_allreduce_mean(C.byref(p), st.cuda_stream), "nvls_allreduce")

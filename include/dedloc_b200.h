@@ -160,6 +160,27 @@ int dedloc_fused_allreduce_v2(const DedlocAR2Params* params, int n_ranks, void* 
 int dedloc_ar2_params_size(void);
 int dedloc_ar2_max_ctas(int mode, int codec);   /* co-resident CTAs of the kernel on the current device */
 
+/* ---- NVLS variant of the weighted mean (csrc/nvls_allreduce.cu): in-switch reduction with multimem.ld_reduce,
+ *      broadcast of the result with multimem.st, barriers with multimem.red. The windows are CUDA VMM allocations
+ *      bound to a multicast object (dedloc_b200/parallel/nvls.py). Same reference call site as dedloc_fused_allreduce. */
+typedef struct DedlocNvlsParams {
+  void* mc_base;                 /* multicast address of the window (all members at once) */
+  void* uc_base;                 /* ordinary address of MY window */
+  long long n;                   /* elements, multiple of the chunk size */
+  long long off_flags, off_payload, off_result;   /* byte offsets inside the window */
+  int P, me;
+  uint32_t round;                /* 1, 2, 3, ...: the barrier counters only grow */
+  int ctas;                      /* grid size; must be the same on every member */
+  int payload_is_bf16;           /* else fp16 */
+  int reserved;
+  unsigned long long timeout_ns;
+  uint32_t* status;
+  uint16_t* out16;               /* optional: bf16 copy of the result */
+  float* out32;                  /* optional: fp32 copy of the result */
+} DedlocNvlsParams;
+int dedloc_nvls_allreduce_mean(const DedlocNvlsParams* params, void* stream);
+int dedloc_nvls_params_size(void);
+
 /* ---- tcgen05/TMEM/TMA GEMM with fused epilogues (cuBLAS calls under HF AlbertForPreTraining built at
  *      albert/run_trainer.py:64-68 and the VISSL swav_head, swav_prototypes_head.py:64-110) ----------- */
 enum {
