@@ -712,6 +712,18 @@ __device__ void role_apply(const Params& p, int b, float* red) {
 
 template <int CODEC, int MODE>
 __device__ __forceinline__ void run_role(const Params& p, int b, float* red, float* lut, int* s_last) {
+  if (p.debug_flags >> 8) {
+    // test hook: this member starts late, by a pseudo-random time below (debug_flags >> 8) * 16 us that depends on
+    // the round tag (bit 7 set: by exactly that time) -- arrival skew for the flag soak, a parked kernel for the
+    // "peer dies inside the kernel" test
+    if (threadIdx.x == 0) {
+      const unsigned long long span = (unsigned long long)((unsigned)p.debug_flags >> 8) * 16000ull;
+      const unsigned long long wait = (p.debug_flags & 128) ? span : ((p.tag * 2654435761u + (unsigned)p.me * 40503u) % 1000u) * span / 1000u;
+      const unsigned long long t0 = globaltimer_ns();
+      while (globaltimer_ns() - t0 < wait) __nanosleep(200);
+    }
+    __syncthreads();
+  }
   if (p.sequential) {
     // Every CTA runs the four roles one after the other over ALL stages (nP = nR = nU = nA = grid): each phase has
     // the whole chip, which hides load latency far better than a quarter of the CTAs per role, and both the gradient

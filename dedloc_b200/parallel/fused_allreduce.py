@@ -431,7 +431,8 @@ def fused_allreduce_v2(buf: PeerBuffers, group: GroupSpec, codec: CompressionTyp
 def fused_allreduce_v2_emulated(bufs: Sequence[PeerBuffers], weights: Sequence[float], shards: Sequence[tuple],
                                 codec: CompressionType, hyper: OptHyper, tag: int, src_f32: bool = True,
                                 scale: float = 1.0, write_p16: bool = True, mean_out32: bool = True,
-                                timeout_s: float = 20.0, ctas_per_rank: int = 0, split=None) -> None:
+                                timeout_s: float = 20.0, ctas_per_rank: int = 0, split=None,
+                                debug_flags: int = 0) -> None:
     """All members of a group as ONE cooperative launch over buffer sets on one GPU (tests, single-GPU soak runs):
     co-dependent ranks must not be separate launches on one device. The device code is the production code."""
     P = len(bufs)
@@ -447,6 +448,7 @@ def fused_allreduce_v2_emulated(bufs: Sequence[PeerBuffers], weights: Sequence[f
                           tag=tag, timeout_s=timeout_s)
             assert v2_supported(bufs[rnk].layout, bufs[rnk].regions, g, codec)
             _fill_v2(arr[rnk], bufs[rnk], g, codec, hyper, ctas, src_f32, scale, write_p16, mean_out32, split)
+            arr[rnk].debug_flags = debug_flags
         st = torch.cuda.current_stream(dev)
         native.check(native.lib().dedloc_fused_allreduce_v2(arr, P, bufs[0].params_dev.data_ptr(), st.cuda_stream),
                      "fused_allreduce_v2 (emulated ranks)")

@@ -151,7 +151,9 @@ typedef struct DedlocAR2Params {
   float* m_all[DEDLOC_MAX_PEERS];             /* replicate_state targets */
   float* v_all[DEDLOC_MAX_PEERS];
   unsigned long long* trace;                  /* optional [4 roles][MAX_STAGES][4] %globaltimer stamps of CTA 0 of each role */
-  int debug_flags;                            /* diagnostics only; 1 = omit the system-scope fences (results undefined) */
+  int debug_flags;                            /* tests / diagnostics: 1 omit system fences, 2 omit per-warp fences, 4 keep PUSH local
+                                                 (results undefined for 1, 2, 4); bits 8.. = start this member late by up to
+                                                 (flags >> 8) * 16 us (bit 7: exactly) */
   int sequential;                             /* 1: every CTA runs PUSH, REDUCE, UPDATE, APPLY one after the other (all n* = grid) */
 } DedlocAR2Params;
 

@@ -2,7 +2,8 @@
 gradient) at 2/4/8 GPUs vs NCCL, in MEAN mode (plain weighted all-reduce) and in LAMB mode (the production call:
 all-reduce + trust-ratio update on the owned shard + all-gather of the result).
 
-    python -m torch.distributed.run --nproc-per-node N --master-addr 127.0.0.1 scripts/bench_allreduce.py [sizes_mb]
+    python -m torch.distributed.run --nproc-per-node N --master-addr 127.0.0.1 scripts/bench_allreduce.py \
+        [sizes_mb] [kernels: push,pull,nvls]
 
 The vector keeps ALBERT-large's tensor structure (32 tensors; scaled down below 68 MB, repeated above), because LAMB
 needs per-tensor norms. Two kernels: `push` = csrc/fused_allreduce_v2.cu (push-based, stage-pipelined, 2 bytes per
@@ -68,6 +69,7 @@ def main():
                    CompressionType.BLOCKWISE_FP8]
     numels = albert_shapes()
     rows = []
+    nvls_server = [None]
     tag = [1000]
     frac = (world - 1) / world
 
@@ -159,6 +161,23 @@ def main():
                 res[key + "_pull"] = entry(t_pull_enc, pb + out_bytes,
                                            {"includes_encode": True, "ms_payload_pre_encoded": round(t_pull, 4)})
                 assert buf.read_status()["code"] == 0, buf.read_status()
+        if "nvls" in kernels:
+            # in-switch reduction (csrc/nvls_allreduce.cu): fp32 -> fp16 encode + multimem all-reduce, bf16 result
+            from dedloc_b200.parallel import nvls
+
+            if nvls.multicast_supported(local):
+                if nvls_server[0] is None:
+                    nvls_server[0] = nvls.FdServer()
+                ar = nvls.NvlsAllreduce(n, local, nvls_server[0])
+                ids = [None] * world
+                dist.all_gather_object(ids, nvls_server[0].path + "#" + ar.window.key)
+                grp = ar.group([s.split("#")[0] for s in ids], rank, salt="|".join(s.split("#")[1] for s in ids))
+                t_nvls = timed(lambda: ar.allreduce(buf.acc, 1.0 / world, grp, out16=buf.p16))
+                # per GPU and direction: N/P reduced elements in + the other members' pulls out, and the mirror image
+                # for the result: about (P+1)/P * n * 2 B; the fraction below uses the peer-to-peer byte count so that
+                # the columns stay comparable (it can exceed 1)
+                res["MEAN_FLOAT16_nvls"] = entry(t_nvls, 4, {"includes_encode": True})
+                assert int(ar.status[0]) == 0
         rows.append(res)
         if rank == 0:
             print(json.dumps(res), flush=True)

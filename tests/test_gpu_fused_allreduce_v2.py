@@ -251,3 +251,35 @@ def test_absent_member_times_out_cleanly(native):
         assert b.read_status()["name"] == "abort_before_reduce", b.read_status()
         assert torch.equal(b.p32, flat_p)
         assert b.m.abs().max().item() == 0.0
+
+
+@pytest.mark.parametrize("schedule", ["sequential", "concurrent"])
+def test_flag_protocol_soak(native, schedule, monkeypatch):
+    """Thousands of back-to-back rounds with a fresh tag each and members that start up to ~50 us apart: a stale flag, a
+    norm word of the previous round or a counter that did not reset would let a member run ahead on old data. The
+    gradient scale changes every round, so every round has a different right answer; errors are counted on the
+    device and read once."""
+    from dedloc_b200.parallel.fused_allreduce import OptHyper, fused_allreduce_v2_emulated
+
+    monkeypatch.setenv("DEDLOC_AR2_SCHEDULE", schedule)
+    monkeypatch.setenv("DEDLOC_AR2_STAGE_MB", "0.25")
+    P, rounds = 4, 1500
+    shapes = [(96, 128), (64,), (640, 64), (3,)]
+    layout, bufs, _, grads = _setup(P, seed=11, with_state=False, shapes=shapes)
+    weights = [1.0, 2.0, 3.0, 2.0]
+    for r in range(P):
+        bufs[r].acc.copy_(layout.pack(grads[r]).cuda())
+    wsum = sum(weights)
+    base = sum(w / wsum * layout.pack(grads[r]) for r, w in enumerate(weights)).cuda()
+    bad = torch.zeros((), dtype=torch.int64, device="cuda")
+    for i in range(rounds):
+        scale = 1.0 + (i % 7) * 0.25
+        fused_allreduce_v2_emulated(bufs, weights, _owners([1] * P), CompressionType.NONE, OptHyper(mode=0),
+                                    tag=10_000 + i, scale=scale, debug_flags=(3 << 8))
+        ref = base * scale
+        for b in (bufs[i % P],):                       # one member per round keeps the host side cheap
+            bad += ((b.p32 - ref).abs().max() > 1e-6).long()
+    torch.cuda.synchronize()
+    assert int(bad) == 0
+    for b in bufs:
+        assert b.read_status()["code"] == 0

@@ -59,3 +59,20 @@ def test_late_joiner_and_peer_death(tmp_path):
         assert a["digests"][s] == b["digests"][s], (s, a["digests"][s], b["digests"][s])
     assert a["death_step"] is not None and a["local_step"] >= a["death_step"] + 3, a   # kept going after the peer died
     assert a["stats"]["solo_rounds"] >= 1, a["stats"]
+
+
+def test_nvls_multimem_allreduce_two_gpus():
+    """In-switch reduction (multimem.ld_reduce / multimem.st / multimem.red over a multicast object bound to CUDA VMM
+    windows): weighted mean on 2 GPUs against a torch reference. Skipped when the device has no multicast support."""
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs 2 GPUs")
+    from dedloc_b200.parallel import nvls
+
+    if not nvls.multicast_supported(0):
+        pytest.skip("no NVLS / multicast support on this device")
+    port = 29900 + (os.getpid() % 90)
+    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node=2", "--master-addr",
+           "127.0.0.1", "--master-port", str(port), os.path.join(ROOT, "scripts", "test_nvls.py"), "4,20"]
+    res = subprocess.run(cmd, capture_output=True, text=True, timeout=300, cwd=ROOT)
+    assert res.returncode == 0, res.stdout[-3000:] + res.stderr[-3000:]
+    assert "NVLS OK" in res.stdout
