@@ -42,6 +42,9 @@ def parse_args():
                     help="sahajbert = ALBERT-large with the 32 000-entry Bengali vocabulary (BASELINE.json config 3)")
     ap.add_argument("--ops", default="native", choices=["native", "torch"], help="linear layers: tcgen05 or torch")
     ap.add_argument("--skip-e2e", action="store_true")
+    ap.add_argument("--padded", action="store_true",
+                    help="instances of random length in [S/2, S] with padding and a real attention mask (the masked "
+                         "attention kernel) instead of full-length sequences")
     ap.add_argument("--ddp-micro-batch", type=int, default=0,
                     help="micro-batch of the --impl ddp arm (0 = the same as ours, halved until it fits in memory)")
     ap.add_argument("--ddp-variant", default="stock", choices=["stock", "fp16hook", "best"],
@@ -163,7 +166,7 @@ def main_ours(args):
                      averaging_expiration=5.0, averaging_timeout=60.0, impl=args.ops,
                      overlap_wgrad=args.overlap_wgrad)
     trainer = build_albert_peer(dht, cfg, model_cfg, device=device, seed=0)
-    data = SyntheticMLMBatches(model_cfg.vocab_size, seq, args.micro_batch, seed=1234 + rank)
+    data = SyntheticMLMBatches(model_cfg.vocab_size, seq, args.micro_batch, seed=1234 + rank, padded=args.padded)
     resident = [data.to_device(b, device) for b in data.batches]   # device-resident copies for the kernel-timed arm
     graphed = False if args.no_cuda_graph else trainer.enable_cuda_graph(resident[0])
     barrier()
@@ -245,6 +248,7 @@ def main_ours(args):
             "config": {"model": args.model, "global_batch": args.target_batch_size, "seq_len": seq,
                        "parallelism": f"dedloc-dp{world}", "optimizer": "LAMB (fused in all-reduce kernel)",
                        "micro_batch": args.micro_batch, "compression": args.compression, "linear_ops": args.ops,
+                       "padded_inputs": bool(args.padded),
                        "cuda_graph_micro_step": bool(graphed),
                        "samples_per_step_measured": round(dev["samples"] / args.steps, 1),
                        "l2": "inputs larger than L2 (activations of one micro-batch >> 126 MB)",

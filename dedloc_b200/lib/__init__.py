@@ -174,6 +174,21 @@ def _declare(lib: C.CDLL) -> None:
     lib.dedloc_attention_bwd_scratch_floats.restype = ll
     lib.dedloc_attention_bwd.argtypes = [vp, vp, vp, vp, vp, vp, vp, i, i, i, i, f, vp]
     lib.dedloc_attention_bwd.restype = i
+    newer = {
+        "dedloc_embed_ln_fwd": [vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, i, i, i, f, vp],
+        "dedloc_embed_ln_bwd": [vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, i, i, i, ll, i, vp],
+        "dedloc_ln128_fwd": [vp, vp, vp, vp, vp, vp, i, f, vp],
+        "dedloc_ln128_bwd": [vp, vp, vp, vp, vp, vp, vp, vp, i, vp],
+        "dedloc_l2norm128_fwd": [vp, vp, i, f, vp],
+        "dedloc_l2norm128_bwd": [vp, vp, vp, i, f, vp],
+        "dedloc_swav_ce_fwd": [vp, i, ll, vp, i, vp, i, i, i, f, vp, vp, vp],
+        "dedloc_swav_ce_bwd": [vp, i, ll, vp, i, vp, i, i, i, f, vp, vp, vp, vp],
+    }
+    for name, argtypes in newer.items():
+        if not hasattr(lib, name):
+            raise NativeError(f"{LIB_PATH} is older than its Python binding (no {name}): run `python -m dedloc_b200._build`")
+        fn = getattr(lib, name)
+        fn.argtypes, fn.restype = argtypes, i
     lib.dedloc_ce_fwd.argtypes = [vp, ll, vp, i, i, vp, vp, vp]
     lib.dedloc_ce_fwd.restype = i
     lib.dedloc_ce_bwd.argtypes = [vp, ll, vp, vp, vp, vp, ll, i, i, vp]

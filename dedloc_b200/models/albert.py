@@ -148,8 +148,15 @@ class AlbertEmbeddings(nn.Module):
         self.LayerNorm = nn.LayerNorm(cfg.embedding_size, eps=cfg.layer_norm_eps)
         self.dropout_p = cfg.hidden_dropout_prob
 
-    def forward(self, input_ids, token_type_ids):
+    def forward(self, input_ids, token_type_ids, impl: str = "torch"):
         S = input_ids.shape[1]
+        if impl == "native" and input_ids.is_cuda:
+            from ..ops import embedding as _emb
+
+            if _emb.embed_supported(self, input_ids) and S <= self.position_embeddings.weight.shape[0]:
+                # gather + add + LayerNorm(128) in one kernel; its backward also does the three embedding backwards
+                x = _emb.embed_layer_norm(self, input_ids, token_type_ids)
+                return F.dropout(x, self.dropout_p, self.training)
         pos = torch.arange(S, device=input_ids.device)
         x = self.word_embeddings(input_ids) + self.token_type_embeddings(token_type_ids) \
             + self.position_embeddings(pos)[None]
@@ -277,7 +284,7 @@ class AlbertModel(nn.Module):
 
     def forward(self, input_ids, attention_mask, token_type_ids, impl: str, pending_flush: list):
         cfg = self.cfg
-        x = self.embeddings(input_ids, token_type_ids)
+        x = self.embeddings(input_ids, token_type_ids, impl)
         x = fused_linear(x, self.encoder.embedding_hidden_mapping_in, impl)
         attn_bias = None
         if attention_mask is not None:
@@ -319,6 +326,11 @@ class AlbertMLMHead(nn.Module):
 
     def hidden(self, x, impl: str):
         h = fused_linear(x, self.dense, impl, act="gelu")
+        if impl == "native" and h.is_cuda:
+            from ..ops import embedding as _emb
+
+            if _emb.ln128_supported(h, self.LayerNorm):
+                return _emb.layer_norm128(h, self.LayerNorm)
         return self.LayerNorm(h)
 
 
@@ -350,6 +362,8 @@ class AlbertForPreTraining(nn.Module):
         self.config = cfg
         self.impl = impl
         self.max_predictions_ratio = max_predictions_ratio
+        # masked positions that did not fit the static MLM capacity since the last read (0 with the 15 % recipe)
+        self.register_buffer("mlm_dropped", torch.zeros((), dtype=torch.int64), persistent=False)
         self.albert = AlbertModel(cfg)
         self.predictions = AlbertMLMHead(cfg)
         self.sop_classifier = AlbertSOPHead(cfg)
@@ -433,8 +447,13 @@ class AlbertForPreTraining(nn.Module):
                 per_tok = _ce.cross_entropy_rows(logits, sel_labels.clamp_min(0))
             else:
                 per_tok = F.cross_entropy(logits.float(), sel_labels.clamp_min(0), reduction="none")
-            denom = is_masked.sum().clamp_min(1)
-            # positions beyond the capacity (never with 15% masking) would be dropped from the numerator only
+            n_masked = is_masked.sum()
+            # The capacity is static (no host sync, CUDA-graph friendly). Positions beyond it cannot be scored, so they
+            # are taken out of the denominator too (the loss stays the mean over the scored positions) and counted on
+            # the device: `mlm_dropped_positions()` reports them and the trainers warn when it is not zero.
+            n_scored = sel_valid.sum()
+            self.mlm_dropped += (n_masked - n_scored).to(self.mlm_dropped.dtype)
+            denom = n_scored.clamp_min(1)
             mlm_loss = (per_tok * sel_valid).sum() / denom
             out.mlm_loss = mlm_loss
             out.loss = mlm_loss
@@ -442,6 +461,13 @@ class AlbertForPreTraining(nn.Module):
                 out.sop_loss = F.cross_entropy(sop_logits.float(), sentence_order_label.reshape(-1))
                 out.loss = mlm_loss + out.sop_loss
         return out
+
+    def mlm_dropped_positions(self, reset: bool = True) -> int:
+        """Masked positions beyond `max_predictions_ratio` of the tokens that were left out of the loss (host read)."""
+        n = int(self.mlm_dropped.item())
+        if reset and n:
+            self.mlm_dropped.zero_()
+        return n
 
     def flush_fused_grads(self) -> None:
         """Scatter the fused-QKV weight gradients into the per-parameter main_grad buffers (after backward)."""

@@ -69,7 +69,59 @@ class SwAVPrototypesHead(nn.Module):
     def prototypes(self, i: int) -> nn.Linear:
         return getattr(self, f"prototypes{i}")
 
+    def _native_ok(self, feats: torch.Tensor) -> bool:
+        """The head runs on this repo's kernels when it sits on a GPU, its parameters carry the fused optimizer's fp32
+        `main_grad` buffers, and the shapes suit the tcgen05 GEMM (token count and widths multiples of 64; the
+        prototype count only needs a multiple of 8: TMA zero-fills the tail of the 64-wide K block)."""
+        if not (feats.is_cuda and feats.dim() == 2 and feats.shape[0] % 64 == 0 and self.normalize_feats):
+            return False
+        lins = [m for m in self.projection_head if isinstance(m, nn.Linear)]
+        protos = [self.prototypes(i) for i in range(self.nmb_heads)]
+        if len(lins) != 2 or lins[-1].out_features != 128:
+            return False
+        from .. import lib as native
+
+        if not native.available():
+            return False
+        for lin in lins + protos:
+            if getattr(lin.weight, "main_grad", None) is None or lin.in_features % 64 or lin.out_features % 8:
+                return False
+            if lin.bias is not None and getattr(lin.bias, "main_grad", None) is None:
+                return False
+        return all(l.out_features % 64 == 0 for l in lins)
+
+    def _forward_native(self, feats: torch.Tensor) -> List[torch.Tensor]:
+        """C13 on the repo's kernels: Linear 2048 -> 2048 (tcgen05 GEMM, bias in the epilogue) -> BatchNorm1d + ReLU
+        (batch statistics: PyTorch) -> Linear 2048 -> 128 (GEMM) -> L2-normalise (csrc/swav_ops.cu) -> prototypes
+        128 -> 3000 (GEMM). Weight and bias gradients accumulate into the fp32 main_grad buffers (wgrad GEMM)."""
+        from ..ops.gemm import linear as native_linear
+        from ..ops.swav_ops import l2_normalize128
+
+        def lin16(x, lin):
+            w = lin.weight.detach().to(torch.bfloat16)
+            b = lin.bias.detach().to(torch.bfloat16) if lin.bias is not None else None
+            return native_linear(x, w, b, wgrad_out=lin.weight.main_grad,
+                                 bgrad_out=lin.bias.main_grad if lin.bias is not None else None)
+
+        x = feats.to(torch.bfloat16)
+        if not x.requires_grad:
+            x.requires_grad_(feats.requires_grad)
+        for m in self.projection_head:
+            if isinstance(m, nn.Linear):
+                x = lin16(x, m)
+            else:
+                x = m(x)                      # BatchNorm1d (bf16 in, fp32 statistics) / ReLU
+                if x.dtype != torch.bfloat16:
+                    x = x.to(torch.bfloat16)
+        x = l2_normalize128(x.contiguous())
+        out = [x] if self.return_embeddings else []
+        for i in range(self.nmb_heads):
+            out.append(lin16(x, self.prototypes(i)))
+        return out
+
     def forward(self, feats: torch.Tensor) -> List[torch.Tensor]:
+        if self._native_ok(feats):
+            return self._forward_native(feats)
         x = self.projection_head(feats)
         if self.normalize_feats:
             x = F.normalize(x, dim=1, p=2)
@@ -174,6 +226,19 @@ class SwAVLoss(nn.Module):
     def criterion(self, scores: torch.Tensor, head_id: int) -> torch.Tensor:
         assert scores.shape[0] % self.num_crops == 0
         bs = scores.shape[0] // self.num_crops
+        from ..ops import swav_ops
+
+        if swav_ops.swav_ce_supported(scores) and not self.use_double_precision:
+            # C15: assignments first (Sinkhorn kernel, no gradient), then ONE kernel for log-softmax + all dot products
+            with torch.no_grad():
+                qs = []
+                for i, crop_id in enumerate(self.crops_for_assign):
+                    s = scores[bs * crop_id: bs * (crop_id + 1)].detach()
+                    if self.use_queue:
+                        s = torch.cat((s, getattr(self, f"local_queue{head_id}")[i].to(s.dtype)))
+                    qs.append(self.assignments(s, bs).float())
+                q_all = torch.stack(qs)
+            return swav_ops.swav_cross_entropy(scores, q_all, self.crops_for_assign, self.num_crops, self.temperature)
         logp = F.log_softmax(scores.float() / self.temperature, dim=1).view(self.num_crops, bs, -1)
         total = 0
         for i, crop_id in enumerate(self.crops_for_assign):
@@ -206,7 +271,15 @@ class SwAVLoss(nn.Module):
         for i in range(len(self.crops_for_assign)):
             for h in range(head.nmb_heads):
                 w = head.prototypes(h).weight
-                getattr(self, f"local_queue{h}")[i] = (self.local_emb_queue[i].to(w.dtype) @ w.t()).float()
+                emb, dst = self.local_emb_queue[i], getattr(self, f"local_queue{h}")[i]
+                if (w.is_cuda and emb.shape[0] % 64 == 0 and emb.shape[1] % 64 == 0 and w.shape[0] % 8 == 0
+                        and dst.dtype == torch.float32 and dst.is_contiguous()):
+                    # C16: queue re-scoring on the tcgen05 GEMM, fp32 scores written in place
+                    from ..ops.gemm import gemm
+
+                    gemm(emb.to(torch.bfloat16).contiguous(), w.detach().to(torch.bfloat16).contiguous(), dst)
+                else:
+                    getattr(self, f"local_queue{h}")[i] = (emb.to(w.dtype) @ w.t()).float()
 
 
 @torch.no_grad()

@@ -41,7 +41,10 @@ class SyntheticMLMBatches:
     15 % of the positions masked -> 80 % [MASK] / 10 % random / 10 % kept)."""
 
     def __init__(self, vocab_size: int, seq_len: int, batch_size: int, seed: int = 0, mlm_probability: float = 0.15,
-                 pin: bool = True, pool: int = 8, mask_token_id: int = 4, cls_id: int = 2, sep_id: int = 3):
+                 pin: bool = True, pool: int = 8, mask_token_id: int = 4, cls_id: int = 2, sep_id: int = 3,
+                 padded: bool = False, pad_id: int = 0):
+        """`padded`: instance lengths are drawn from [seq_len / 2, seq_len] and the tail is padding with
+        attention_mask 0, like tokenised WikiText instances (the default packs every sequence to full length)."""
         g = torch.Generator().manual_seed(seed)
         self.batches: List[Dict[str, torch.Tensor]] = []
         for _ in range(pool):
@@ -59,8 +62,17 @@ class SyntheticMLMBatches:
             ids = torch.where(masked & (r < 0.8), torch.full_like(ids, mask_token_id), ids)
             rnd = torch.randint(5, vocab_size, (batch_size, seq_len), generator=g)
             ids = torch.where(masked & (r >= 0.8) & (r < 0.9), rnd, ids)
+            attn = torch.ones_like(ids)
+            if padded:
+                length = torch.randint(seq_len // 2, seq_len + 1, (batch_size,), generator=g)
+                keep = pos < length[:, None]
+                ids = torch.where(keep, ids, torch.full_like(ids, pad_id))
+                ids[torch.arange(batch_size), length - 1] = sep_id
+                labels = torch.where(keep, labels, torch.full_like(labels, -100))
+                token_type = token_type * keep
+                attn = keep.long()
             batch = {"input_ids": ids, "token_type_ids": token_type, "labels": labels,
-                     "attention_mask": torch.ones_like(ids),
+                     "attention_mask": attn,
                      "sentence_order_label": torch.randint(0, 2, (batch_size,), generator=g)}
             if pin and torch.cuda.is_available():
                 batch = {k: v.pin_memory() for k, v in batch.items()}
@@ -206,6 +218,14 @@ class PeerTrainer:
     def pop_mean_loss(self) -> float:
         """Device->host read of the mean loss since the last call (the per-step result of the e2e timing)."""
         val = float(self.loss_sum.item()) / max(self.mini_steps, 1)
+        if hasattr(self.model, "mlm_dropped_positions"):
+            dropped = self.model.mlm_dropped_positions()
+            if dropped:
+                import logging
+
+                logging.getLogger(__name__).warning(
+                    "%d masked positions exceeded the MLM capacity (max_predictions_ratio) and were not scored: raise "
+                    "AlbertForPreTraining(max_predictions_ratio=...) for collators that mask more than 25 %%", dropped)
         self.loss_sum.zero_()
         self.mini_steps = 0
         return val

@@ -230,6 +230,22 @@ int dedloc_layernorm_bwd(const void* dy, const void* x, const void* gamma, const
                          void* dx, float* dgamma, float* dbeta, int M, int H, void* stream);
 int dedloc_colsum_accumulate(const void* dy, float* out, int M, int N, long long ld, void* stream);
 
+/* ---- ALBERT embedding front end and the 128-wide LayerNorm of the MLM head (HF AlbertEmbeddings / AlbertMLMHead under
+ *      AlbertForPreTraining, albert/run_trainer.py:64-68) ------------------------------------------------------------ */
+/* y[t] = LayerNorm(word[ids[t]] + type[token_types[t]] + pos[t % S]); tables, gamma, beta, y: bf16, E = 128 */
+int dedloc_embed_ln_fwd(const long long* ids, const long long* token_types, const void* word, const void* pos,
+                        const void* type, const void* gamma, const void* beta, void* y, float* mean, float* rstd, int M,
+                        int S, int E, float eps, void* stream);
+/* LayerNorm backward + the three embedding backwards; every gradient is ACCUMULATED into an fp32 buffer */
+int dedloc_embed_ln_bwd(const void* dy, const long long* ids, const long long* token_types, const void* word,
+                        const void* pos, const void* type, const void* gamma, const float* mean, const float* rstd,
+                        float* gword, float* gpos, float* gtype, float* dgamma, float* dbeta, int M, int S, int E,
+                        long long pad_id, int n_types, void* stream);
+int dedloc_ln128_fwd(const void* x, const void* gamma, const void* beta, void* y, float* mean, float* rstd, int M,
+                     float eps, void* stream);
+int dedloc_ln128_bwd(const void* dy, const void* x, const void* gamma, const float* mean, const float* rstd, void* dx,
+                     float* dgamma, float* dbeta, int M, void* stream);
+
 /* ---- SwAV Sinkhorn-Knopp assignments in one persistent kernel (vissl/losses/swav_loss.py:177-244) -------- */
 /* scores: [n, K] bf16 or fp32 (rows = samples: batch first, then the queue); out: [n_out, K] fp32 assignments of
  * the first n_out rows; scratch: dedloc_sinkhorn_scratch_floats(K, iters) floats, clobbered. */
@@ -243,6 +259,20 @@ int dedloc_sinkhorn(const void* scores, int is_bf16, long long ld, int n, int K,
 int dedloc_sinkhorn_noalloc_capacity_floats(void);
 int dedloc_sinkhorn_noalloc(const void* scores, int is_bf16, long long ld, int n, int K, int n_out, float epsilon,
                             int iters, float world_size, float* out, long long ld_out, void* stream);
+
+/* ---- SwAV head / loss kernels (vissl/models/heads/swav_prototypes_head.py:100-104, vissl/losses/swav_loss.py:275-302) */
+/* y = x / max(||x||, eps), rows of 128 bf16 */
+int dedloc_l2norm128_fwd(const void* x, void* y, int M, float eps, void* stream);
+int dedloc_l2norm128_bwd(const void* x, const void* dy, void* dx, int M, float eps, void* stream);
+/* swapped-prediction cross-entropy. scores: [num_crops * bs, K] bf16 or fp32; q: [n_assign, bs, K] fp32 assignments of the
+ * crops assign_crop[0..n_assign) (device array); loss_row[r] = sum_{i: assign_crop[i] != crop(r)} sum_k q_i[b,k] *
+ * log_softmax(scores[r] / T)[k]; lse[r] is kept for the backward, which writes
+ * dscores[r,k] = grad_scale[0] / T * sum_i (q_i[b,k] - softmax[k] * sum_j q_i[b,j]). */
+int dedloc_swav_ce_fwd(const void* scores, int is_bf16, long long ld, const float* q, int n_assign, const int* assign_crop,
+                       int num_crops, int bs, int K, float temperature, float* loss_row, float* lse, void* stream);
+int dedloc_swav_ce_bwd(const void* scores, int is_bf16, long long ld, const float* q, int n_assign, const int* assign_crop,
+                       int num_crops, int bs, int K, float temperature, const float* lse, const float* grad_scale,
+                       void* dscores, void* stream);
 
 /* ---- shared-layer attention on the packed QKV layout (HF AlbertAttention: bmm + softmax + bmm) ----------- */
 /* qkv: [B, S, 3, H, 64] bf16 (output of the fused QKV GEMM); mask: [B, S] bytes (1 = attend) or NULL;

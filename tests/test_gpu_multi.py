@@ -76,3 +76,39 @@ def test_nvls_multimem_allreduce_two_gpus():
     res = subprocess.run(cmd, capture_output=True, text=True, timeout=300, cwd=ROOT)
     assert res.returncode == 0, res.stdout[-3000:] + res.stderr[-3000:]
     assert "NVLS OK" in res.stdout
+
+
+@pytest.mark.parametrize("sig", ["SIGKILL", "SIGSTOP"])
+def test_peer_dies_inside_the_kernel(tmp_path, sig):
+    """A member is killed (or frozen) while it sits INSIDE the all-reduce kernel, before it has sent anything: the
+    survivor's bounded waits expire, its launch returns `abort_before_reduce` within the timeout with parameters and
+    moments untouched, and it steps on its own gradient instead of hanging."""
+    import signal
+    import time
+
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs 2 GPUs")
+    worker = os.path.join(ROOT, "tests", "abort_worker.py")
+    victim = subprocess.Popen([sys.executable, worker, "--role", "victim", "--dir", str(tmp_path)], cwd=ROOT,
+                              stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True)
+    survivor = subprocess.Popen([sys.executable, worker, "--role", "survivor", "--dir", str(tmp_path)], cwd=ROOT,
+                                stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True)
+    try:
+        t0 = time.time()
+        while not (tmp_path / "victim_launching").exists():
+            assert victim.poll() is None, victim.stdout.read()[-3000:]
+            assert time.time() - t0 < 120
+            time.sleep(0.05)
+        time.sleep(1.0)                                   # the victim is parked inside its kernel now
+        os.kill(victim.pid, getattr(signal, sig))
+        out, _ = survivor.communicate(timeout=120)
+        assert survivor.returncode == 0, out[-3000:]
+        res = json.load(open(tmp_path / "survivor.json"))
+        assert res["status"]["name"] == "abort_before_reduce", res
+        assert res["seconds"] < 10.0, res                 # timeout_s = 2: bounded, not a hang
+        assert res["untouched"] is True, res
+        assert res["solo_status"]["code"] == 0 and res["solo_moved"] is True, res
+    finally:
+        for p in (victim, survivor):
+            if p.poll() is None:
+                p.kill()

@@ -59,3 +59,75 @@ def test_swav_gpu_step_with_fused_lars(native, tmp_path):
     assert torch.allclose(w.float().norm(dim=1), torch.ones(w.shape[0], device=w.device), atol=1e-3)
     task.optimizer.optimizer.shutdown()
     dht.shutdown()
+
+
+def test_l2_normalize128_matches_torch(native):
+    import torch.nn.functional as F
+
+    from dedloc_b200.ops.swav_ops import l2_normalize128
+
+    torch.manual_seed(0)
+    x = (torch.randn(512, 128, device="cuda") * 3).to(torch.bfloat16).requires_grad_(True)
+    y = l2_normalize128(x)
+    dy = torch.randn_like(y)
+    y.backward(dy)
+    xr = x.detach().float().requires_grad_(True)
+    ref = F.normalize(xr, dim=1, p=2)
+    ref.backward(dy.float())
+    assert torch.allclose(y.float(), ref, atol=1e-2, rtol=1e-2)
+    assert (x.grad.float() - xr.grad).abs().max() <= 2e-2 * xr.grad.abs().max()
+
+
+@pytest.mark.parametrize("dtype", [torch.bfloat16, torch.float32])
+def test_swav_cross_entropy_matches_the_loss_restatement(native, dtype):
+    """csrc/swav_ops.cu against the PyTorch restatement of vissl/losses/swav_loss.py:275-302 (fp32)."""
+    import torch.nn.functional as F
+
+    from dedloc_b200.ops.swav_ops import swav_cross_entropy
+
+    torch.manual_seed(1)
+    num_crops, bs, K, T = 8, 64, 3000, 0.1
+    scores = (torch.randn(num_crops * bs, K, device="cuda") * 0.3).to(dtype).requires_grad_(True)
+    assign = [0, 1]
+    q = torch.softmax(torch.randn(len(assign), bs, K, device="cuda") * 2, dim=-1)
+    loss = swav_cross_entropy(scores, q, assign, num_crops, T)
+    loss.backward()
+    sr = scores.detach().float().requires_grad_(True)
+    logp = F.log_softmax(sr / T, dim=1).view(num_crops, bs, K)
+    total = 0
+    for i, c in enumerate(assign):
+        others = [p for p in range(num_crops) if p != c]
+        total = total - torch.einsum("bk,pbk->", q[i], logp[others]) / (bs * len(others))
+    ref = total / len(assign)
+    ref.backward()
+    assert abs(float(loss) - float(ref)) <= 2e-3 * abs(float(ref)), (float(loss), float(ref))
+    tol = 2e-2 if dtype == torch.bfloat16 else 1e-4
+    assert (scores.grad.float() - sr.grad).abs().max() <= tol * sr.grad.abs().max()
+
+
+def test_head_on_own_kernels_matches_torch_path(native):
+    """SwAVPrototypesHead._forward_native (tcgen05 GEMMs + fused L2-normalise) against the module's PyTorch path in
+    fp32: embeddings, prototype scores and every parameter gradient (accumulated in main_grad)."""
+    from dedloc_b200.models.swav import SwAVPrototypesHead
+
+    torch.manual_seed(2)
+    head = SwAVPrototypesHead((2048, 2048, 128), use_bn=True, num_clusters=(3000,)).cuda().train()
+    ref = SwAVPrototypesHead((2048, 2048, 128), use_bn=True, num_clusters=(3000,)).cuda().train()
+    ref.load_state_dict(head.state_dict())
+    for p in head.parameters():
+        p.main_grad = torch.zeros_like(p, dtype=torch.float32)
+    feats = torch.randn(512, 2048, device="cuda")
+    f1 = feats.clone().requires_grad_(True)
+    f2 = feats.clone().requires_grad_(True)
+    assert head._native_ok(f1)
+    emb, scores = head(f1)
+    emb_r, scores_r = ref(f2)
+    assert torch.allclose(emb.float(), emb_r, atol=2e-2, rtol=5e-2)
+    assert torch.allclose(scores.float(), scores_r, atol=3e-2, rtol=5e-2)
+    g = torch.randn_like(scores_r) * 0.1
+    scores.backward(g.to(scores.dtype))
+    scores_r.backward(g)
+    assert (f1.grad - f2.grad).abs().max() <= 8e-2 * f2.grad.abs().max()
+    for (n, p), (_, pr) in zip(head.named_parameters(), ref.named_parameters()):
+        got = p.main_grad if p.grad is None else p.main_grad + p.grad.float()
+        assert (got - pr.grad).abs().max() <= 8e-2 * pr.grad.abs().max() + 1e-6, n
