@@ -132,6 +132,10 @@ def test_head_on_own_kernels_matches_torch_path(native):
         got = p.main_grad if p.grad is None else p.main_grad + p.grad.float()
         # bf16 activations in front of a BatchNorm with a large 1/std: single elements of dW1 move by up to 15 % of
         # the maximum even in a pure-PyTorch bf16 emulation of this path, so the check is on the whole tensor
+        if float(pr.grad.abs().max()) < 1e-5:
+            # the bias in front of the BatchNorm has a zero gradient (the batch mean is subtracted): only rounding noise
+            assert float(got.abs().max()) <= 5e-2, (n, float(got.abs().max()))
+            continue
         rel = float((got - pr.grad).norm() / pr.grad.norm().clamp_min(1e-12))
         assert rel <= 6e-2, (n, rel)
         assert (got - pr.grad).abs().max() <= 0.3 * pr.grad.abs().max() + 1e-6, n
