@@ -274,8 +274,20 @@ def main(argv=None):
         return
     callback.on_train_begin()
     batches = make_batches(training_args, dataset_args, model.config, independent_shuffling_seed(local_public_key))
+    train_loop(training_args, model, opt, scheduler, collaborative_optimizer, callback, batches, device,
+               total_batch_size_per_step, entry="dedloc_b200.trainers.albert.run_trainer")
+    collaborative_optimizer.shutdown()
+    dht.shutdown()
+
+
+def train_loop(training_args, model, opt, scheduler, collaborative_optimizer, callback, batches, device,
+               total_batch_size_per_step: int, entry: str) -> None:
+    """The training loop of the ALBERT and sahajBERT trainers: `PeerTrainer` (the code path bench.py times) plus the
+    reference's per-step bookkeeping (CollaborativeCallback, checkpoints every `save_steps`), done once per
+    collaborative step."""
     from ..pretrain import PeerConfig, PeerTrainer
 
+    on_gpu = device.type == "cuda"
     peer_cfg = PeerConfig(micro_batch=total_batch_size_per_step,
                           gradient_accumulation_steps=training_args.gradient_accumulation_steps,
                           seq_len=training_args.seq_length)
@@ -316,13 +328,13 @@ def main(argv=None):
         import json
 
         dt = time.time() - t_log
-        print(json.dumps({"entry": "dedloc_b200.trainers.albert.run_trainer", "local_steps": local_steps,
+        print(json.dumps({"entry": entry, "local_steps": local_steps,
                           "collaborative_steps": collaborative_optimizer.local_step,
                           "samples": trainer.samples_processed, "seconds": round(dt, 3),
                           "samples_per_second_incl_startup": round(trainer.samples_processed / max(dt, 1e-9), 2),
-                          "cuda_graph": trainer._graph is not None}), flush=True)
-    collaborative_optimizer.shutdown()
-    dht.shutdown()
+                          "cuda_graph": trainer._graph is not None,
+                          "collab": {k: v for k, v in collaborative_optimizer.stats.items() if isinstance(v, (int, float))}}),
+              flush=True)
 
 
 def _train_with_hf_trainer(training_args, dataset_args, model, collaborative_optimizer, callback):

@@ -21,7 +21,7 @@ from ...utils.compression import CompressionType
 from ..albert import metrics_utils
 from ..albert.data import MLMCollator
 from ..albert.run_trainer import (CollaborativeCallback, get_model, get_optimizer_and_scheduler,
-                                  independent_shuffling_seed, load_config, save_checkpoint, setup_logging)
+                                  independent_shuffling_seed, load_config, save_checkpoint, setup_logging, train_loop)
 from ..pretrain import SyntheticMLMBatches
 from .arguments import AlbertTrainingArguments, CollaborationArguments, DatasetArguments
 
@@ -108,29 +108,9 @@ def main(argv=None):
     else:
         batches = streaming_batches(tokenizer, training_args, dataset_args, seed)
     callback.on_train_begin()
-    accum = training_args.gradient_accumulation_steps
-    local_steps, last_saved = 0, collaborative_optimizer.local_step
-    while collaborative_optimizer.local_step < training_args.max_steps:
-        host = next(batches)
-        batch = {k: v.to(device, non_blocking=True) for k, v in host.items()}
-        n = batch["input_ids"].shape[0]
-        loss_val = torch.zeros((), device=device)
-        for c in range(accum):
-            sub = {k: v[c * n // accum:(c + 1) * n // accum] for k, v in batch.items()}
-            out = model(**sub)
-            (out.loss / accum).backward()
-            loss_val += out.loss.detach().float() / accum
-        model.flush_fused_grads()
-        collaborative_optimizer.step()
-        collaborative_optimizer.zero_grad()
-        callback.on_step_end(loss=float(loss_val))
-        local_steps += 1
-        step = collaborative_optimizer.local_step
-        if step != last_saved and step % training_args.save_steps == 0:
-            save_checkpoint(training_args, model, collaborative_optimizer, step)
-            last_saved = step
-        if training_args.max_local_steps and local_steps >= training_args.max_local_steps:
-            break
+    # the same loop as the ALBERT trainer (PeerTrainer: CUDA-graph micro-step, one host read per collaborative step)
+    train_loop(training_args, model, opt, scheduler, collaborative_optimizer, callback, batches, device,
+               total_batch_size_per_step, entry="dedloc_b200.trainers.sahajbert.run_trainer")
     collaborative_optimizer.shutdown()
     dht.shutdown()
 

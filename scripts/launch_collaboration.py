@@ -5,6 +5,9 @@ loop that keeps the fleet at size (spot-preemption behaviour: a killed peer come
 `checkpoint*` and immediately overwrites it with the collaboration's state), and optional fault injection
 (`--kill_every S` kills a random trainer every S seconds; `--pause_every S` SIGSTOPs one for `--pause_for`).
 Bandwidth shaping (wondershaper in the reference) is meaningless on NVLink and is not emulated.
+`--fleet_report FILE` turns a run into the elasticity benchmark of BASELINE.json config 3: collaboration-wide samples/s
+over the window after `--measure_after` seconds (from the coordinator's view of the global step), faults injected,
+rounds that failed / ran solo, state downloads and the time a respawned peer needs to contribute again.
 
     python scripts/launch_collaboration.py --experiment_prefix demo --trainers 8 --aux 1 --synthetic_data \
         --target_batch_size 4096 --per_device_train_batch_size 64 --run_for 600
@@ -49,6 +52,8 @@ def main():
     ap.add_argument("--pause_for", type=float, default=10)
     ap.add_argument("--log_dir", default="fleet_logs")
     ap.add_argument("--device", default=None, help="cpu to run the fleet without GPUs")
+    ap.add_argument("--fleet_report", default="", help="write the elasticity report here when the run ends")
+    ap.add_argument("--measure_after", type=float, default=60.0, help="seconds of start-up excluded from the report")
     args, passthrough = ap.parse_known_args()
     os.makedirs(args.log_dir, exist_ok=True)
     pkg = f"dedloc_b200.trainers.{args.family}"
@@ -95,6 +100,9 @@ def main():
                 env = {} if args.device == "cpu" else {"CUDA_VISIBLE_DEVICES": str(i)}
                 fleet[key] = spawn(f"{pkg}.run_trainer", trainer_args(i), env, os.path.join(args.log_dir, f"trainer_{i}.log"))
                 print(f"(re)started trainer {i} pid {fleet[key].pid}", flush=True)
+                if key in started_once:
+                    events["respawns"].append({"trainer": i, "t": time.time() - t0})
+                started_once.add(key)
         for j in range(args.aux if args.family == "albert" else 0):
             key = ("aux", j)
             if key not in fleet or fleet[key].poll() is not None:
@@ -104,6 +112,8 @@ def main():
 
     t0 = last_kill = last_pause = time.time()
     paused = None
+    events = {"kills": [], "pauses": [], "respawns": []}
+    started_once = set()
     try:
         while not args.run_for or time.time() - t0 < args.run_for:
             ensure_fleet()
@@ -113,12 +123,14 @@ def main():
                 victim = random.choice(trainers)
                 os.killpg(fleet[victim].pid, signal.SIGKILL)     # exact process group we started
                 print(f"fault injection: killed {victim}", flush=True)
+                events["kills"].append({"trainer": victim[1], "t": now - t0})
                 last_kill = now
             if args.pause_every and paused is None and now - last_pause > args.pause_every and trainers:
                 victim = random.choice(trainers)
                 os.killpg(fleet[victim].pid, signal.SIGSTOP)
                 paused = (victim, now)
                 print(f"fault injection: paused {victim}", flush=True)
+                events["pauses"].append({"trainer": victim[1], "t": now - t0, "for": args.pause_for})
             if paused is not None and now - paused[1] > args.pause_for:
                 os.killpg(fleet[paused[0]].pid, signal.SIGCONT)
                 print(f"fault injection: resumed {paused[0]}", flush=True)
@@ -134,6 +146,65 @@ def main():
                 except ProcessLookupError:
                     pass
         print("fleet stopped", flush=True)
+        if args.fleet_report:
+            write_report(args, events, t0, coord_log)
+
+
+def _stamp(line: str):
+    """Seconds since the epoch of a log line that starts with a time stamp, or None."""
+    import datetime
+
+    for fmt in ("%m/%d/%Y %H:%M:%S", "%Y-%m-%d %H:%M:%S"):      # trainers / coordinator
+        try:
+            return datetime.datetime.strptime(line[:19], fmt).timestamp()
+        except ValueError:
+            continue
+    return None
+
+
+def write_report(args, events, t0, coord_log):
+    import json
+
+    # the coordinator logs "Step #N loss = L" (run_first_peer.py) whenever the collaboration's step advanced
+    steps = []
+    for line in open(coord_log, errors="replace"):
+        m = re.search(r"Step #(\d+)", line)
+        ts = _stamp(line)
+        if m and ts is not None:
+            steps.append((ts - t0, int(m.group(1))))
+    window = [(t, s) for t, s in steps if t >= args.measure_after]
+    report = {"family": args.family, "trainers": args.trainers, "aux": args.aux, "clients": args.clients,
+              "compression": args.compression, "target_batch_size": args.target_batch_size,
+              "micro_batch": args.per_device_train_batch_size, "run_for_s": args.run_for,
+              "measure_after_s": args.measure_after, "faults": events}
+    if len(window) >= 2:
+        (ta, sa), (tb, sb) = window[0], window[-1]
+        report.update(window_s=round(tb - ta, 1), collaborative_steps_in_window=sb - sa,
+                      samples_per_second=round((sb - sa) * args.target_batch_size / max(tb - ta, 1e-9), 1))
+    per_trainer = {}
+    rejoin = []
+    for i in range(args.trainers):
+        path = os.path.join(args.log_dir, f"trainer_{i}.log")
+        if not os.path.exists(path):
+            continue
+        text = open(path, errors="replace").read()
+        per_trainer[i] = {"failed_rounds": text.count("Skipped averaging"),
+                          "state_downloads": len(re.findall(r"downloading state|Loading state from peers", text)),
+                          "torn_rounds": text.count("must resynchronise after a torn round"),
+                          "solo_or_local_steps_logged": text.count("averaging round failed"),
+                          "collaborative_steps_logged": len(re.findall(r"-\s+Step \d+$", text, flags=re.M))}
+        # time from a respawn to the first "Step N" line of the new process
+        stamps = [(_stamp(l), l) for l in text.splitlines()]
+        for ev in events["respawns"]:
+            if ev["trainer"] != i:
+                continue
+            after = [ts - t0 for ts, l in stamps if ts is not None and ts - t0 > ev["t"] and re.search(r"-\s+Step \d+$", l)]
+            if after:
+                rejoin.append(round(after[0] - ev["t"], 1))
+    report["per_trainer"] = per_trainer
+    report["seconds_from_respawn_to_first_collaborative_step"] = rejoin
+    json.dump(report, open(args.fleet_report, "w"), indent=1)
+    print(json.dumps({k: v for k, v in report.items() if k != "per_trainer"}), flush=True)
 
 
 if __name__ == "__main__":
