@@ -184,7 +184,14 @@ class CollaborativeOptimizer:
                                        auxiliary=self.auxiliary, **self._tracker_kwargs)
         self._started = True
         self._publish_state_sharing()
-        self.tracker.report(self.local_step, 0)
+        # A peer that never trains (the coordinator builds an optimizer without a batch size, only to pull state) must
+        # not show up in the progress records: the trainers would count it as a peer and wait for it in matchmaking.
+        if self._reports_progress:
+            self.tracker.report(self.local_step, 0)
+
+    @property
+    def _reports_progress(self) -> bool:
+        return self.batch_size_per_step is not None or self.auxiliary
 
     def shutdown(self) -> None:
         if not self._started:
@@ -867,7 +874,8 @@ class CollaborativeOptimizer:
                 self.stats["state_downloads"] += 1
                 self._sync_scheduler()
                 self.tracker.local_step = self.local_step
-                self.tracker.report(self.local_step, self.local_samples_accumulated)
+                if self._reports_progress:
+                    self.tracker.report(self.local_step, self.local_samples_accumulated)
                 return True
         if donors:
             logger.warning("could not load state from any of %d peers", len(donors))
