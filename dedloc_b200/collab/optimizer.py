@@ -72,7 +72,8 @@ class CollaborativeOptimizer:
                  listen_on: str = "127.0.0.1:*", start: bool = True, max_grad_norm: Optional[float] = None,
                  peer_key: Optional[bytes] = None, expected_group_size_from_tracker: bool = True,
                  replicate_state: bool = False, replicate_state_every: int = 8,
-                 step_slack_fraction: float = 0.75, **unused_kwargs):
+                 step_slack_fraction: float = 0.75, liveness_window: float = 3.0, kernel_timeout: Optional[float] = None,
+                 **unused_kwargs):
         if compression is not None:  # sgd_collaborative.py:150 spells the kwarg `compression=`
             compression_type = compression
         if isinstance(compression_type, str):
@@ -81,6 +82,10 @@ class CollaborativeOptimizer:
         self.step_slack_fraction = step_slack_fraction
         self.target_batch_size, self.batch_size_per_step = target_batch_size, batch_size_per_step
         self.averaging_timeout = averaging_timeout if averaging_timeout is not None else 30.0
+        # How long the all-reduce kernel waits for a member's data. averaging_timeout (30 s) bounds a round over
+        # sockets; members that share NVLink launch within milliseconds of each other once the group is formed, so a
+        # member that is still absent after a few seconds was killed between matchmaking and the launch.
+        self.kernel_timeout = min(self.averaging_timeout, 5.0) if kernel_timeout is None else float(kernel_timeout)
         self.averaging_expiration, self.target_group_size = averaging_expiration, target_group_size
         self.step_tolerance, self.client_mode, self.auxiliary = step_tolerance, client_mode, auxiliary
         self.allow_state_sharing = allow_state_sharing and not auxiliary
@@ -136,7 +141,7 @@ class CollaborativeOptimizer:
             metadata_expiration=metadata_expiration, min_refresh_period=min_refresh_period,
             max_refresh_period=max_refresh_period, default_refresh_period=default_refresh_period,
             expected_drift_peers=expected_drift_peers, expected_drift_rate=expected_drift_rate,
-            performance_ema_alpha=performance_ema_alpha)
+            performance_ema_alpha=performance_ema_alpha, liveness_window=liveness_window)
         self.metadata_expiration = metadata_expiration
         self.listen_on = listen_on
         self._started = False
@@ -382,7 +387,8 @@ class CollaborativeOptimizer:
             self._params_parked = True
             group: Optional[GroupInfo] = None
             if state.num_peers > 1:  # num_peers counts this peer's own progress record too
-                expected = state.num_peers if self.expected_group_size_from_tracker else None
+                # wait for the peers that are still reporting, not for the records dead peers left behind
+                expected = max(state.live_peers, 2) if self.expected_group_size_from_tracker else None
                 try:
                     with nvtx_range("matchmaking"):
                         group = self.dht.run_coroutine(
@@ -639,7 +645,7 @@ class CollaborativeOptimizer:
             shares = [0.0 if b["mode"] == MODE_CLIENT else 1.0 for b in blobs]
             base_tag = (int.from_bytes(group.group_id[4:8], "little") & 0x3FFFFFF0) or 16
             spec = GroupSpec(bases=bases, me=group.my_index, weights=weights, shards=opt.layout.shard_ranges(shares),
-                             slots=list(range(len(blobs))), tag=base_tag, timeout_s=self.averaging_timeout)
+                             slots=list(range(len(blobs))), tag=base_tag, timeout_s=self.kernel_timeout)
             if not v2_supported(opt.layout, buf.regions, spec, CompressionType.NONE):
                 raise AllreduceException("parameter averaging needs the push-based kernel")
             self._state_seq += 1
@@ -695,7 +701,7 @@ class CollaborativeOptimizer:
         owners = [h for h, s in zip(handles, shares) if s > 0]
         spec = GroupSpec(bases=bases, me=group.my_index, weights=weights,
                          shards=opt.layout.shard_ranges(shares), slots=list(range(len(blobs))),
-                         tag=self._next_tag(group.group_id), timeout_s=self.averaging_timeout)
+                         tag=self._next_tag(group.group_id), timeout_s=self.kernel_timeout)
         push = (os.environ.get("DEDLOC_AR_KERNEL", "push") != "pull"
                 and v2_supported(opt.layout, buf.regions, spec, self.compression_type))
         # every member derives the same answer from the agreed step, so the whole group replicates in the same rounds

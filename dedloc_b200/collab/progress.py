@@ -32,6 +32,9 @@ class TrainingState(BaseModel):
     time: StrictFloat
     client_mode: StrictBool
     auxiliary: StrictBool = False
+    # typical seconds between two reports of this peer (0 = unknown); readers use it to tell a peer that stopped
+    # reporting from one whose micro-steps are simply long
+    report_period: confloat(ge=0.0) = 0.0
 
 
 @dataclass(frozen=True)
@@ -44,6 +47,11 @@ class CollaborationState:
     eta_next_step: float
     next_fetch_time: float
     num_aux: int = 0
+    num_live_peers: int = -1   # peers whose record is fresh (see ProgressTracker.liveness_window); -1 = not computed
+
+    @property
+    def live_peers(self) -> int:
+        return self.num_peers if self.num_live_peers < 0 else self.num_live_peers
 
     @property
     def ready_for_step(self) -> bool:
@@ -57,7 +65,8 @@ class CollaborationState:
 
     def register_step(self, local_step: int) -> "CollaborationState":
         return CollaborationState(max(local_step, self.optimizer_step), 0, self.target_batch_size, self.num_peers,
-                                  self.num_clients, float("inf"), self.next_fetch_time, self.num_aux)
+                                  self.num_clients, float("inf"), self.next_fetch_time, self.num_aux,
+                                  self.num_live_peers)
 
 
 class PerformanceEMA:
@@ -101,7 +110,8 @@ class ProgressTracker:
                  client_mode: bool = False, auxiliary: bool = False, metadata_expiration: float = 30.0,
                  min_refresh_period: float = 0.5, max_refresh_period: float = 30.0,
                  default_refresh_period: float = 3.0, expected_drift_peers: float = 3.0,
-                 expected_drift_rate: float = 0.2, performance_ema_alpha: float = 0.1, start: bool = True):
+                 expected_drift_rate: float = 0.2, performance_ema_alpha: float = 0.1, start: bool = True,
+                 liveness_window: float = 3.0):
         self.dht, self.prefix, self.peer_key = dht, prefix, peer_key
         self.target_batch_size = target_batch_size
         self.endpoint, self.client_mode, self.auxiliary = endpoint, client_mode, auxiliary
@@ -113,6 +123,11 @@ class ProgressTracker:
         self.local_step = 0
         self.local_samples_accumulated = 0
         self.last_reported_time = 0.0
+        # A record stays in the DHT for metadata_expiration (30 s) after its author died. A peer counts as LIVE while
+        # its last report is younger than max(liveness_window, 4 x its own report period): matchmaking waits only for
+        # live peers, and only they are extrapolated in the ETA.
+        self.liveness_window = liveness_window
+        self.report_period = 0.0
         self.lock = threading.Lock()
         self.state_updated = threading.Event()
         self.should_refresh = threading.Event()
@@ -150,10 +165,14 @@ class ProgressTracker:
             if update_ema_with > 0:
                 self.performance_ema.update(update_ema_with)
             now = get_dht_time()
+            if self.last_reported_time > 0:
+                gap = now - self.last_reported_time
+                self.report_period = gap if self.report_period == 0 else 0.9 * self.report_period + 0.1 * gap
             self.last_reported_time = now
             state = TrainingState(endpoint=self.endpoint, step=local_step, samples_accumulated=samples_accumulated,
                                   samples_per_second=float(self.performance_ema.samples_per_second), time=now,
-                                  client_mode=self.client_mode, auxiliary=self.auxiliary)
+                                  client_mode=self.client_mode, auxiliary=self.auxiliary,
+                                  report_period=float(self.report_period))
         fut = self.dht.store(self.training_progress_key, state.model_dump(), now + self.metadata_expiration,
                              subkey=self.peer_key, return_future=True)
         if wait:
@@ -216,13 +235,16 @@ class ProgressTracker:
         for s in valid.values():
             if not s.client_mode:
                 global_step = max(global_step, s.step)
-        total_samples, estimated_samples, total_sps = 0, 0.0, 0.0
-        for s in valid.values():
-            total_sps += s.samples_per_second
+        total_samples, estimated_samples, total_sps, num_live = 0, 0.0, 0.0, 0
+        for key, s in valid.items():
+            live = key == self.peer_key or now - s.time <= max(self.liveness_window, 4.0 * s.report_period)
+            num_live += live
+            if live:
+                total_sps += s.samples_per_second
             if s.step == global_step:
                 total_samples += s.samples_accumulated
-                # the ETA (not the sample count) extrapolates what the peer did since it last reported
-                estimated_samples += s.samples_accumulated + max(0.0, now - s.time) * s.samples_per_second
+                # the ETA (not the sample count) extrapolates what a live peer did since it last reported
+                estimated_samples += s.samples_accumulated + (max(0.0, now - s.time) * s.samples_per_second if live else 0)
         total_sps = max(total_sps, 1e-9)
         eta_seconds = max(0.0, self.target_batch_size - estimated_samples) / total_sps
         trainers = max(num_peers - num_aux, 1)
@@ -231,4 +253,4 @@ class ProgressTracker:
                                            self.min_refresh_period, self.max_refresh_period))
         return CollaborationState(global_step, total_samples, self.target_batch_size, num_peers, num_clients,
                                   eta_next_step=now + eta_seconds, next_fetch_time=now + time_to_next_fetch,
-                                  num_aux=num_aux)
+                                  num_aux=num_aux, num_live_peers=num_live)

@@ -41,6 +41,10 @@ class AveragerArguments:
     target_group_size: int = field(default=256, metadata={"help": "Largest number of peers that average together in one round; more peers split into several groups"})
     metadata_expiration: float = field(
         default=30, metadata={"help": "Lifetime (s) of a progress record: a peer that stops reporting drops out of the count after this"})
+    liveness_window: float = field(
+        default=3.0, metadata={"help": "A peer whose last progress report is older than this (and older than 4x its usual reporting interval) is no longer waited for when a group forms"})
+    kernel_timeout: float = field(
+        default=5.0, metadata={"help": "How long (s) the NVLink all-reduce kernel waits for a group member that never shows up before the round is abandoned"})
 
 
 @dataclass
