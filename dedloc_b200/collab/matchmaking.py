@@ -15,7 +15,7 @@ import logging
 import os
 import random
 from dataclasses import dataclass
-from typing import Any, Dict, List, Optional, Tuple
+from typing import Any, Callable, Dict, List, Optional, Tuple
 
 from ..dht import DHT, get_dht_time
 from ..dht.protocol import RPCClient, RPCServer
@@ -65,6 +65,8 @@ class Matchmaking:
         self.current_leader: Optional[str] = None
         self.my_blob: Any = None
         self.expected_size: Optional[int] = None
+        self.expected_size_fn: Optional[Callable[[], Optional[int]]] = None
+        self.give_up_fn: Optional[Callable[[], bool]] = None
         if server is not None:
             server.handlers["join_group"] = self.rpc_join_group
 
@@ -110,10 +112,7 @@ class Matchmaking:
         if len(self.followers) + 1 >= self.target_group_size or self.assembled is None or self.assembled.done():
             return {"code": "REJECTED", "suggested_leader": None}
         self.followers[follower] = blob
-        want = self.target_group_size
-        if self.expected_size is not None:
-            want = min(want, max(self.expected_size, self.min_group_size))
-        if len(self.followers) + 1 >= want:
+        if len(self.followers) + 1 >= self._wanted_size():
             self.group_full.set()
         assembled = self.assembled
         try:
@@ -124,14 +123,35 @@ class Matchmaking:
             return {"code": "GROUP_DISBANDED"}
         return {"code": "BEGIN_ALLREDUCE", **result}
 
+    def _wanted_size(self) -> int:
+        """The group is complete at this many members: target_group_size, or fewer when the caller knows how many
+        peers can still show up. `expected_size_fn` is re-read while the leader waits, so a peer that died after the
+        round began to form stops being waited for as soon as the caller notices."""
+        want = self.target_group_size
+        expected = self.expected_size
+        if self.expected_size_fn is not None:
+            try:
+                latest = self.expected_size_fn()
+                expected = latest if expected is None else (expected if latest is None else min(expected, latest))
+            except Exception:
+                pass
+        if expected is not None:
+            want = min(want, max(expected, self.min_group_size))
+        return want
+
     # ---------------------------------------------------------------- main entry
     async def look_for_group(self, blob: Any, *, timeout: Optional[float] = None,
-                             expected_size: Optional[int] = None) -> Optional[GroupInfo]:
-        """Returns GroupInfo, or None when nobody else showed up before the deadline."""
+                             expected_size: Optional[int] = None,
+                             expected_size_fn: Optional[Callable[[], Optional[int]]] = None,
+                             give_up_fn: Optional[Callable[[], bool]] = None) -> Optional[GroupInfo]:
+        """Returns GroupInfo, or None when nobody else showed up before the deadline -- or when `give_up_fn` says
+        that waiting is pointless (the caller saw the collaboration finish this step without us) and nobody has joined
+        us yet."""
         async with self.lock:
             loop = asyncio.get_event_loop()
             now = get_dht_time()
-            self.my_blob, self.expected_size = blob, expected_size
+            self.my_blob, self.expected_size, self.expected_size_fn = blob, expected_size, expected_size_fn
+            self.give_up_fn = give_up_fn
             self.declared_expiration = now + self.averaging_expiration
             deadline = now + (timeout if timeout is not None else self.averaging_expiration * 2)
             self.followers = {}
@@ -187,6 +207,10 @@ class Matchmaking:
             now = get_dht_time()
             if self.followers:
                 return await self._lead()
+            # (not in the first second: with several groups per round, another group may simply have been faster)
+            if (self.give_up_fn is not None and now > self.declared_expiration - self.averaging_expiration + 1.0
+                    and self.give_up_fn()):
+                return None
             if now >= min(deadline, self.declared_expiration) and not self.client_mode:
                 return await self._lead()
             if now >= deadline:
@@ -226,10 +250,12 @@ class Matchmaking:
 
     async def _lead(self) -> Optional[GroupInfo]:
         """Wait until the group is full or our declaration expires, then begin."""
-        wait = max(0.0, self.declared_expiration - get_dht_time())
-        if not self.group_full.is_set() and wait > 0:
+        while not self.group_full.is_set():
+            wait = self.declared_expiration - get_dht_time()
+            if wait <= 0 or len(self.followers) + 1 >= self._wanted_size():
+                break
             try:
-                await asyncio.wait_for(self.group_full.wait(), timeout=wait)
+                await asyncio.wait_for(self.group_full.wait(), timeout=min(wait, 0.2))
             except asyncio.TimeoutError:
                 pass
         if len(self.followers) + 1 < self.min_group_size:

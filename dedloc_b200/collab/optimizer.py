@@ -389,16 +389,24 @@ class CollaborativeOptimizer:
             if state.num_peers > 1:  # num_peers counts this peer's own progress record too
                 # wait for the peers that are still reporting, not for the records dead peers left behind
                 expected = max(state.live_peers, 2) if self.expected_group_size_from_tracker else None
+                # the tracker thread keeps re-reading the records while we wait for the group
+                live_now = ((lambda: max(self.tracker.collaboration_state.live_peers, 2))
+                            if self.expected_group_size_from_tracker else None)
+                # the others finished this step while we were looking for them: nobody is left to form a group with
+                left_behind = lambda: self.tracker.collaboration_state.optimizer_step > self.local_step  # noqa: E731
                 try:
                     with nvtx_range("matchmaking"):
                         group = self.dht.run_coroutine(
                             lambda dht, node: self._matchmaking.look_for_group(
-                                self._my_blob(), timeout=self.averaging_timeout, expected_size=expected))
+                                self._my_blob(), timeout=self.averaging_timeout, expected_size=expected,
+                                expected_size_fn=live_now, give_up_fn=left_behind))
                 except Exception as e:
                     logger.warning("matchmaking failed: %r", e)
             t1 = time.perf_counter()
             self.stats["matchmaking_s"] += t1 - t0
             self.stats["rounds"] += 1
+            self._last_round = {"expected": state.live_peers, "records": state.num_peers,
+                                "group": group.group_size if group is not None else 0, "matchmaking_s": t1 - t0}
             # next round's bucket: members of one group scatter, so large collaborations reshuffle every round
             self._matchmaking.rederive_group_bits(group, state.num_peers)
             averaged = False
@@ -425,6 +433,7 @@ class CollaborativeOptimizer:
             elif averaged:
                 self.lineage = self._round_lineage
                 self.lineage_depth = self._agreed_depth + 1
+            self._last_round["averaging_s"] = time.perf_counter() - t1
             self._finish_global_step()
             self.stats["averaging_host_s"] += time.perf_counter() - t1
 
@@ -444,7 +453,10 @@ class CollaborativeOptimizer:
         self.tracker.should_refresh.set()
         self._publish_state_sharing()
         if self.verbose:
-            logger.info("%s: collaborative step %d done", self.endpoint, self.local_step)
+            r = getattr(self, "_last_round", None) or {}
+            logger.info("%s: collaborative step %d done (group of %d, %d live of %d records; matchmaking %.2f s, "
+                        "averaging %.2f s)", self.endpoint, self.local_step, r.get("group", 0), r.get("expected", 0),
+                        r.get("records", 0), r.get("matchmaking_s", 0.0), r.get("averaging_s", 0.0))
 
     def _sync_scheduler(self) -> None:
         if self.scheduler is not None:

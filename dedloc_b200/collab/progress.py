@@ -165,7 +165,8 @@ class ProgressTracker:
             if update_ema_with > 0:
                 self.performance_ema.update(update_ema_with)
             now = get_dht_time()
-            if self.last_reported_time > 0:
+            if self.last_reported_time > 0 and update_ema_with > 0:
+                # micro-step reports only: the report that follows a round would add the round's length to the period
                 gap = now - self.last_reported_time
                 self.report_period = gap if self.report_period == 0 else 0.9 * self.report_period + 0.1 * gap
             self.last_reported_time = now
