@@ -388,9 +388,12 @@ class CollaborativeOptimizer:
             group: Optional[GroupInfo] = None
             if state.num_peers > 1:  # num_peers counts this peer's own progress record too
                 # wait for the peers that are still reporting, not for the records dead peers left behind
-                expected = max(state.live_peers, 2) if self.expected_group_size_from_tracker else None
+                # ... and, when the collaboration is split into buckets, for this bucket's share of them
+                buckets = 1 << len(self._matchmaking.group_bits)
+                share = lambda live: max(-(-live // buckets), 2)  # noqa: E731
+                expected = share(state.live_peers) if self.expected_group_size_from_tracker else None
                 # the tracker thread keeps re-reading the records while we wait for the group
-                live_now = ((lambda: max(self.tracker.collaboration_state.live_peers, 2))
+                live_now = ((lambda: share(self.tracker.collaboration_state.live_peers))
                             if self.expected_group_size_from_tracker else None)
                 # the others finished this step while we were looking for them: nobody is left to form a group with
                 left_behind = lambda: self.tracker.collaboration_state.optimizer_step > self.local_step  # noqa: E731
@@ -408,7 +411,8 @@ class CollaborativeOptimizer:
             self._last_round = {"expected": state.live_peers, "records": state.num_peers,
                                 "group": group.group_size if group is not None else 0, "matchmaking_s": t1 - t0}
             # next round's bucket: members of one group scatter, so large collaborations reshuffle every round
-            self._matchmaking.rederive_group_bits(group, state.num_peers)
+            # (counted over live peers: the record of a dead peer must not push the collaboration over target_group_size)
+            self._matchmaking.rederive_group_bits(group, state.live_peers)
             averaged = False
             if group is not None and group.group_size > 1:
                 try:
@@ -917,7 +921,9 @@ class CollaborativeOptimizer:
         already be waiting for us -- nothing in that round modifies anybody's state before every member has launched
         (every member either sends a gradient or owns a share) -- so an odd sequence number is fine as long as it
         does not move."""
-        meta = self._call(endpoint, "download_state", {"can_map": can_map}, self.averaging_timeout)
+        # with can_map the first answer is metadata only: a donor that does not give it within seconds is frozen or dead
+        meta = self._call(endpoint, "download_state", {"can_map": can_map},
+                          self.kernel_timeout if can_map else self.averaging_timeout)
         handle = meta.get("handle")
         mappable = bool(handle) and any(bytes(handle)) and meta.get("host") == _host_id()
         if meta.get("fused") and can_map and mappable and meta["total"] == self.opt.layout.total:

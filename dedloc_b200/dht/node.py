@@ -6,6 +6,7 @@ from __future__ import annotations
 import asyncio
 import dataclasses
 import logging
+import time
 from typing import Any, Dict, List, Optional, Sequence, Set, Tuple
 
 import msgpack
@@ -42,6 +43,11 @@ class DHTNode:
         self.server: Optional[RPCServer] = None
         self.port: Optional[int] = None
         self.endpoint_host = "127.0.0.1"
+        # endpoint -> (do not call before, current back-off). A node that failed to answer (dead, or frozen: a stopped
+        # process still accepts connections, so every call to it costs the full wait_timeout) is left alone for a
+        # while; the back-off doubles with every further failure and is forgotten on the first answer.
+        self._avoid: Dict[Endpoint, Tuple[float, float]] = {}
+        self.backoff_first, self.backoff_max = 5.0, 60.0
 
     # ------------------------------------------------------------------ lifecycle
     @classmethod
@@ -78,6 +84,7 @@ class DHTNode:
         if sender:
             node_id, port = DHTID.from_bytes(sender[0]), sender[1]
             self.routing.add_or_update_node(node_id, f"{peer_host}:{port}")
+            self._note_success(f"{peer_host}:{port}")      # it just called us: whatever kept it silent is over
 
     # ------------------------------------------------------------------ RPC handlers (server side)
     async def rpc_ping(self, peer_host: str, payload) -> bytes:
@@ -127,6 +134,20 @@ class DHTNode:
         return best[0] if best else None
 
     # ------------------------------------------------------------------ RPC calls (client side)
+    def _avoided(self, endpoint: Endpoint) -> bool:
+        entry = self._avoid.get(endpoint)
+        return entry is not None and time.monotonic() < entry[0]
+
+    def _note_failure(self, endpoint: Endpoint) -> None:
+        backoff = min(self._avoid[endpoint][1] * 2, self.backoff_max) if endpoint in self._avoid else self.backoff_first
+        self._avoid[endpoint] = (time.monotonic() + backoff, backoff)
+        if len(self._avoid) > 4096:     # bounded: forget the entries whose back-off ran out long ago
+            now = time.monotonic()
+            self._avoid = {ep: e for ep, e in self._avoid.items() if now < e[0] + self.backoff_max}
+
+    def _note_success(self, endpoint: Endpoint) -> None:
+        self._avoid.pop(endpoint, None)
+
     async def call_ping(self, endpoint: Endpoint) -> Optional[DHTID]:
         try:
             raw = await self.client.call(endpoint, "ping", {"sender": self._sender()}, self.wait_timeout)
@@ -138,11 +159,16 @@ class DHTNode:
             return None
 
     async def _call_find(self, endpoint: Endpoint, keys: List[bytes]):
+        if self._avoided(endpoint):
+            return None
         try:
-            return await self.client.call(endpoint, "find", {"sender": self._sender(), "keys": keys},
-                                          self.wait_timeout)
+            reply = await self.client.call(endpoint, "find", {"sender": self._sender(), "keys": keys},
+                                           self.wait_timeout)
+            self._note_success(endpoint)
+            return reply
         except Exception as e:
             logger.debug("find @ %s failed: %r", endpoint, e)
+            self._note_failure(endpoint)
             nid = self.routing.endpoint_to_id.get(endpoint)
             if nid is not None:
                 self.routing.remove(nid)
@@ -173,7 +199,7 @@ class DHTNode:
                 payload, nearest = reply[0]
                 for raw_id, ep in nearest:
                     other = DHTID.from_bytes(raw_id)
-                    if other != self.node_id and other not in candidates:
+                    if other != self.node_id and other not in candidates and not self._avoided(ep):
                         candidates[other] = ep
                         self.routing.add_or_update_node(other, ep)
                 if payload is not None and collect_values:
@@ -208,10 +234,15 @@ class DHTNode:
                    "expirations": [expiration_time]}
 
         async def _one(ep):
+            if self._avoided(ep):
+                return False
             try:
-                return (await self.client.call(ep, "store", payload, self.wait_timeout))[0]
+                ok = (await self.client.call(ep, "store", payload, self.wait_timeout))[0]
+                self._note_success(ep)
+                return ok
             except Exception as e:
                 logger.debug("store @ %s failed: %r", ep, e)
+                self._note_failure(ep)
                 return False
 
         results = await asyncio.gather(*(_one(ep) for ep in targets))

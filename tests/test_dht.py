@@ -140,3 +140,38 @@ def test_signature_and_schema_validation():
     finally:
         a.shutdown()
         b.shutdown()
+
+
+def test_frozen_node_is_left_alone_after_its_first_timeout():
+    """A stopped process (SIGSTOP, swapped out, wedged) still accepts TCP connections; every call to it costs the whole
+    wait_timeout. After the first one the node is avoided for a back-off period, so progress reads stay fast."""
+    import socket
+
+    frozen = socket.socket()
+    frozen.bind(("127.0.0.1", 0))
+    frozen.listen(8)                       # accepts (kernel backlog), never answers
+    first = DHT(start=True, wait_timeout=0.6)
+    second = DHT(start=True, initial_peers=[f"127.0.0.1:{first.port}"], wait_timeout=0.6)
+    try:
+        ghost_id = DHTID.generate()
+        endpoint = f"127.0.0.1:{frozen.getsockname()[1]}"
+        first.run_coroutine(lambda dht, node: _add(node, ghost_id, endpoint))
+        assert second.store("k", 1, get_dht_time() + 30)
+        t0 = time.perf_counter()
+        assert first.get("k", latest=True).value == 1
+        slow = time.perf_counter() - t0
+        t0 = time.perf_counter()
+        for _ in range(5):
+            assert first.get("k", latest=True).value == 1
+        fast = (time.perf_counter() - t0) / 5
+        assert slow >= 0.5, "the first read runs into the frozen node"
+        assert fast < 0.2, f"later reads must not wait for it again ({fast:.2f} s)"
+        assert first.node._avoided(endpoint)
+    finally:
+        frozen.close()
+        second.shutdown()
+        first.shutdown()
+
+
+async def _add(node, node_id, endpoint):
+    node.routing.add_or_update_node(node_id, endpoint)
