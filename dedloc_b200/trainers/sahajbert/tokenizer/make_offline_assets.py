@@ -43,7 +43,7 @@ def _syllable(rng: random.Random) -> str:
     return onset + rng.choice(VOWEL_SIGNS) + rng.choice(FINALS)
 
 
-def synthetic_corpus(n_words: int = 120_000, n_sentences: int = 200_000, seed: int = 0):
+def synthetic_corpus(n_words: int = 80_000, n_sentences: int = 100_000, seed: int = 0):
     """Yields sentences. The lexicon has `n_words` pseudo-words of 1-5 syllables; word ranks follow a Zipf law."""
     rng = random.Random(seed)
     lexicon = set()
@@ -62,7 +62,7 @@ def synthetic_corpus(n_words: int = 120_000, n_sentences: int = 200_000, seed: i
         yield " ".join(words) + (" ।" if rng.random() < 0.9 else " ॥")
 
 
-def write_assets(out_dir: str, n_words: int = 120_000, n_sentences: int = 200_000, vocab_size: int = VOCAB_SIZE,
+def write_assets(out_dir: str, n_words: int = 80_000, n_sentences: int = 100_000, vocab_size: int = VOCAB_SIZE,
                  show_progress: bool = False) -> str:
     os.makedirs(out_dir, exist_ok=True)
     tokenizer = train_tokenizer(synthetic_corpus(n_words, n_sentences), vocab_size=vocab_size,
@@ -85,7 +85,7 @@ def write_assets(out_dir: str, n_words: int = 120_000, n_sentences: int = 200_00
 if __name__ == "__main__":
     ap = argparse.ArgumentParser()
     ap.add_argument("--out", default=os.path.join(os.path.dirname(os.path.abspath(__file__)), "data"))
-    ap.add_argument("--words", type=int, default=120_000)
-    ap.add_argument("--sentences", type=int, default=200_000)
+    ap.add_argument("--words", type=int, default=80_000)
+    ap.add_argument("--sentences", type=int, default=100_000)
     a = ap.parse_args()
     print(write_assets(a.out, a.words, a.sentences, show_progress=True))

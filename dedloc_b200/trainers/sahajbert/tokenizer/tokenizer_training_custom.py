@@ -27,8 +27,9 @@ def train_tokenizer(texts=None, vocab_size: int = VOCAB_SIZE, out_path: str = "d
         iterator = batch_iterator(dataset)
     else:
         iterator = ([t] for t in texts)
-    tokenizer.train_from_iterator(iterator=iterator, vocab_size=vocab_size, show_progress=show_progress,
-                                  special_tokens=SPECIAL_TOKENS)
+    # `vocab_size` counts the learned pieces; the trainer's budget includes the special tokens (tokenizers >= 0.10)
+    tokenizer.train_from_iterator(iterator=iterator, vocab_size=vocab_size + len(SPECIAL_TOKENS),
+                                  show_progress=show_progress, special_tokens=SPECIAL_TOKENS)
     if out_path:
         os.makedirs(os.path.dirname(out_path) or ".", exist_ok=True)
         tokenizer.save(out_path)
