@@ -299,6 +299,7 @@ def train_loop(training_args, model, opt, scheduler, collaborative_optimizer, ca
     last_saved = collaborative_optimizer.local_step
     pending: Optional[Dict[str, torch.Tensor]] = first
     samples_at_last_step = 0
+    marks = []          # (wall clock, samples processed) right after every collaborative step's loss read
     t_log = time.time()
     while collaborative_optimizer.local_step < training_args.max_steps:
         host = pending if pending is not None else next(batches)
@@ -313,6 +314,7 @@ def train_loop(training_args, model, opt, scheduler, collaborative_optimizer, ca
             callback.on_step_end(loss=mean_loss * n_mini, mini_steps=n_mini,
                                  samples=trainer.samples_processed - samples_at_last_step)
             samples_at_last_step = trainer.samples_processed
+            marks.append((time.time(), trainer.samples_processed))
             step = collaborative_optimizer.local_step
             if training_args.logging_steps and step % max(training_args.logging_steps, 1) == 0:
                 dt = time.time() - t_log
@@ -328,7 +330,11 @@ def train_loop(training_args, model, opt, scheduler, collaborative_optimizer, ca
         import json
 
         dt = time.time() - t_log
-        print(json.dumps({"entry": entry, "local_steps": local_steps,
+        steady = None
+        if len(marks) >= 5:       # from the end of the 3rd collaborative step to the end of the last one
+            (ta, sa), (tb, sb) = marks[2], marks[-1]
+            steady = round((sb - sa) / max(tb - ta, 1e-9), 2)
+        print(json.dumps({"entry": entry, "local_steps": local_steps, "samples_per_second_steady": steady,
                           "collaborative_steps": collaborative_optimizer.local_step,
                           "samples": trainer.samples_processed, "seconds": round(dt, 3),
                           "samples_per_second_incl_startup": round(trainer.samples_processed / max(dt, 1e-9), 2),
