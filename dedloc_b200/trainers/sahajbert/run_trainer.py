@@ -32,6 +32,12 @@ def load_tokenizer(dataset_args):
     from .tokenization_albert_bengali_fast import AlbertBengaliTokenizerFast
 
     path = dataset_args.tokenizer_path
+    if not os.path.exists(path):
+        # the default "tokenizer/data" is relative to the sahajbert directory (the reference is run from there)
+        packaged = os.path.join(os.path.dirname(os.path.abspath(__file__)), "tokenizer", "data")
+        if os.path.isdir(packaged):
+            logger.info("tokenizer path %r not found: using the packaged assets in %s", path, packaged)
+            path = packaged
     if os.path.isdir(path):
         path = os.path.join(path, "tokenizer.json")
     return AlbertBengaliTokenizerFast(tokenizer_file=path)

@@ -36,6 +36,37 @@ def test_tokenizer_class(bn_tokenizer):
     assert tok("ক|")["input_ids"] == tok("ক।")["input_ids"]
 
 
+def test_packaged_tokenizer_assets_and_offline_builder(tmp_path):
+    """S5 assets: `tokenizer/data/` holds a 32 000-entry Unigram tokenizer (sahajbert/tokenizer/data/tokenizer.json in
+    the reference), loadable by directory with the installed transformers; the builder that made it runs offline."""
+    import json
+    import os
+    from types import SimpleNamespace
+
+    from dedloc_b200.trainers.sahajbert import run_trainer
+    from dedloc_b200.trainers.sahajbert.tokenization_albert_bengali_fast import AlbertBengaliTokenizerFast
+    from dedloc_b200.trainers.sahajbert.tokenizer import make_offline_assets
+
+    data = os.path.join(os.path.dirname(run_trainer.__file__), "tokenizer", "data")
+    assert sorted(os.listdir(data)) == ["special_tokens_map.json", "tokenizer.json", "tokenizer_config.json"]
+    model = json.load(open(os.path.join(data, "tokenizer.json"), encoding="utf-8"))["model"]
+    assert model["type"] == "Unigram" and model["unk_id"] == 1 and len(model["vocab"]) == 32000
+    for tok in (AlbertBengaliTokenizerFast.from_pretrained(data),
+                run_trainer.load_tokenizer(SimpleNamespace(tokenizer_path="tokenizer/data"))):   # default path, any cwd
+        assert len(tok) == 32000
+        assert (tok.pad_token_id, tok.unk_token_id, tok.cls_token_id, tok.sep_token_id, tok.mask_token_id) == (0, 1, 2, 3, 4)
+        text = "আমি বাংলায় গান গাই। ১২৩"
+        ids = tok(text)["input_ids"]
+        assert tok.unk_token_id not in ids and tok.decode(ids, skip_special_tokens=True).replace(" ", "") == text.replace(" ", "")
+        assert tok.convert_ids_to_tokens(tok("ক [MASK] খ")["input_ids"]).count("[MASK]") == 1
+    # the builder, at toy size
+    out = make_offline_assets.write_assets(str(tmp_path / "data"), n_words=400, n_sentences=600, vocab_size=300)
+    small = AlbertBengaliTokenizerFast.from_pretrained(out)
+    assert 250 <= len(small) <= 305 and small.mask_token_id == 4
+    sents = list(make_offline_assets.synthetic_corpus(50, 20, seed=1))
+    assert sents == list(make_offline_assets.synthetic_corpus(50, 20, seed=1)) and all(s[-1] in "।॥" for s in sents)
+
+
 def test_streaming_dataset_sop_instances(bn_tokenizer):
     from dedloc_b200.trainers.sahajbert.dataset_streaming import (bengali_sentence_tokenize,
                                                                     make_lazy_wikioscar_dataset)
