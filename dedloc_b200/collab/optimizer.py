@@ -20,6 +20,7 @@ from __future__ import annotations
 
 import asyncio
 import logging
+import os
 import threading
 import time
 from typing import Any, Dict, List, Optional
@@ -73,7 +74,7 @@ class CollaborativeOptimizer:
                  peer_key: Optional[bytes] = None, expected_group_size_from_tracker: bool = True,
                  replicate_state: bool = False, replicate_state_every: int = 8,
                  step_slack_fraction: float = 0.75, liveness_window: float = 3.0, kernel_timeout: Optional[float] = None,
-                 **unused_kwargs):
+                 emulated_uplink_mbps: Optional[float] = None, **unused_kwargs):
         if compression is not None:  # sgd_collaborative.py:150 spells the kwarg `compression=`
             compression_type = compression
         if isinstance(compression_type, str):
@@ -86,6 +87,10 @@ class CollaborativeOptimizer:
         # sockets; members that share NVLink launch within milliseconds of each other once the group is formed, so a
         # member that is still absent after a few seconds was killed between matchmaking and the launch.
         self.kernel_timeout = min(self.averaging_timeout, 5.0) if kernel_timeout is None else float(kernel_timeout)
+        # socket rounds only: shape this peer's sends to a link of that speed (the reference's `tc` setup, AWS_runner.ipynb)
+        if not emulated_uplink_mbps and os.environ.get("DEDLOC_EMULATED_UPLINK_MBPS"):
+            emulated_uplink_mbps = float(os.environ["DEDLOC_EMULATED_UPLINK_MBPS"])
+        self.emulated_uplink_mbps = emulated_uplink_mbps
         self.averaging_expiration, self.target_group_size = averaging_expiration, target_group_size
         self.step_tolerance, self.client_mode, self.auxiliary = step_tolerance, client_mode, auxiliary
         self.allow_state_sharing = allow_state_sharing and not auxiliary
@@ -181,7 +186,7 @@ class CollaborativeOptimizer:
                                         averaging_expiration=self.averaging_expiration,
                                         client_mode=self.client_mode)
         self._cpu_averager = CPUAverager(self._server, self._client, self.compression_type,
-                                         timeout=self.averaging_timeout)
+                                         timeout=self.averaging_timeout, uplink_mbps=self.emulated_uplink_mbps)
         if self._server is not None:
             self._server.handlers["download_state"] = self._rpc_download_state
         self.tracker = ProgressTracker(self.dht, self.prefix, self.peer_key, self.target_batch_size,

@@ -77,12 +77,34 @@ class _RoundState:
             self.done.set_result(self.acc / max(self.total_weight, 1e-30))
 
 
+class UplinkShaper:
+    """Emulated uplink of one peer (the reference shapes its AWS peers with `tc`: 200 / 100 / 50 Mbit/s trainers, 500
+    Mbit/s aux peers -- albert/AWS_runner.ipynb cells 1, 9, 12). Everything this peer sends in an averaging round goes
+    through `send(nbytes)`, which returns when a link of `mbit_per_s` would have finished transmitting it; concurrent
+    transmissions share the link (they queue). None / 0 = unshaped."""
+
+    def __init__(self, mbit_per_s: Optional[float]):
+        self.bytes_per_s = float(mbit_per_s) * 1e6 / 8 if mbit_per_s else 0.0
+        self._free_at = 0.0
+        self.sent_bytes = 0
+
+    async def send(self, nbytes: int) -> None:
+        self.sent_bytes += nbytes
+        if self.bytes_per_s <= 0:
+            return
+        loop = asyncio.get_event_loop()
+        start = max(loop.time(), self._free_at)
+        self._free_at = start + nbytes / self.bytes_per_s
+        await asyncio.sleep(max(0.0, self._free_at - loop.time()))
+
+
 class CPUAverager:
     """Serves `allreduce_part` on the peer's RPC server and runs rounds on the DHT loop."""
 
     def __init__(self, server: Optional[RPCServer], client: RPCClient, compression: CompressionType,
-                 timeout: float = 30.0):
+                 timeout: float = 30.0, uplink_mbps: Optional[float] = None):
         self.client, self.compression, self.timeout = client, CompressionType(compression), timeout
+        self.uplink = UplinkShaper(uplink_mbps)
         self.rounds: Dict[bytes, _RoundState] = {}
         self.early: Dict[bytes, List[tuple]] = {}
         if server is not None:
@@ -102,7 +124,9 @@ class CPUAverager:
         state.add(sender, decoded, state.weights[sender])
         average = await asyncio.wait_for(asyncio.shield(state.done), self.timeout)
         delta = average - decoded
-        return comp.to_bytes(comp.encode(delta, state.codec if state.codec is not None else self._delta_codec()))
+        reply = comp.to_bytes(comp.encode(delta, state.codec if state.codec is not None else self._delta_codec()))
+        await self.uplink.send(len(reply))
+        return reply
 
     def _delta_codec(self) -> CompressionType:
         return self.compression
@@ -134,9 +158,10 @@ class CPUAverager:
                     return
                 enc = comp.encode(flat[b:e], codec)
                 sent = comp.decode(enc)  # what the owner will see from us
+                data = comp.to_bytes(enc)
+                await self.uplink.send(len(data))
                 raw = await self.client.call(group.endpoints[j], "allreduce_part",
-                                             {"group_id": group.group_id, "phase": phase, "sender": me,
-                                              "data": comp.to_bytes(enc)},
+                                             {"group_id": group.group_id, "phase": phase, "sender": me, "data": data},
                                              timeout=self.timeout)
                 delta = comp.decode(comp.from_bytes(raw))
                 out[b:e] = sent + delta

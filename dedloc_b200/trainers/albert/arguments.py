@@ -43,6 +43,8 @@ class AveragerArguments:
         default=30, metadata={"help": "Lifetime (s) of a progress record: a peer that stops reporting drops out of the count after this"})
     liveness_window: float = field(
         default=3.0, metadata={"help": "A peer whose last progress report is older than this (and older than 4x its usual reporting interval) is no longer waited for when a group forms"})
+    emulated_uplink_mbps: float = field(
+        default=0.0, metadata={"help": "Socket rounds only: pace everything this peer sends as a link of this many Mbit/s would (0 = as fast as the machine allows); for reproducing heterogeneous-bandwidth experiments on one machine"})
     kernel_timeout: float = field(
         default=5.0, metadata={"help": "How long (s) the NVLink all-reduce kernel waits for a group member that never shows up before the round is abandoned"})
 

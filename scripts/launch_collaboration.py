@@ -46,6 +46,11 @@ def main():
     ap.add_argument("--compression", default="FLOAT16")
     ap.add_argument("--synthetic_data", action="store_true")
     ap.add_argument("--config_path", default="")
+    ap.add_argument("--uplinks", default="",
+                    help="comma-separated Mbit/s, cycled over the trainers (the reference's AWS fleet: 200,200,200,200,"
+                         "100,100,100,100,100,100,100,100,50,50,50,50): sets --bandwidth (load balancing) and "
+                         "--emulated_uplink_mbps (pacing of the socket all-reduce) of each trainer; --aux_uplink for aux peers")
+    ap.add_argument("--aux_uplink", type=float, default=0.0)
     ap.add_argument("--run_for", type=float, default=0, help="seconds; 0 = until interrupted")
     ap.add_argument("--kill_every", type=float, default=0)
     ap.add_argument("--pause_every", type=float, default=0)
@@ -89,6 +94,10 @@ def main():
             a.append("--client_mode")
         if args.device:
             a += ["--device", args.device]
+        uplinks = [float(x) for x in args.uplinks.split(",") if x]
+        rate = args.aux_uplink if i >= args.trainers else (uplinks[i % len(uplinks)] if uplinks else 0.0)
+        if rate > 0:
+            a += ["--bandwidth", str(rate), "--emulated_uplink_mbps", str(rate)]
         return a + passthrough
 
     fleet = {}

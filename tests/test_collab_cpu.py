@@ -272,3 +272,46 @@ def test_silent_peer_stops_counting_as_live_long_before_its_record_expires():
     finally:
         second.shutdown()
         first.shutdown()
+
+
+def test_emulated_uplinks_pace_the_round_and_shift_load_to_the_fast_peer():
+    """A7 link shaping (albert/AWS_runner.ipynb shapes peers to 200 / 100 / 50 Mbit/s with tc): `bandwidth` decides
+    the share of the vector a peer reduces, `emulated_uplink_mbps` paces what it sends."""
+    import asyncio
+
+    from dedloc_b200.collab.matchmaking import GroupInfo
+    from dedloc_b200.dht.protocol import RPCClient, RPCServer
+    from dedloc_b200.parallel.cpu_backend import CPUAverager, load_balance_peers
+    from dedloc_b200.utils.compression import CHUNK
+
+    n = 64 * CHUNK                                   # 512 KiB of fp32
+    rates = [8.0, 2.0]                               # Mbit/s: 1 MB/s and 0.25 MB/s
+    counts = load_balance_peers(n // CHUNK, rates)
+    assert counts[0] > counts[1] and sum(counts) == n // CHUNK
+
+    async def main():
+        servers = [RPCServer({}), RPCServer({})]
+        ports = [await s.start("127.0.0.1", 0) for s in servers]
+        clients = [RPCClient(), RPCClient()]
+        avg = [CPUAverager(servers[i], clients[i], CompressionType.NONE, timeout=30.0, uplink_mbps=rates[i])
+               for i in range(2)]
+        endpoints = tuple(f"127.0.0.1:{p}" for p in ports)
+        xs = [torch.full((n,), float(i + 1)) for i in range(2)]
+        t0 = time.perf_counter()
+        outs = await asyncio.gather(*(avg[i].allreduce(GroupInfo(b"g" * 16, endpoints, ({}, {}), i), xs[i],
+                                                       [1.0, 1.0], rates) for i in range(2)))
+        dt = time.perf_counter() - t0
+        for c in clients:
+            await c.shutdown()
+        for s in servers:
+            await s.shutdown()
+        return outs, dt, [a.uplink.sent_bytes for a in avg]
+
+    outs, dt, sent = asyncio.run(main())
+    for o in outs:
+        assert torch.allclose(o, torch.full((n,), 1.5))
+    # each peer sends the other's part and returns the delta of its own: both directions carry about the same bytes
+    part_bytes = [c * CHUNK * 4 for c in counts]
+    assert abs(sent[0] - (part_bytes[1] + part_bytes[0])) < 0.05 * n * 4 and abs(sent[1] - sent[0]) < 0.05 * n * 4
+    slowest = max(sent[i] / (rates[i] * 1e6 / 8) for i in range(2))
+    assert 0.5 * slowest <= dt <= slowest + 2.0, (dt, slowest)
