@@ -239,3 +239,26 @@ class AuthRPCWrapper:
         envelope = await self.authorizer.sign_request(payload, service_public_key)
         reply = await client.call(endpoint, method, envelope, timeout)
         return await self.authorizer.validate_response(reply, envelope)
+
+
+class AuthenticatedClient:
+    """An RPCClient look-alike whose every call travels in a signed envelope and whose every reply is verified
+    (what hivemind's `authorizer=` argument does for the averager's and the optimizer's RPCs; the sahajBERT
+    notebook passes the Hugging Face authorizer there -- sahajbert/contributor_notebook.ipynb cell 3)."""
+
+    def __init__(self, client, authorizer: AuthorizerBase):
+        self._client, self._wrapper = client, AuthRPCWrapper(authorizer)
+
+    async def call(self, endpoint: str, method: str, payload: Any, timeout: float = 5.0) -> Any:
+        return await self._wrapper.call(self._client, endpoint, method, payload, timeout)
+
+    async def shutdown(self) -> None:
+        await self._client.shutdown()
+
+
+def protect_handlers(server, authorizer: AuthorizerBase, names) -> None:
+    """Replace the named handlers of an RPCServer by versions that refuse requests without a valid token."""
+    wrapper = AuthRPCWrapper(authorizer)
+    for name in names:
+        if name in server.handlers:
+            server.handlers[name] = wrapper.wrap_handler(server.handlers[name])

@@ -74,7 +74,7 @@ class CollaborativeOptimizer:
                  peer_key: Optional[bytes] = None, expected_group_size_from_tracker: bool = True,
                  replicate_state: bool = False, replicate_state_every: int = 8,
                  step_slack_fraction: float = 0.75, liveness_window: float = 3.0, kernel_timeout: Optional[float] = None,
-                 emulated_uplink_mbps: Optional[float] = None, **unused_kwargs):
+                 emulated_uplink_mbps: Optional[float] = None, authorizer: Any = None, **unused_kwargs):
         if compression is not None:  # sgd_collaborative.py:150 spells the kwarg `compression=`
             compression_type = compression
         if isinstance(compression_type, str):
@@ -137,6 +137,14 @@ class CollaborativeOptimizer:
         self._cpu_acc: Optional[List[torch.Tensor]] = None
         self._server: Optional[RPCServer] = None
         self._client = RPCClient()
+        # With an authorizer (collab/auth.py) the peer-to-peer RPCs of this optimizer -- group formation, socket
+        # all-reduce parts and, most of all, state download -- travel in signed envelopes carrying an access token;
+        # a peer without a valid token can neither join a group nor read anybody's parameters.
+        self.authorizer = authorizer
+        if authorizer is not None:
+            from .auth import AuthenticatedClient
+
+            self._client = AuthenticatedClient(self._client, authorizer)
         self._matchmaking: Optional[Matchmaking] = None
         self._cpu_averager = None
         self.endpoint: Optional[str] = None
@@ -148,6 +156,10 @@ class CollaborativeOptimizer:
             expected_drift_peers=expected_drift_peers, expected_drift_rate=expected_drift_rate,
             performance_ema_alpha=performance_ema_alpha, liveness_window=liveness_window)
         self.metadata_expiration = metadata_expiration
+        # mapped buffers of peers nobody met for two record lifetimes are unmapped (parallel/symm.py MappingLeases)
+        from ..parallel.symm import MappingLeases
+
+        self._mapping_leases = MappingLeases(ttl=2.0 * metadata_expiration)
         self.listen_on = listen_on
         self._started = False
         if start:
@@ -189,6 +201,10 @@ class CollaborativeOptimizer:
                                          timeout=self.averaging_timeout, uplink_mbps=self.emulated_uplink_mbps)
         if self._server is not None:
             self._server.handlers["download_state"] = self._rpc_download_state
+            if self.authorizer is not None:
+                from .auth import protect_handlers
+
+                protect_handlers(self._server, self.authorizer, ("download_state", "join_group", "allreduce_part"))
         self.tracker = ProgressTracker(self.dht, self.prefix, self.peer_key, self.target_batch_size,
                                        endpoint=self.endpoint, client_mode=self.client_mode,
                                        auxiliary=self.auxiliary, **self._tracker_kwargs)
@@ -444,7 +460,20 @@ class CollaborativeOptimizer:
                 self.lineage_depth = self._agreed_depth + 1
             self._last_round["averaging_s"] = time.perf_counter() - t1
             self._finish_global_step()
+            self._close_stale_mappings()
             self.stats["averaging_host_s"] += time.perf_counter() - t1
+
+    def _close_stale_mappings(self) -> None:
+        if not (self.is_fused and self.on_gpu):
+            return
+        keep = list(self._moment_owners or ())          # their moment chunks may still have to be pulled
+        for handle in self._mapping_leases.expired(time.monotonic(), keep=keep):
+            if handle != self.opt.buffers.handle:
+                try:
+                    self.opt.buffers.close_peer(handle)
+                    self.stats["mappings_closed"] = self.stats.get("mappings_closed", 0) + 1
+                except Exception as e:   # the peer's process is gone: nothing to salvage
+                    logger.debug("closing a stale peer mapping failed: %r", e)
 
     def _finish_global_step(self) -> None:
         self._params_parked = False
@@ -631,6 +660,7 @@ class CollaborativeOptimizer:
         if self.is_fused and self.on_gpu and all_gpu:
             try:
                 bases = [self.opt.buffers.peer_base(bytes(h)) for h in handles]
+                self._mapping_leases.touch(handles, time.monotonic())
             except Exception as e:
                 logger.warning("cannot map peer memory (%r): falling back to the socket butterfly", e)
                 bases = None
@@ -937,6 +967,7 @@ class CollaborativeOptimizer:
             r = buf.regions
             for _attempt in range(5):
                 base = buf.peer_base(bytes(meta["handle"]))
+                self._mapping_leases.touch([meta["handle"]], time.monotonic())
                 from .. import lib as native
 
                 stream = torch.cuda.current_stream(buf.device)

@@ -144,6 +144,11 @@ class PeerBuffers:
     def peer_base(self, handle: bytes) -> int:
         return self.symm.open_peer(handle)
 
+    def close_peer(self, handle: bytes) -> None:
+        """Unmap a peer that left (see symm.MappingLeases); cached launch parameters may hold its address."""
+        self.symm.close_peer(handle)
+        self._v2_cache.clear()
+
     def read_status(self) -> Dict[str, int]:
         self._status_host.copy_(self.status, non_blocking=False)
         code = int(self._status_host[0])

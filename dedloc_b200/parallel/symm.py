@@ -25,6 +25,29 @@ class _CudaArray:
         self._owner = owner  # keeps the allocation alive as long as a view exists
 
 
+class MappingLeases:
+    """Which peer mappings are still worth keeping. A mapping of a peer that left pins that peer's whole buffer on ITS
+    GPU until every importer closes it (CUDA IPC keeps the allocation alive for the importers), so a trainer that is
+    killed and restarted a few times would fill its GPU with the buffers of its dead predecessors. Every use of a
+    mapping renews its lease; `expired()` names the handles nobody used for `ttl` seconds."""
+
+    def __init__(self, ttl: float):
+        self.ttl = float(ttl)
+        self._last_used: Dict[bytes, float] = {}
+
+    def touch(self, handles, now: float) -> None:
+        for h in handles:
+            if h:
+                self._last_used[bytes(h)] = now
+
+    def expired(self, now: float, keep=()) -> list:
+        keep = {bytes(h) for h in keep if h}
+        out = [h for h, t in self._last_used.items() if now - t > self.ttl and h not in keep]
+        for h in out:
+            del self._last_used[h]
+        return out
+
+
 class SymmetricBuffer:
     """One device allocation that can be mapped by peer processes through a CUDA IPC handle."""
 

@@ -95,8 +95,14 @@ def main(argv=None):
     statistics_expiration = collaboration_args_dict.pop("statistics_expiration")
     adjusted_target_batch_size = collaboration_args_dict.pop("target_batch_size") - collaboration_args_dict.pop(
         "batch_size_lead")
+    authorizer = None
+    if getattr(training_args, "authorize", False):
+        from .huggingface_auth import authorize_with_huggingface
+
+        authorizer = authorize_with_huggingface()     # contributor_notebook.ipynb cell 3
     collaborative_optimizer = CollaborativeOptimizer(
         opt=opt, dht=dht, scheduler=scheduler, prefix=collaboration_args_dict.pop("experiment_prefix"),
+        authorizer=authorizer,
         compression_type=CompressionType.Value(collaboration_args_dict.pop("compression")),
         batch_size_per_step=total_batch_size_per_step, throughput=collaboration_args_dict.pop("bandwidth"),
         target_batch_size=adjusted_target_batch_size, client_mode=collaboration_args_dict.pop("client_mode"),

@@ -17,3 +17,20 @@ def test_stage_geometry_and_role_split():
                     nP, nR, nU, nA = _role_split(total, mode, owner, K)
                     assert nP + nR + nU + nA == total and nP >= 1 and nA >= 1
                     assert (nR >= 1) == owner and (nU >= 1) == (owner and mode != 0)
+
+
+def test_mapping_leases_expire_unused_peers_only():
+    """parallel/symm.py MappingLeases: mappings of peers that left are closed after two record lifetimes, except those
+    that still own optimizer moments."""
+    from dedloc_b200.parallel.symm import MappingLeases
+
+    leases = MappingLeases(ttl=60.0)
+    a, b, c = b"a" * 64, b"b" * 64, b"c" * 64
+    leases.touch([a, b, c, None, b""], now=0.0)
+    leases.touch([a], now=50.0)
+    assert leases.expired(now=61.0, keep=[c]) == [b]       # a was used recently, c still owns moment chunks
+    assert leases.expired(now=61.0) == [c]                 # ... until it no longer does
+    assert leases.expired(now=100.0) == []
+    assert leases.expired(now=111.0) == [a]
+    leases.touch([b], now=120.0)                           # a peer that comes back is tracked again
+    assert leases.expired(now=200.0) == [b]

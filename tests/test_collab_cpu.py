@@ -315,3 +315,51 @@ def test_emulated_uplinks_pace_the_round_and_shift_load_to_the_fast_peer():
     assert abs(sent[0] - (part_bytes[1] + part_bytes[0])) < 0.05 * n * 4 and abs(sent[1] - sent[0]) < 0.05 * n * 4
     slowest = max(sent[i] / (rates[i] * 1e6 / 8) for i in range(2))
     assert 0.5 * slowest <= dt <= slowest + 2.0, (dt, slowest)
+
+
+def test_authorizer_protects_group_formation_and_state_download():
+    """With `authorizer=` every optimizer RPC carries a signed access token: peers of one authority average together
+    and share state; a peer holding a token from somewhere else gets neither a group nor anybody's parameters."""
+    from dedloc_b200.collab.auth import LocalAuthority, LocalTokenAuthorizer
+    from dedloc_b200.dht.validation import RSAPrivateKey
+
+    authority = LocalAuthority(allowlist={"alice", "bob"})
+    auth = lambda name, a=authority: LocalTokenAuthorizer(a, name, RSAPrivateKey())   # noqa: E731
+    first, m0, c0 = make_peer(None, "cfg1auth", target=8, authorizer=auth("alice"))
+    d1, m1, c1 = make_peer(first, "cfg1auth", target=8, authorizer=auth("bob"))
+    d2 = m2 = c2 = None
+    log = []
+    try:
+        threads = [threading.Thread(target=run_trainer, args=(i, m, c, 2, log)) for i, (m, c) in enumerate(((m0, c0), (m1, c1)))]
+        [t.start() for t in threads]
+        [t.join(timeout=120) for t in threads]
+        assert c0.local_step == c1.local_step == 2
+        assert c0.stats["solo_rounds"] == 0 and c0.stats["failed_rounds"] == 0, c0.stats
+        assert_same_params(m0, m1)
+        # an outsider: right DHT, wrong authority
+        d2, m2, c2 = make_peer(first, "cfg1auth", target=8, seed=5,
+                               authorizer=auth("mallory", LocalAuthority(allowlist={"mallory"})))
+        before = [p.detach().clone() for p in m2.parameters()]
+        assert c2.load_state_from_peers() is False
+        assert all(torch.equal(a, b) for a, b in zip(before, m2.parameters())), "nothing was downloaded"
+        assert c2.stats["state_downloads"] == 0
+        # ... and one without any authorizer at all
+        d3, m3, c3 = make_peer(first, "cfg1auth", target=8, seed=6)
+        try:
+            assert c3.load_state_from_peers() is False
+        finally:
+            c3.shutdown()
+            d3.shutdown()
+        # a member with a valid token does get the state
+        d4, m4, c4 = make_peer(first, "cfg1auth", target=8, seed=7, authorizer=auth("alice"))
+        try:
+            assert c4.load_state_from_peers() is True and c4.local_step == 2
+            assert_same_params(m4, m0)
+        finally:
+            c4.shutdown()
+            d4.shutdown()
+    finally:
+        for c, d in ((c0, first), (c1, d1), (c2, d2)):
+            if c is not None:
+                c.shutdown()
+                d.shutdown()
