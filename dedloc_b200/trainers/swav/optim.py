@@ -194,12 +194,14 @@ class SGDCollaborative(ClassyOptimizer):
                                    clip=self._larc_config.get("clip", False), eps=self._larc_config["eps"])
         self.dht = self._dht or DHT(listen_on=self._listen_on_dht, initial_peers=self._dht_initial_peers, start=True,
                                     listen=True)
+        # sgd_collaborative.py:145-157 fixes these; `collab_kwargs` (tests, benchmarks) may override any of them
+        options = dict(verbose=True, compression=CompressionType.Value(self._compression), prefix=self._exp_prefix,
+                       target_group_size=self._target_group_size, target_batch_size=self._target_batch_size,
+                       batch_size_per_step=self._batch_size_for_tracking, listen_on=self._listen_on_averager,
+                       averaging_expiration=5.0, metadata_expiration=30, averaging_timeout=30, start=True)
+        options.update(self._collab_kwargs)
         self.optimizer = CollaborativeOptimizer(
-            opt=inner, scheduler=self._scheduler_cls(inner) if self._scheduler_cls else None, dht=self.dht, verbose=True,
-            compression=CompressionType.Value(self._compression), prefix=self._exp_prefix,
-            target_group_size=self._target_group_size, target_batch_size=self._target_batch_size,
-            batch_size_per_step=self._batch_size_for_tracking, listen_on=self._listen_on_averager,
-            averaging_expiration=5.0, metadata_expiration=30, averaging_timeout=30, start=True, **self._collab_kwargs)
+            opt=inner, scheduler=self._scheduler_cls(inner) if self._scheduler_cls else None, dht=self.dht, **options)
 
     def get_classy_state(self) -> Dict[str, Any]:
         return None
