@@ -10,11 +10,27 @@ def _rand(shape, seed, scale=1.0, dtype=torch.bfloat16):
     return (torch.randn(shape, generator=g) * scale).to(dtype).cuda()
 
 
-def _check(out, ref, what, rtol=2e-2, atol=2e-2):
+def _check(out, ref, what, rtol=2e-2, atol=2e-2, tile=64):
+    """Element-wise bound relative to the largest reference value, AND a per-tile bound relative to that tile's own
+    norm: a wrong tile of small values passes the first check, not the second. The tile tolerance is 5x the rounding
+    of the output format (bf16: 2^-9 per element; fp32 outputs only differ by accumulation order)."""
+    is_fp32 = out.dtype == torch.float32
     out, ref = out.float(), ref.float()
     err = (out - ref).abs().max().item()
     denom = ref.abs().max().item() + 1e-6
     assert torch.allclose(out, ref, rtol=rtol, atol=atol * denom), f"{what}: max err {err:.4g} (ref max {denom:.4g})"
+    if out.dim() != 2:
+        return
+    M, N = out.shape
+    pm, pn = (-M) % tile, (-N) % tile
+    d = torch.nn.functional.pad(out - ref, (0, pn, 0, pm))
+    r = torch.nn.functional.pad(ref, (0, pn, 0, pm))
+    tiles = lambda x: x.reshape((M + pm) // tile, tile, (N + pn) // tile, tile).pow(2).sum(dim=(1, 3)).sqrt()  # noqa: E731
+    d_norm, r_norm = tiles(d), tiles(r)
+    tol = 2e-3 if is_fp32 else 1e-2
+    bad = d_norm > tol * r_norm + 1e-3 * denom * tile
+    assert not bool(bad.any()), (f"{what}: tile {tuple(bad.nonzero()[0].tolist())} is off by "
+                                 f"{float((d_norm / (r_norm + 1e-12))[bad].max()):.3g} of its own norm")
 
 
 @pytest.mark.parametrize("a_mn,b_mn", [(False, False), (False, True), (True, False), (True, True)])
