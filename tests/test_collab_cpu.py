@@ -363,3 +363,43 @@ def test_authorizer_protects_group_formation_and_state_download():
             if c is not None:
                 c.shutdown()
                 d.shutdown()
+
+
+def test_dead_peers_record_neither_delays_rounds_nor_splits_the_fleet():
+    """Regression for the elasticity benchmark: a killed peer's progress record outlives it by
+    metadata_expiration. While it is there (a) the leader must not wait averaging_expiration for it in every round and
+    (b) it must not push the peer count over target_group_size (which would split the fleet into matchmaking buckets).
+    A replacement peer joins meanwhile, as the fleet launcher does."""
+    kw = dict(target=32, target_group_size=4, averaging_expiration=3.0, metadata_expiration=30.0, liveness_window=0.6)
+    first, m0, c0 = make_peer(None, "cfg1live", **kw)
+    peers = [(first, m0, c0)] + [make_peer(first, "cfg1live", **kw) for _ in range(3)]
+    stop_victim = threading.Event()
+    log, n_rounds = [], 9
+    threads = [threading.Thread(target=run_trainer, args=(i, m, c, n_rounds, log, stop_victim if i == 3 else None))
+               for i, (_, m, c) in enumerate(peers)]
+    newcomer = None
+    try:
+        [t.start() for t in threads]
+        while peers[3][2].local_step < 2:
+            time.sleep(0.01)
+        stop_victim.set()                      # peer 3 stops stepping and reporting; nothing is withdrawn from the DHT
+        threads[3].join(timeout=30)
+        newcomer = make_peer(first, "cfg1live", seed=3, **kw)
+        assert newcomer[2].load_state_from_peers()
+        t_new = threading.Thread(target=run_trainer, args=(4, newcomer[1], newcomer[2], n_rounds, log))
+        t_new.start()
+        [t.join(timeout=240) for t in threads[:3] + [t_new]]
+        survivors = [c for _, _, c in peers[:3]]
+        for c in survivors + [newcomer[2]]:
+            assert c.local_step == n_rounds, [x.local_step for x in survivors]
+            assert c._matchmaking.group_bits == "", "the dead peer's record must not create matchmaking buckets"
+        for c in survivors:
+            rounds_after_death = n_rounds - 2
+            # before the fix: >= averaging_expiration (3 s) in each of them
+            assert c.stats["matchmaking_s"] < 0.35 * 3.0 * rounds_after_death, c.stats
+            assert c.stats["solo_rounds"] <= 1 and c.stats["failed_rounds"] <= 1, c.stats
+        assert_same_params(peers[0][1], peers[1][1])
+    finally:
+        for d, _, c in peers + ([newcomer] if newcomer else []):
+            c.shutdown()
+            d.shutdown()
