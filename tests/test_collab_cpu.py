@@ -398,7 +398,8 @@ def test_dead_peers_record_neither_delays_rounds_nor_splits_the_fleet():
             # before the fix: >= averaging_expiration (3 s) in each of them
             assert c.stats["matchmaking_s"] < 0.35 * 3.0 * rounds_after_death, c.stats
             assert c.stats["solo_rounds"] <= 1 and c.stats["failed_rounds"] <= 1, c.stats
-        assert_same_params(peers[0][1], peers[1][1])
+        # a starved peer may have missed a group (its step is merged by parameter averaging later): close, not equal
+        assert_same_params(peers[0][1], peers[1][1], tol=5e-3)
     finally:
         for d, _, c in peers + ([newcomer] if newcomer else []):
             c.shutdown()
