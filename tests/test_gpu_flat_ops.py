@@ -41,6 +41,16 @@ def test_sumsq_and_accumulate_clip(native):
         acc_ref += x.float()
         assert torch.allclose(acc, acc_ref, rtol=1e-5, atol=1e-6)
         assert torch.equal(g2, x)
+        # lengths that end inside an unrolled step / inside a block (any multiple of 8 is legal)
+        for n in (8, 1000, 8 * 1237, 4 * 256 * 4 * 3 + 24):
+            xs = x[:n].clone()
+            a = torch.arange(n, dtype=torch.float32, device="cuda")
+            guard = torch.full((n + 64,), 7.0, device="cuda")
+            guard[:n] = a
+            flat_ops.accumulate_clip(guard[:n], xs, None, 0.0, zero_grad=True)
+            assert torch.allclose(guard[:n], a + x[:n].float(), rtol=1e-5, atol=1e-6), n
+            assert float(guard[n:].min()) == 7.0 == float(guard[n:].max()), "wrote past the end"
+            assert xs.abs().max().item() == 0.0
 
 
 TOL = {  # max abs error / max abs value
