@@ -27,7 +27,7 @@ class AlbertTrainingArguments(_AlbertTrainingArguments):
     dataloader_num_workers: int = 0
     authorize: bool = field(
         default=False,
-        metadata={"help": "Log in to the Hugging Face hub (HF_USER_NAME / HF_PASSWORD or a prompt), obtain an access "
+        metadata={"help": "Log in to the Hugging Face hub (HF_USERNAME / HF_PASSWORD or a prompt), obtain an access "
                           "token for the experiment and sign every averaging / state-sharing RPC with it; peers "
                           "without a token of the same experiment are refused (what the contributor notebook does)"})
 
