@@ -1046,6 +1046,7 @@ class CollaborativeOptimizer:
             src_is_me = h == buf.handle
             try:
                 base = buf.symm.ptr if src_is_me else buf.peer_base(h)
+                self._mapping_leases.touch([h], time.monotonic())
             except Exception:
                 continue          # that owner is gone: its chunks keep the donor's (older) values
             if src_is_me:
