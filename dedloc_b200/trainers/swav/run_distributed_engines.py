@@ -19,6 +19,9 @@ from .train import train_main
 
 
 def hydra_main(overrides):
+    if any(ov in ("-h", "--help", "help") for ov in overrides):
+        print(__doc__)
+        return None
     max_iterations = 0
     rest = []
     for ov in overrides:
