@@ -414,8 +414,13 @@ class CollaborativeOptimizer:
                 share = lambda live: max(-(-live // buckets), 2)  # noqa: E731
                 expected = share(state.live_peers) if self.expected_group_size_from_tracker else None
                 # the tracker thread keeps re-reading the records while we wait for the group
-                live_now = ((lambda: share(self.tracker.collaboration_state.live_peers))
-                            if self.expected_group_size_from_tracker else None)
+                # (a failed read shows up as "no records": keep the earlier expectation then)
+                def live_now():
+                    live = self.tracker.collaboration_state.live_peers
+                    return share(live) if live >= 1 else None
+
+                if not self.expected_group_size_from_tracker:
+                    live_now = None
                 # the others finished this step while we were looking for them: nobody is left to form a group with
                 left_behind = lambda: self.tracker.collaboration_state.optimizer_step > self.local_step  # noqa: E731
                 try:
