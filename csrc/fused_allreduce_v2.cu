@@ -20,6 +20,14 @@
 //        APPLY(s)   wait outflag[s][*]; p32 -= scale_t * direction; bf16 mirror; optional row normalisation
 //     so the NVLink stores of PUSH and UPDATE, the local reduction and the HBM-bound APPLY overlap stage by stage,
 //     and a tensor's update starts as soon as ITS norms are complete (not after a barrier over all tensors).
+//     Two schedules of the same roles (Params::sequential): CONCURRENT splits the CTAs into four role groups that
+//     work on different stages at once; SEQUENTIAL (the default) lets every CTA run PUSH, REDUCE, UPDATE, APPLY in
+//     turn over ONE stage, so each phase has the whole chip. Measured (profiles/traces/, profiles/README.md): the
+//     thread that completes a stage pays a system-scope fence that waits for ALL traffic in flight on the GPU
+//     (7-25 us under load, even when its own stores were local), so every additional stage adds latency that the
+//     overlap does not win back at these sizes, and a role group that owns a quarter of the SMs cannot saturate
+//     NVLink or HBM on its own. The hand-over between phases stays flag-based either way (no grid.sync, no barrier
+//     across GPUs): a CTA starts REDUCE on the chunks whose senders have arrived while other CTAs still push.
 //   * 2 bytes per element leave the owner instead of 6 (fp32 master + bf16 mirror) or 14 (with moments): every
 //     member applies the same rounded direction to its own replica of the fp32 master, which therefore stays
 //     bit-identical on all members; moments live with the owner (replicate_state pushes them as well).
