@@ -27,7 +27,8 @@
 //     (7-25 us under load, even when its own stores were local), so every additional stage adds latency that the
 //     overlap does not win back at these sizes, and a role group that owns a quarter of the SMs cannot saturate
 //     NVLink or HBM on its own. The hand-over between phases stays flag-based either way (no grid.sync, no barrier
-//     across GPUs): a CTA starts REDUCE on the chunks whose senders have arrived while other CTAs still push.
+//     across GPUs): a CTA that has finished its share of a phase polls the flags of the next one (raised by the last
+//     CTA of every sender for that stage) while other CTAs, here or on other GPUs, are still working.
 //   * 2 bytes per element leave the owner instead of 6 (fp32 master + bf16 mirror) or 14 (with moments): every
 //     member applies the same rounded direction to its own replica of the fp32 master, which therefore stays
 //     bit-identical on all members; moments live with the owner (replicate_state pushes them as well).
