@@ -164,6 +164,7 @@ def main_ours(args):
     cfg = PeerConfig(prefix="bench", target_batch_size=args.target_batch_size, micro_batch=args.micro_batch,
                      seq_len=seq, compression=args.compression, target_group_size=max(world, 2),
                      averaging_expiration=5.0, averaging_timeout=60.0, impl=args.ops,
+                     kernel_timeout=30.0,     # no faults in this run: a late member is start-up skew, not a dead peer
                      overlap_wgrad=args.overlap_wgrad)
     trainer = build_albert_peer(dht, cfg, model_cfg, device=device, seed=0)
     data = SyntheticMLMBatches(model_cfg.vocab_size, seq, args.micro_batch, seed=1234 + rank, padded=args.padded)

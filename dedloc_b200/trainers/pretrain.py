@@ -107,6 +107,7 @@ class PeerConfig:
     target_group_size: int = 256
     averaging_expiration: float = 5.0
     averaging_timeout: float = 30.0
+    kernel_timeout: Optional[float] = None     # None = CollaborativeOptimizer's default (5 s)
     metadata_expiration: float = 30.0
     min_refresh_period: float = 0.05
     max_refresh_period: float = 1.0
@@ -258,7 +259,7 @@ def build_albert_peer(dht: DHT, cfg: PeerConfig, model_cfg: Optional[AlbertConfi
         batch_size_per_step=cfg.micro_batch, scheduler=scheduler,
         compression_type=CompressionType.Value(cfg.compression), target_group_size=cfg.target_group_size,
         averaging_expiration=cfg.averaging_expiration, averaging_timeout=cfg.averaging_timeout,
-        metadata_expiration=cfg.metadata_expiration, min_refresh_period=cfg.min_refresh_period,
+        kernel_timeout=cfg.kernel_timeout, metadata_expiration=cfg.metadata_expiration, min_refresh_period=cfg.min_refresh_period,
         max_refresh_period=cfg.max_refresh_period, default_refresh_period=cfg.default_refresh_period,
         client_mode=cfg.client_mode, max_grad_norm=cfg.max_grad_norm, peer_key=peer_key, **collab_kwargs)
     model.train()
