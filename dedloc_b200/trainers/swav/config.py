@@ -44,6 +44,8 @@ DEFAULTS: Dict[str, Any] = {
     "MULTI_PROCESSING_METHOD": "fork",
     "HOOKS": {"LOG_GPU_STATS": False, "MEMORY_SUMMARY": {"PRINT_MEMORY_SUMMARY": False, "LOG_ITERATION_NUM": 0},
               "PERF_STATS": {"MONITOR_PERF_STATS": False, "ROLLING_BTIME_FREQ": -1},
+              "MODEL_COMPLEXITY": {"COMPUTE_COMPLEXITY": False, "INPUT_SHAPE": [3, 224, 224]},
+              "PROFILER": {"PROFILE_FORWARD": False},
               "TENSORBOARD_SETUP": {"USE_TENSORBOARD": False, "LOG_DIR": ".", "EXPERIMENT_LOG_DIR": "tensorboard",
                                     "FLUSH_EVERY_N_MIN": 5, "LOG_PARAMS": True, "LOG_PARAMS_GRADIENTS": True,
                                     "LOG_PARAMS_EVERY_N_ITERS": 310}},

@@ -3,7 +3,7 @@
 SwAVUpdateQueueScoresHook, NormalizePrototypesHook (swav_hooks.py:11-92), CheckNanLossHook, FreezeParametersHook
 (state_update_hooks.py:207-280), UpdateBatchesSeenHook / UpdateTrainIterationNumHook / UpdateTrainBatchTimeHook,
 LogLossLrEtaHook, LogPerfTimeMetricsHook, LogGpuStatsHook, LogGpuMemoryHook, LogLossMetricsCheckpointHook
-(log_hooks.py), SSLTensorboardHook. Hook points follow ClassyHook: on_start, on_forward, on_loss_and_meter,
+(log_hooks.py), SSLTensorboardHook, SSLModelComplexityHook (state_update_hooks.py:16-63), ProfilerHook (ClassyVision). Hook points follow ClassyHook: on_start, on_forward, on_loss_and_meter,
 on_backward, on_update, on_step, on_phase_end, on_end."""
 from __future__ import annotations
 
@@ -160,6 +160,89 @@ class LogGpuMemoryHook(ClassyHook):
             logger.info(torch.cuda.memory_summary())
 
 
+def model_complexity(model: torch.nn.Module, input_shape, device=None, batch: int = 2) -> dict:
+    """#parameters, forward multiply-accumulates and activations (outputs of convolutions / linear layers) PER
+    SAMPLE for one crop of `input_shape`, counted with forward hooks on a dummy forward in eval mode
+    (classy_vision/generic/profiler.py:89-560 counts the same three; only conv / linear layers carry MACs here)."""
+    device = device or next(model.parameters()).device
+    macs, acts = [0], [0]
+
+    def conv_hook(m, inp, out):
+        kh, kw = m.kernel_size
+        macs[0] += out.numel() * (m.in_channels // m.groups) * kh * kw
+        acts[0] += out.numel()
+
+    def linear_hook(m, inp, out):
+        macs[0] += out.numel() * m.in_features
+        acts[0] += out.numel()
+
+    handles = []
+    for m in model.modules():
+        if isinstance(m, torch.nn.Conv2d):
+            handles.append(m.register_forward_hook(conv_hook))
+        elif isinstance(m, torch.nn.Linear):
+            handles.append(m.register_forward_hook(linear_hook))
+    was_training = model.training
+    model.eval()
+    try:
+        with torch.no_grad():
+            dtype = next(model.parameters()).dtype
+            model([torch.zeros(batch, *input_shape, device=device, dtype=dtype)])
+    finally:
+        for h in handles:
+            h.remove()
+        model.train(was_training)
+    return {"params": sum(p.numel() for p in model.parameters()), "macs_per_sample": macs[0] // batch,
+            "flops_per_sample": 2 * macs[0] // batch, "activations_per_sample": acts[0] // batch}
+
+
+class SSLModelComplexityHook(ClassyHook):
+    """HOOKS.MODEL_COMPLEXITY.COMPUTE_COMPLEXITY: log #params / #flops / #activations once at start
+    (vissl/hooks/state_update_hooks.py:16-63)."""
+
+    def __init__(self, input_shape):
+        self.input_shape = tuple(input_shape)
+
+    def on_start(self, task):
+        try:
+            c = model_complexity(task.model, self.input_shape, task.device)
+        except Exception as e:       # as in the reference: a model that cannot take the dummy input is not an error
+            logger.info(f"model complexity not computed: {e!r}")
+            return
+        task.model_complexity = c
+        logger.info(f"Model complexity for input {list(self.input_shape)}: params {c['params'] / 1e6:.3f} M, "
+                    f"forward {c['flops_per_sample'] / 1e9:.3f} GFLOPs ({c['macs_per_sample'] / 1e9:.3f} GMACs), "
+                    f"activations {c['activations_per_sample'] / 1e6:.3f} M")
+
+
+class ProfilerHook(ClassyHook):
+    """One profiled dummy forward at start, table sorted by device (or host) time -- classy_vision/hooks/
+    profiler_hook.py:15-38. Off unless HOOKS.PROFILER.PROFILE_FORWARD is set; for kernel-level work use ncu / NVTX
+    (`DEDLOC_NVTX=1`), this is the quick look the reference offers."""
+
+    def __init__(self, input_shape, row_limit: int = 25):
+        self.input_shape, self.row_limit = tuple(input_shape), row_limit
+
+    def on_start(self, task):
+        from torch.profiler import ProfilerActivity, profile
+
+        acts = [ProfilerActivity.CPU] + ([ProfilerActivity.CUDA] if task.device.type == "cuda" else [])
+        model = task.model
+        was_training = model.training
+        model.eval()
+        try:
+            with torch.no_grad(), profile(activities=acts) as prof:
+                dtype = next(model.parameters()).dtype
+                model([torch.zeros(2, *self.input_shape, device=task.device, dtype=dtype)])
+            key = "cuda_time_total" if task.device.type == "cuda" else "cpu_time_total"
+            task.profile_table = prof.key_averages().table(sort_by=key, row_limit=self.row_limit)
+            logger.info("Forward profile:\n" + task.profile_table)
+        except Exception as e:
+            logger.info(f"forward profile not taken: {e!r}")
+        finally:
+            model.train(was_training)
+
+
 class LogLossMetricsCheckpointHook(ClassyHook):
     """VISSL-shaped checkpoints (log_hooks.py:268-417): `model_iteration{N}.torch` every CHECKPOINT_ITER_FREQUENCY
     iterations, `model_phase{N}.torch` every CHECKPOINT_FREQUENCY phases, `model_final_checkpoint_phase{N}.torch`,
@@ -244,5 +327,9 @@ def default_hook_generator(cfg) -> List[ClassyHook]:
         hooks.append(LogGpuMemoryHook(cfg.HOOKS.MEMORY_SUMMARY.LOG_ITERATION_NUM))
     if cfg.HOOKS.TENSORBOARD_SETUP.USE_TENSORBOARD:
         hooks.append(SSLTensorboardHook(cfg))
+    if cfg.HOOKS.MODEL_COMPLEXITY.COMPUTE_COMPLEXITY:
+        hooks.append(SSLModelComplexityHook(cfg.HOOKS.MODEL_COMPLEXITY.INPUT_SHAPE))
+    if cfg.HOOKS.PROFILER.PROFILE_FORWARD:
+        hooks.append(ProfilerHook(cfg.HOOKS.MODEL_COMPLEXITY.INPUT_SHAPE))
     hooks += [LogLossLrEtaHook(cfg.LOG_FREQUENCY), LogLossMetricsCheckpointHook(cfg)]
     return hooks

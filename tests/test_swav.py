@@ -147,3 +147,37 @@ def test_two_collaborative_swav_peers(tmp_path):
         t.optimizer.dht.shutdown()
     boot.shutdown()
     run_initial_dht_node.main(["--listen_on", "127.0.0.1:*", "--refresh_period", "0.01", "--max_iterations", "2"])
+
+
+def test_model_complexity_and_profiler_hooks():
+    """HOOKS.MODEL_COMPLEXITY (#params / #flops / #activations on a dummy forward,
+    vissl/hooks/state_update_hooks.py:16-63) and the one-forward ProfilerHook of ClassyVision."""
+    import types
+
+    from dedloc_b200.models.swav import SwAVModel
+    from dedloc_b200.trainers.swav.hooks import (ProfilerHook, SSLModelComplexityHook, default_hook_generator,
+                                                  model_complexity)
+
+    model = SwAVModel(depth=18, head_dims=(512, 64, 16), num_clusters=(32,))
+    c = model_complexity(model, (3, 64, 64))
+    assert c["params"] == sum(p.numel() for p in model.parameters())
+    head_macs = 512 * 64 + 64 * 16 + 16 * 32
+    # ResNet-18 at 224 px is 1.814 GMACs; convolutions scale with the pixel count
+    trunk = c["macs_per_sample"] - head_macs
+    assert abs(trunk / (1.814e9 * (64 / 224) ** 2) - 1) < 0.03, trunk
+    assert c["flops_per_sample"] == 2 * c["macs_per_sample"] and c["activations_per_sample"] > 0
+    assert model.training, "the hook restores the training mode"
+
+    cfg = compose(["config=pretrain/swav/swav_1node_resnet_submit", "config.HOOKS.MODEL_COMPLEXITY.COMPUTE_COMPLEXITY=true",
+                   "config.HOOKS.MODEL_COMPLEXITY.INPUT_SHAPE=[3, 64, 64]", "config.HOOKS.PROFILER.PROFILE_FORWARD=true",
+                   "config.HOOKS.TENSORBOARD_SETUP.USE_TENSORBOARD=false"])
+    kinds = [type(h) for h in default_hook_generator(cfg)]
+    assert SSLModelComplexityHook in kinds and ProfilerHook in kinds
+    task = types.SimpleNamespace(model=model, device=torch.device("cpu"))
+    for h in default_hook_generator(cfg):
+        if isinstance(h, (SSLModelComplexityHook, ProfilerHook)):
+            h.on_start(task)
+    assert task.model_complexity["params"] == c["params"] and "conv" in task.profile_table.lower()
+    off = [type(h) for h in default_hook_generator(compose(["config=pretrain/swav/swav_1node_resnet_submit",
+                                                           "config.HOOKS.TENSORBOARD_SETUP.USE_TENSORBOARD=false"]))]
+    assert SSLModelComplexityHook not in off and ProfilerHook not in off
