@@ -53,7 +53,9 @@ DEFAULTS: Dict[str, Any] = {
              "TRAIN": {"DATA_SOURCES": ["synthetic"], "DATASET_NAMES": ["synthetic"], "DATA_PATHS": [],
                        "BATCHSIZE_PER_REPLICA": 32, "LABEL_TYPE": "sample_index", "TRANSFORMS": [],
                        "COLLATE_FUNCTION": "default_collate", "DROP_LAST": True, "DATA_LIMIT": -1,
-                       "MMAP_MODE": True, "COPY_TO_LOCAL_DISK": False, "COPY_DESTINATION_DIR": ""}},
+                       "MMAP_MODE": True, "COPY_TO_LOCAL_DISK": False, "COPY_DESTINATION_DIR": "",
+                       # mixed into the shuffle seed of this peer; empty = something unique to the process
+                       "PEER_SHUFFLE_SALT": ""}},
     "TRAINER": {"TRAIN_STEP_NAME": "standard_train_step", "TASK_NAME": "self_supervision_task"},
     "METERS": {"name": ""},
     "MODEL": {"TRUNK": {"NAME": "resnet", "TRUNK_PARAMS": {"RESNETS": {"DEPTH": 50, "WIDTH_MULTIPLIER": 1,

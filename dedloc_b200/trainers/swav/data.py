@@ -157,11 +157,55 @@ class GenericSSLDataset(Dataset):
         return {"data": self.transform(img), "label": idx, "data_valid": valid, "data_idx": idx}
 
 
+class StatefulPeerSampler(torch.utils.data.Sampler):
+    """Shuffled order that is a pure function of (seed, epoch) and can start in the middle of an epoch after a resume
+    (vissl/data/data_helper.py:88-148 StatefulDistributedSampler). Every peer of a collaboration is a world of one,
+    so the rank / world split of the original is replaced by a PER-PEER seed: peers that ran the same config with the
+    same SEED_VALUE would otherwise walk through the dataset in the same order and average duplicate gradients
+    (the ALBERT trainer seeds its shuffle with the hash of the peer's public key for the same reason)."""
+
+    def __init__(self, num_samples: int, batch_size: int, seed: int):
+        self.num_samples, self.batch_size, self.seed = int(num_samples), int(batch_size), int(seed)
+        self.epoch, self.start_iter = 0, 0
+
+    def set_epoch(self, epoch: int) -> None:
+        self.epoch = int(epoch)
+
+    def set_start_iter(self, start_iter: int) -> None:
+        """Skip the first `start_iter` batches of the epoch (they were consumed before the checkpoint)."""
+        self.start_iter = int(start_iter)
+
+    def __iter__(self):
+        g = torch.Generator().manual_seed(self.seed + self.epoch)
+        order = torch.randperm(self.num_samples, generator=g).tolist()
+        skip = min(self.start_iter * self.batch_size, self.num_samples)
+        self.start_iter = 0          # only the first epoch after a resume is partial
+        return iter(order[skip:])
+
+    def __len__(self):
+        return self.num_samples
+
+
+def peer_shuffle_seed(cfg) -> int:
+    """SEED_VALUE mixed with something only this peer has: DATA.TRAIN.PEER_SHUFFLE_SALT when given (reproducible
+    multi-peer runs), else the process id and the clock."""
+    import hashlib
+    import os
+    import time
+
+    salt = cfg.DATA.TRAIN.get("PEER_SHUFFLE_SALT") if hasattr(cfg.DATA.TRAIN, "get") else None
+    if salt in (None, ""):
+        salt = f"{os.getpid()}-{time.time_ns()}-{os.urandom(4).hex()}"
+    digest = hashlib.sha256(f"{cfg.get('SEED_VALUE', 0)}|{salt}".encode()).digest()
+    return int.from_bytes(digest[:4], "little")
+
+
 class DataloaderAsyncGPUWrapper:
     """Prefetches the next batch to the GPU on a side stream (classy_vision DataloaderAsyncGPUWrapper)."""
 
     def __init__(self, loader, device):
         self.loader, self.device = loader, device
+        self.sampler = getattr(loader, "sampler", None)
         self.stream = torch.cuda.Stream(device) if device.type == "cuda" else None
 
     def _to_device(self, batch):
@@ -192,7 +236,8 @@ def build_dataloader(cfg, device) -> DataloaderAsyncGPUWrapper:
     ds = GenericSSLDataset(cfg)
     tr = cfg.DATA.TRAIN
     collate = multicrop_collator if tr.COLLATE_FUNCTION == "multicrop_collator" else None
-    loader = DataLoader(ds, batch_size=tr.BATCHSIZE_PER_REPLICA, shuffle=True, drop_last=tr.DROP_LAST,
+    sampler = StatefulPeerSampler(len(ds), tr.BATCHSIZE_PER_REPLICA, peer_shuffle_seed(cfg))
+    loader = DataLoader(ds, batch_size=tr.BATCHSIZE_PER_REPLICA, sampler=sampler, drop_last=tr.DROP_LAST,
                         num_workers=cfg.DATA.NUM_DATALOADER_WORKERS, collate_fn=collate,
                         pin_memory=device.type == "cuda", persistent_workers=cfg.DATA.NUM_DATALOADER_WORKERS > 0)
     return DataloaderAsyncGPUWrapper(loader, device)

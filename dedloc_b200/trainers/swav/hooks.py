@@ -1,6 +1,7 @@
 """Hooks of the collaborative SwAV run (everything enabled by W4 through vissl/hooks/__init__.py:72-146):
 
-SwAVUpdateQueueScoresHook, NormalizePrototypesHook (swav_hooks.py:11-92), CheckNanLossHook, FreezeParametersHook
+SwAVUpdateQueueScoresHook, NormalizePrototypesHook (swav_hooks.py:11-92), CheckNanLossHook, SetDataSamplerEpochHook,
+FreezeParametersHook
 (state_update_hooks.py:207-280), UpdateBatchesSeenHook / UpdateTrainIterationNumHook / UpdateTrainBatchTimeHook,
 LogLossLrEtaHook, LogPerfTimeMetricsHook, LogGpuStatsHook, LogGpuMemoryHook, LogLossMetricsCheckpointHook
 (log_hooks.py), SSLTensorboardHook, SSLModelComplexityHook (state_update_hooks.py:16-63), ProfilerHook (ClassyVision). Hook points follow ClassyHook: on_start, on_forward, on_loss_and_meter,
@@ -102,6 +103,28 @@ class UpdateTrainIterationNumHook(ClassyHook):
 class UpdateBatchesSeenHook(ClassyHook):
     def on_forward(self, task):
         task.batches += 1
+
+
+class SetDataSamplerEpochHook(ClassyHook):
+    """New shuffle at the start of every phase (vissl/hooks/state_update_hooks.py SetDataSamplerEpochHook)."""
+
+    def on_phase_start(self, task):
+        sampler = getattr(task.dataloader, "sampler", None)
+        if hasattr(sampler, "set_epoch"):
+            sampler.set_epoch(task.phase_idx)
+
+
+class UpdateTestBatchTimeHook(ClassyHook):
+    """Batch times of evaluation phases (the collaborative recipe has none; kept for recipes that add TEST_MODEL)."""
+
+    def on_start(self, task):
+        task.test_batch_time, self._t = [], time.perf_counter()
+
+    def on_forward(self, task):
+        if not getattr(task, "train", True):
+            now = time.perf_counter()
+            task.test_batch_time.append(now - self._t)
+            self._t = now
 
 
 class UpdateTrainBatchTimeHook(ClassyHook):
@@ -316,7 +339,8 @@ def default_hook_generator(cfg) -> List[ClassyHook]:
     hooks: List[ClassyHook] = []
     if cfg.LOSS.name == "swav_loss":
         hooks += [SwAVUpdateQueueScoresHook(), NormalizePrototypesHook()]
-    hooks += [CheckNanLossHook(), UpdateTrainIterationNumHook(), UpdateBatchesSeenHook(), UpdateTrainBatchTimeHook()]
+    hooks += [CheckNanLossHook(), SetDataSamplerEpochHook(), UpdateTrainIterationNumHook(), UpdateBatchesSeenHook(),
+              UpdateTrainBatchTimeHook(), UpdateTestBatchTimeHook()]
     if cfg.MODEL.TEMP_FROZEN_PARAMS_ITER_MAP:
         hooks.append(FreezeParametersHook(cfg.MODEL.TEMP_FROZEN_PARAMS_ITER_MAP))
     if cfg.HOOKS.PERF_STATS.MONITOR_PERF_STATS:

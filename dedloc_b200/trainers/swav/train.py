@@ -112,6 +112,12 @@ class SelfSupervisionTask:
         self.loss.load_state_dict(state["loss"])
         self.phase_idx = state.get("train_phase_idx", 0)
         self.iteration = state.get("num_updates", 0)
+        # resume in the middle of a phase: skip what was consumed (train_task.py:383-401 does it on the sampler)
+        loader = getattr(self, "dataloader", None)
+        sampler = getattr(loader, "sampler", None)
+        if hasattr(sampler, "set_start_iter") and hasattr(loader, "__len__") and len(loader) > 0:
+            sampler.set_epoch(self.phase_idx)
+            sampler.set_start_iter(self.iteration % len(loader))
 
     def _maybe_resume(self) -> None:
         ck = self.cfg.CHECKPOINT

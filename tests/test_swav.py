@@ -181,3 +181,33 @@ def test_model_complexity_and_profiler_hooks():
     off = [type(h) for h in default_hook_generator(compose(["config=pretrain/swav/swav_1node_resnet_submit",
                                                            "config.HOOKS.TENSORBOARD_SETUP.USE_TENSORBOARD=false"]))]
     assert SSLModelComplexityHook not in off and ProfilerHook not in off
+
+
+def test_stateful_peer_sampler_and_epoch_hook():
+    """Per-peer shuffle (no two peers walk the dataset in the same order), new order every phase, mid-epoch resume."""
+    import types
+
+    from dedloc_b200.trainers.swav.data import StatefulPeerSampler, build_dataloader, peer_shuffle_seed
+    from dedloc_b200.trainers.swav.hooks import SetDataSamplerEpochHook
+
+    s = StatefulPeerSampler(20, batch_size=4, seed=7)
+    first = list(s)
+    assert sorted(first) == list(range(20)) and list(s) == first           # a function of (seed, epoch)
+    s.set_epoch(1)
+    assert list(s) != first
+    s.set_epoch(0)
+    s.set_start_iter(2)
+    assert list(s) == first[8:] and list(s) == first, "only the first epoch after a resume is partial"
+    assert list(StatefulPeerSampler(20, 4, seed=8)) != first
+
+    base = ["config=pretrain/swav/swav_1node_resnet_submit", "config.MACHINE.DEVICE=cpu",
+            "config.DATA.TRAIN.DATA_SOURCES=[synthetic]", "config.DATA.TRAIN.DATA_LIMIT=32",
+            "config.DATA.TRAIN.BATCHSIZE_PER_REPLICA=4", "config.DATA.NUM_DATALOADER_WORKERS=0"]
+    a, b = compose(base + ["config.DATA.TRAIN.PEER_SHUFFLE_SALT=peer-a"]), compose(base + ["config.DATA.TRAIN.PEER_SHUFFLE_SALT=peer-b"])
+    assert peer_shuffle_seed(a) == peer_shuffle_seed(a) != peer_shuffle_seed(b)
+    assert peer_shuffle_seed(compose(base)) != peer_shuffle_seed(compose(base)), "no salt: unique per call / process"
+    loader = build_dataloader(a, torch.device("cpu"))
+    order0 = list(loader.sampler)
+    task = types.SimpleNamespace(dataloader=loader, phase_idx=3)
+    SetDataSamplerEpochHook().on_phase_start(task)
+    assert loader.sampler.epoch == 3 and list(loader.sampler) != order0
