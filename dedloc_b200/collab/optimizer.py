@@ -356,6 +356,10 @@ class CollaborativeOptimizer:
             self.load_state_from_peers()
             if self._needs_resync:
                 return False          # an auxiliary peer with a torn state must not own a shard
+        # heartbeat: an auxiliary peer has no micro-steps to report, but group leaders wait only for peers whose
+        # record is fresh (progress.py liveness_window)
+        if self._reports_progress and get_dht_time() - self.tracker.last_reported_time > min(1.0, self.tracker.liveness_window / 3):
+            self.tracker.report(self.local_step, 0)
         state = self.tracker.refresh_now()
         if not state.ready_for_step or state.num_peers - state.num_aux < 1:
             return False
