@@ -426,7 +426,12 @@ class CollaborativeOptimizer:
                 if not self.expected_group_size_from_tracker:
                     live_now = None
                 # the others finished this step while we were looking for them: nobody is left to form a group with
-                left_behind = lambda: self.tracker.collaboration_state.optimizer_step > self.local_step  # noqa: E731
+                # ... or every other record belongs to a peer that stopped reporting (the last survivor of a fleet
+                # would otherwise wait averaging_expiration in every round until those records expire)
+                def left_behind():
+                    cs = self.tracker.collaboration_state
+                    return cs.optimizer_step > self.local_step or (self.expected_group_size_from_tracker
+                                                                   and 0 <= cs.num_live_peers <= 1)
                 try:
                     with nvtx_range("matchmaking"):
                         group = self.dht.run_coroutine(

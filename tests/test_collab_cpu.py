@@ -404,3 +404,29 @@ def test_dead_peers_record_neither_delays_rounds_nor_splits_the_fleet():
         for d, _, c in peers + ([newcomer] if newcomer else []):
             c.shutdown()
             d.shutdown()
+
+
+def test_last_survivor_does_not_wait_for_ghost_records():
+    """The only live peer of a fleet whose other records are still in the DHT (metadata_expiration 30 s) gives up
+    matchmaking after about a second per round instead of averaging_expiration."""
+    kw = dict(target=8, averaging_expiration=4.0, metadata_expiration=30.0, liveness_window=0.5)
+    first, m0, c0 = make_peer(None, "cfg1solo", **kw)
+    d1, m1, c1 = make_peer(first, "cfg1solo", **kw)
+    log = []
+    try:
+        model_out = m1(**make_batch(1, 0)).loss
+        model_out.backward()
+        c1.step()                               # peer 1 reports once ...
+        c1.tracker.shutdown_flag.set()          # ... and goes silent without withdrawing anything
+        time.sleep(0.7)
+        t0 = time.perf_counter()
+        run_trainer(0, m0, c0, 3, log)
+        dt = time.perf_counter() - t0
+        assert c0.local_step == 3 and c0.stats["solo_rounds"] == 3
+        assert c0.stats["matchmaking_s"] < 3 * 2.0 < 3 * 4.0, c0.stats       # ~1 s per round, not averaging_expiration
+        assert dt < 12.0
+    finally:
+        c1.shutdown()
+        d1.shutdown()
+        c0.shutdown()
+        first.shutdown()
