@@ -128,6 +128,7 @@ class ProgressTracker:
         # live peers, and only they are extrapolated in the ETA.
         self.liveness_window = liveness_window
         self.report_period = 0.0
+        self._last_change: Dict[bytes, tuple] = {}     # peer key -> (record timestamp, local clock when it changed)
         self.lock = threading.Lock()
         self.state_updated = threading.Event()
         self.should_refresh = threading.Event()
@@ -237,8 +238,17 @@ class ProgressTracker:
             if not s.client_mode:
                 global_step = max(global_step, s.step)
         total_samples, estimated_samples, total_sps, num_live = 0, 0.0, 0.0, 0
+        mono = time.monotonic()
+        for key in [k for k in self._last_change if k not in valid]:
+            del self._last_change[key]
         for key, s in valid.items():
-            live = key == self.peer_key or now - s.time <= max(self.liveness_window, 4.0 * s.report_period)
+            # fresh by its own timestamp, or -- for peers whose clock is off by seconds -- seen changing recently
+            seen = self._last_change.get(key)
+            if seen is None or seen[0] != s.time:
+                first_look = seen is None
+                seen = self._last_change[key] = (s.time, mono if not first_look else mono - 1e9)
+            window = max(self.liveness_window, 4.0 * s.report_period)
+            live = key == self.peer_key or now - s.time <= window or mono - seen[1] <= window
             num_live += live
             if live:
                 total_sps += s.samples_per_second

@@ -430,3 +430,36 @@ def test_last_survivor_does_not_wait_for_ghost_records():
         d1.shutdown()
         c0.shutdown()
         first.shutdown()
+
+
+def test_liveness_survives_a_skewed_clock():
+    """A peer whose wall clock is 20 s behind writes 'old' timestamps; it still counts as live while its record keeps
+    changing (observed with the reader's own clock), and stops counting once it stops changing."""
+    from unittest import mock
+
+    from dedloc_b200.collab import progress
+    from dedloc_b200.collab.progress import ProgressTracker
+
+    first = DHT(start=True)
+    second = DHT(start=True, initial_peers=[f"127.0.0.1:{first.port}"])
+    a = ProgressTracker(first, "skew", b"a", 64, endpoint=None, liveness_window=0.4, start=False)
+    b = ProgressTracker(second, "skew", b"b", 64, endpoint=None, liveness_window=0.4, start=False)
+    real = progress.get_dht_time
+    try:
+        a.report(0, 8, update_ema_with=8, wait=True)
+
+        def report_b(samples):
+            with mock.patch.object(progress, "get_dht_time", lambda: real() - 20.0):
+                state = progress.TrainingState(endpoint=None, step=0, samples_accumulated=samples, samples_per_second=1.0,
+                                               time=real() - 20.0, client_mode=False)
+            second.store(b.training_progress_key, state.model_dump(), real() + 30.0, subkey=b"b")
+
+        report_b(8)
+        assert a.fetch_collaboration_state().live_peers == 1, "first look at a stale timestamp: not live yet"
+        report_b(16)
+        assert a.fetch_collaboration_state().live_peers == 2, "the record changed under our eyes"
+        time.sleep(0.6)
+        assert a.fetch_collaboration_state().live_peers == 1, "... and then stopped changing"
+    finally:
+        second.shutdown()
+        first.shutdown()
