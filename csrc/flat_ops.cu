@@ -174,7 +174,8 @@ __global__ void __launch_bounds__(256) encode_chunk_kernel(const float* __restri
       amax = fmaxf(amax, __shfl_xor_sync(0xffffffffu, amax, o));
       bad |= (bool)__shfl_xor_sync(0xffffffffu, (int)bad, o);
     }
-    float s = amax > 0.f ? amax / 448.f : 1.f;
+    // (a block of denormals: amax / 448 underflows to 0 and 1 / 0 would poison the block; FLT_MIN keeps it finite)
+    float s = amax > 0.f ? fmaxf(amax / 448.f, 1.17549435e-38f) : 1.f;
     if (bad) s = __int_as_float(0x7fc00000);  // NaN scale: decoder reproduces a non-finite block
     const float inv = bad ? 0.f : 1.f / s;
     uint32_t lo = 0, hi = 0;

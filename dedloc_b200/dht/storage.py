@@ -78,8 +78,8 @@ class DHTLocalStorage:
         cur = self.data.get(key)
         if subkey is not None:
             if cur is None or not isinstance(cur.value, DictionaryDHTValue):
-                if cur is not None and cur.expiration_time > expiration_time:
-                    return False  # a fresher plain value shadows this dictionary entry
+                if cur is not None and cur.expiration_time >= expiration_time:
+                    return False  # a plain value that is at least as fresh shadows this dictionary entry (ties lose)
                 d = DictionaryDHTValue()
             else:
                 d = cur.value

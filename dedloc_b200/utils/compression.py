@@ -109,7 +109,8 @@ def encode(x: torch.Tensor, codec: CompressionType, scale: float = 1.0) -> Encod
     if codec == CompressionType.BLOCKWISE_FP8:
         xb = x.view(-1, FP8_BLOCK)
         amax = xb.abs().amax(dim=1, keepdim=True)
-        s = torch.where(amax > 0, amax / FP8_MAX, torch.ones_like(amax))
+        # (a block of denormals: amax / 448 underflows to 0 and x / 0 would be inf / NaN; FLT_MIN keeps it finite)
+        s = torch.where(amax > 0, (amax / FP8_MAX).clamp_min(torch.finfo(torch.float32).tiny), torch.ones_like(amax))
         y = (xb / s).to(torch.float8_e4m3fn)
         return Encoded(codec, y.reshape(-1).view(torch.uint8).clone(), s.reshape(-1).contiguous(), n)
     # 8-bit codebook codecs, one codebook per 65536-element block

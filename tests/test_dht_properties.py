@@ -7,10 +7,14 @@ from hypothesis import given, settings, strategies as st
 from dedloc_b200.dht.routing import DHTID, RoutingTable
 from dedloc_b200.dht.storage import DHTLocalStorage
 
+import os
+
 ids = st.integers(min_value=0, max_value=DHTID.MAX - 1)
+# deterministic in CI (same examples every run); HYPOTHESIS_CAMPAIGN=N runs N random examples per test instead
+_N = int(os.environ.get("HYPOTHESIS_CAMPAIGN", "0"))
 
 
-@settings(max_examples=60, deadline=None)
+@settings(max_examples=_N or 60, deadline=None, derandomize=not _N)
 @given(own=ids, nodes=st.lists(ids, min_size=1, max_size=120, unique=True), query=ids, k=st.integers(1, 12))
 def test_routing_table_returns_the_k_nearest_of_what_it_kept(own, nodes, query, k):
     table = RoutingTable(DHTID(own), bucket_size=8)
@@ -31,11 +35,13 @@ def test_routing_table_returns_the_k_nearest_of_what_it_kept(own, nodes, query, 
         assert int(victim) not in {int(nid) for nid, _ in table}
 
 
-@settings(max_examples=80, deadline=None)
+@settings(max_examples=_N or 80, deadline=None, derandomize=not _N)
 @given(ops=st.lists(st.tuples(st.sampled_from([b"k1", b"k2"]), st.sampled_from([None, b"a", b"b"]),
-                              st.integers(0, 50), st.floats(min_value=10.0, max_value=1000.0)), min_size=1, max_size=40))
+                              st.integers(0, 50), st.one_of(st.sampled_from([10.0, 20.0, 30.0]),       # ties on purpose
+                                                            st.floats(min_value=10.0, max_value=1000.0))),
+                    min_size=1, max_size=40))
 def test_local_storage_keeps_the_record_with_the_latest_expiration(ops):
-    now = time.time()
+    now = time.time() + 100.0      # one base for every expiration of the example: equal ttl = equal expiration
     storage = DHTLocalStorage()
     model = {}          # (key, subkey) -> (value, expiration); a plain value and sub-keys exclude each other per key
     for key, subkey, value, ttl in ops:
