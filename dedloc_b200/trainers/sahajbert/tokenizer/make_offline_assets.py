@@ -69,7 +69,8 @@ def write_assets(out_dir: str, n_words: int = 80_000, n_sentences: int = 100_000
                                 out_path=os.path.join(out_dir, "tokenizer.json"), show_progress=show_progress)
     specials = {"bos_token": "[CLS]", "eos_token": "[SEP]", "unk_token": "<unk>", "sep_token": "[SEP]",
                 "pad_token": "<pad>", "cls_token": "[CLS]",
-                "mask_token": {"content": "[MASK]", "single_word": False, "lstrip": False, "rstrip": False,
+                # lstrip: the space in front of [MASK] belongs to it (the shipped reference assets set it the same way)
+                "mask_token": {"content": "[MASK]", "single_word": False, "lstrip": True, "rstrip": False,
                                "normalized": False}}
     with open(os.path.join(out_dir, "special_tokens_map.json"), "w", encoding="utf-8") as f:
         json.dump(specials, f, ensure_ascii=False, indent=1)
