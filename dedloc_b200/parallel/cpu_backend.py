@@ -26,23 +26,43 @@ logger = logging.getLogger(__name__)
 
 
 def load_balance_peers(n_chunks: int, throughputs: Sequence[Optional[float]], min_chunks: int = 0) -> List[int]:
-    """How many chunks each member reduces. The reference solves an LP (scipy linprog) so that the slowest link
-    finishes earliest; its optimum for a star of independent links is the proportional split computed here in
-    closed form. `None` throughput = client mode = 0 chunks. On the uniform NVSwitch fabric this is an equal
-    split among non-client members."""
+    """How many chunks each member reduces (H6). The reference solves a linear program (scipy linprog) that minimises
+    the time of the slowest member; this is the same optimum in closed form. In a butterfly round member i sends
+    its vector minus its own part, then its averaged part to the other P - 1 members (and receives the mirror image),
+    so its link carries N + (P - 2) x_i chunks and it finishes after (N + (P - 2) x_i) / b_i. Minimising the maximum
+    over members with sum x_i = N, x_i >= 0:
+        t* = max( max_i N / b_i ,  N (P - 2 + A) / sum_active b_i ),     x_i proportional to (t* b_i - N) / (P - 2)
+    (A = members that may own a part). The first term is the floor set by the slowest link -- that member then owns
+    nothing; when the second term binds everybody finishes at the same moment. P = 2 is indifferent to the split
+    (P - 2 = 0) and gets the proportional one. `None` throughput = client mode = 0 chunks and unknown link speed.
+    On the uniform NVSwitch fabric this is an equal split among non-client members."""
     tp = np.array([0.0 if t is None else max(float(t), 0.0) for t in throughputs], dtype=np.float64)
     if tp.sum() <= 0:
         raise ValueError("at least one member must be able to reduce (non-client with positive throughput)")
-    ideal = tp / tp.sum() * n_chunks
+    P, N = len(tp), float(n_chunks)
+
+    def solve(tp: np.ndarray) -> np.ndarray:
+        active = tp > 0
+        if P <= 2 or active.sum() == 1 or N <= 0:
+            return tp / tp.sum() * N
+        t_floor = float((N / tp[active]).max())
+        t_even = N * (P - 2 + int(active.sum())) / float(tp[active].sum())
+        t = max(t_floor, t_even)
+        cap = np.where(active, np.maximum(t * tp - N, 0.0) / (P - 2), 0.0)
+        if cap.sum() <= 0:            # every link is exactly at its floor: nothing to choose
+            return tp / tp.sum() * N
+        return cap * (N / cap.sum())
+
+    ideal = solve(tp)
     if min_chunks > 0:  # members whose share would be tiny are not worth a round trip
         small = (ideal < min_chunks) & (tp > 0)
         if small.any() and (~small & (tp > 0)).any():
             tp = np.where(small, 0.0, tp)
-            ideal = tp / tp.sum() * n_chunks
-    counts = np.floor(ideal).astype(np.int64)
+            ideal = solve(tp)
+    counts = np.floor(ideal + 1e-9).astype(np.int64)
     remainder = int(n_chunks - counts.sum())
     order = np.argsort(-(ideal - counts), kind="stable")
-    for i in order[:remainder]:
+    for i in order[:max(remainder, 0)]:
         counts[i] += 1
     return counts.tolist()
 
