@@ -44,7 +44,18 @@ def pack_state(obj: Any, _depth: int = 0) -> Any:
     raise ValueError(f"cannot serialise a {type(obj).__name__} without pickle")
 
 
-def unpack_state(obj: Any, max_tensor_bytes: int = 1 << 34, _depth: int = 0) -> Any:
+def unpack_state(obj: Any, max_tensor_bytes: int = 1 << 34) -> Any:
+    """Rebuild what `pack_state` produced. Whatever the bytes from the network decode to, the outcome is either plain
+    data (scalars, lists, tuples, dicts, tensors of whitelisted dtypes) or a ValueError."""
+    try:
+        return _unpack(obj, max_tensor_bytes, 0)
+    except ValueError:
+        raise
+    except (TypeError, KeyError, IndexError, OverflowError, RuntimeError, AttributeError) as e:
+        raise ValueError(f"malformed state message: {e!r}") from e
+
+
+def _unpack(obj: Any, max_tensor_bytes: int, _depth: int) -> Any:
     if _depth > _MAX_DEPTH:
         raise ValueError("state is nested too deeply")
     if obj is None or isinstance(obj, (bool, int, float, str, bytes)):
@@ -52,8 +63,11 @@ def unpack_state(obj: Any, max_tensor_bytes: int = 1 << 34, _depth: int = 0) -> 
     if isinstance(obj, dict):
         if "__tensor__" in obj:
             name, shape, data = obj["__tensor__"], obj.get("shape"), obj.get("data")
-            if name not in _DTYPES or not isinstance(shape, (list, tuple)) or not isinstance(data, (bytes, bytearray)):
+            if (not isinstance(name, str) or name not in _DTYPES or not isinstance(shape, (list, tuple))
+                    or not isinstance(data, (bytes, bytearray))):
                 raise ValueError("malformed tensor record")
+            if not all(isinstance(s, int) and not isinstance(s, bool) for s in shape):
+                raise ValueError("malformed tensor shape")
             shape = [int(s) for s in shape]
             if any(s < 0 for s in shape) or len(shape) > 8:
                 raise ValueError("malformed tensor shape")
@@ -76,15 +90,15 @@ def unpack_state(obj: Any, max_tensor_bytes: int = 1 << 34, _depth: int = 0) -> 
             for pair in pairs:
                 if not isinstance(pair, (list, tuple)) or len(pair) != 2:
                     raise ValueError("malformed dict record")
-                k = unpack_state(pair[0], max_tensor_bytes, _depth + 1)
+                k = _unpack(pair[0], max_tensor_bytes, _depth + 1)
                 if not isinstance(k, (bool, int, float, str, bytes)):
                     raise ValueError("dict keys must be scalars")
-                out[k] = unpack_state(pair[1], max_tensor_bytes, _depth + 1)
+                out[k] = _unpack(pair[1], max_tensor_bytes, _depth + 1)
             return out
         if "__list__" in obj:
             items = obj["__list__"]
             if not isinstance(items, (list, tuple)):
                 raise ValueError("malformed list record")
-            vals = [unpack_state(v, max_tensor_bytes, _depth + 1) for v in items]
+            vals = [_unpack(v, max_tensor_bytes, _depth + 1) for v in items]
             return tuple(vals) if obj.get("tuple") else vals
     raise ValueError(f"unexpected {type(obj).__name__} in a state message")
