@@ -89,6 +89,8 @@ class _RoundState:
     def add(self, sender: int, decoded: torch.Tensor, weight: float) -> None:
         if sender not in self.remaining:
             raise AllreduceException(f"unexpected part from member {sender}")
+        if decoded.shape != self.acc.shape:      # checked before anything is recorded: the sender may try again
+            raise AllreduceException(f"member {sender} sent {decoded.numel()} elements for a part of {self.acc.numel()}")
         self.remaining.discard(sender)
         self.received[sender] = decoded
         self.acc += decoded * weight

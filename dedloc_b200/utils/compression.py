@@ -175,7 +175,17 @@ def from_bytes(raw: bytes) -> Encoded:
     import msgpack
     import numpy as np
 
-    d = msgpack.unpackb(raw, raw=False)
-    payload = torch.from_numpy(np.frombuffer(d["p"], dtype=np.uint8).copy())
-    aux = torch.from_numpy(np.frombuffer(d["a"], dtype=np.float32).copy()) if d["a"] else None
-    return Encoded(CompressionType(d["c"]), payload, aux, d["n"])
+    # bytes from another peer: every field is checked before anything is allocated from it
+    try:
+        d = msgpack.unpackb(raw, raw=False)
+        codec, n, p, a = CompressionType(d["c"]), d["n"], d["p"], d["a"]
+    except Exception as e:
+        raise ValueError(f"malformed encoded tensor: {e!r}") from e
+    if not isinstance(n, int) or isinstance(n, bool) or n <= 0 or n % CHUNK or not isinstance(p, (bytes, bytearray)) \
+            or not isinstance(a, (bytes, bytearray)):
+        raise ValueError("malformed encoded tensor: bad field types or element count")
+    if len(p) != n * payload_bytes_per_elem(codec) or len(a) != 4 * aux_floats(codec, n):
+        raise ValueError("malformed encoded tensor: payload / side information do not match the element count")
+    payload = torch.from_numpy(np.frombuffer(p, dtype=np.uint8).copy())
+    aux = torch.from_numpy(np.frombuffer(a, dtype=np.float32).copy()) if a else None
+    return Encoded(codec, payload, aux, n)

@@ -110,3 +110,29 @@ def test_flat_layout_pack_views_and_shards(shapes, shares):
             if e > b:
                 assert b == prev
                 prev = e
+
+
+@given(st.sampled_from(list(__import__("dedloc_b200.utils.compression", fromlist=["CompressionType"]).CompressionType)),
+       st.integers(1, 3), st.integers(0, 2 ** 31 - 1), st.lists(st.tuples(st.integers(0, 10 ** 6), st.integers(0, 255)),
+                                                                max_size=6), st.integers(-40, 40))
+@settings(**SETTINGS)
+def test_encoded_tensor_messages_from_the_network(codec, n_chunks, seed, flips, cut):
+    """utils/compression.from_bytes on what a peer may send: a valid message round-trips; a corrupted one either raises
+    ValueError or still describes exactly the number of elements it claims (the reducer then checks that number)."""
+    from dedloc_b200.utils import compression as comp
+
+    x = torch.randn(n_chunks * comp.CHUNK, generator=torch.Generator().manual_seed(seed))
+    raw = comp.to_bytes(comp.encode(x, codec))
+    again = comp.from_bytes(raw)
+    assert again.numel == x.numel() and torch.equal(comp.decode(again), comp.decode(comp.encode(x, codec)))
+    bad = bytearray(raw)
+    for pos, val in flips:
+        bad[pos % len(bad)] = val
+    bad = bytes(bad[:len(bad) + cut]) if cut < 0 else bytes(bad) + bytes(cut)
+    try:
+        enc = comp.from_bytes(bad)
+    except ValueError:
+        return
+    assert enc.numel > 0 and enc.numel % comp.CHUNK == 0
+    assert enc.payload.numel() == enc.numel * comp.payload_bytes_per_elem(enc.codec)
+    assert comp.decode(enc).numel() == enc.numel
