@@ -62,6 +62,10 @@ class RPCServer:
                     req_id, method, payload = await read_frame(reader)
                 except (asyncio.IncompleteReadError, ConnectionError):
                     break
+                except Exception:
+                    # not a frame of ours (garbage bytes, oversized length, wrong arity): drop THIS connection, the
+                    # server and every other connection keep running
+                    break
                 asyncio.ensure_future(self._handle(writer, peer_host, req_id, method, payload))
         finally:
             self._conns.discard(writer)

@@ -175,3 +175,52 @@ def test_frozen_node_is_left_alone_after_its_first_timeout():
 
 async def _add(node, node_id, endpoint):
     node.routing.add_or_update_node(node_id, endpoint)
+
+
+def test_rpc_server_survives_garbage_from_the_network():
+    """Anything may connect to an open collaboration's ports: malformed frames cost the sender its connection and
+    nothing else; malformed payloads of well-formed calls come back as errors."""
+    import asyncio
+    import random
+    import socket
+    import struct
+
+    import msgpack
+
+    node = DHT(start=True)
+    other = DHT(start=True, initial_peers=[f"127.0.0.1:{node.port}"])
+    rng = random.Random(0)
+
+    def frame(obj):
+        raw = msgpack.packb(obj, use_bin_type=True)
+        return struct.pack("!I", len(raw)) + raw
+
+    garbage = [
+        b"GET / HTTP/1.1\r\n\r\n",                                   # somebody's browser
+        struct.pack("!I", 1 << 31) + b"x" * 64,                        # absurd length
+        struct.pack("!I", 16) + bytes(rng.randrange(256) for _ in range(16)),   # not msgpack
+        frame([1, 2]),                                                # wrong arity
+        frame({"a": 1}),                                              # not a list
+        frame([7, ["find"], None]),                                   # unhashable method
+        frame([8, "find", {"keys": "nope"}]),                         # bad payload of a real method
+        frame([9, "store", {"keys": [b"k"], "subkeys": [b"s"], "values": [1.5], "expirations": ["soon"]}]),
+        frame([10, "no_such_method", None]),
+        frame([11, "ping", {"sender": [b"short", "port"]}]),
+        bytes(rng.randrange(256) for _ in range(257)),
+    ]
+    try:
+        for blob in garbage:
+            with socket.create_connection(("127.0.0.1", node.port), timeout=5) as s:
+                s.sendall(blob)
+                s.settimeout(0.3)
+                try:
+                    s.recv(4096)           # an error reply, or nothing, or a close: all fine
+                except (socket.timeout, ConnectionError):
+                    pass
+        # the node still works for well-behaved peers
+        assert other.store("after_garbage", 42, get_dht_time() + 30)
+        assert node.get("after_garbage", latest=True).value == 42
+        assert other.get("after_garbage", latest=True).value == 42
+    finally:
+        other.shutdown()
+        node.shutdown()
