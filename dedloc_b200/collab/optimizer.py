@@ -660,8 +660,31 @@ class CollaborativeOptimizer:
             self.stats["lineage_resyncs"] += 1
         return agreed
 
+    @staticmethod
+    def _check_blobs(blobs: List[Any]) -> None:
+        """Every member's blob came over the network through the group leader. One malformed blob must cost a failed
+        round (the peer steps on its own gradients), not an exception out of step()."""
+        import math
+
+        for i, b in enumerate(blobs):
+            ok = isinstance(b, dict) and b.get("mode") in (MODE_NODE, MODE_CLIENT, MODE_AUX)
+            if ok:
+                w, tp, h = b.get("weight"), b.get("throughput"), b.get("handle")
+                ok = (isinstance(w, (int, float)) and not isinstance(w, bool) and math.isfinite(w) and w >= 0
+                      and (tp is None or (isinstance(tp, (int, float)) and not isinstance(tp, bool)
+                                          and math.isfinite(tp) and tp >= 0))
+                      and isinstance(b.get("step"), int) and b["step"] >= 0
+                      and (h is None or (isinstance(h, (bytes, bytearray)) and len(h) <= 256))
+                      and (b.get("total") is None or (isinstance(b["total"], int) and b["total"] > 0))
+                      and isinstance(b.get("lineage", ""), str) and len(b.get("lineage", "")) <= 128
+                      and isinstance(b.get("lineage_depth", 0) or 0, int)
+                      and isinstance(b.get("n_avg_tensors", 0) or 0, int))
+            if not ok:
+                raise AllreduceException(f"member {i} of the group sent a malformed description of itself")
+
     def _run_group_round(self, group: GroupInfo) -> None:
         blobs = list(group.gathered)
+        self._check_blobs(blobs)
         agreed = self._heal_lineage(group, blobs)
         self._round_lineage = self._mix(agreed, "G", blobs[0].get("step"), *sorted(group.endpoints))
         from .. import lib as native

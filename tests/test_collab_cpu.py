@@ -463,3 +463,17 @@ def test_liveness_survives_a_skewed_clock():
     finally:
         second.shutdown()
         first.shutdown()
+
+
+def test_malformed_member_blob_is_a_failed_round_not_a_crash():
+    from dedloc_b200.collab.matchmaking import AllreduceException
+
+    good = {"weight": 8.0, "mode": 0, "throughput": 1.0, "step": 3, "handle": None, "total": None, "device": None,
+            "lineage": "ab12", "lineage_depth": 3, "host": "h", "n_avg_tensors": 2}
+    CollaborativeOptimizer._check_blobs([good, dict(good, mode=1, throughput=None), dict(good, mode=2, weight=0.0),
+                                         dict(good, handle=b"\\x01" * 64, total=4096, device=0)])
+    for bad in (dict(good, weight="many"), dict(good, weight=float("nan")), dict(good, weight=-1.0), dict(good, mode=7),
+                dict(good, step=-1), dict(good, step="3"), dict(good, handle="not bytes"), dict(good, total=0),
+                dict(good, lineage=["x"]), dict(good, throughput="fast"), "not a dict", None):
+        with pytest.raises(AllreduceException):
+            CollaborativeOptimizer._check_blobs([good, bad])
