@@ -457,6 +457,12 @@ class CollaborativeOptimizer:
                 except AllreduceException as e:
                     self.stats["failed_rounds"] += 1
                     logger.warning("Skipped averaging: averaging round failed with %r", e)
+                except Exception as e:
+                    # hivemind logs and swallows ANY failure of the averaging step (H3 step 6): a round must never take
+                    # the trainer down. What the others did in the meantime shows up as a lineage difference in the
+                    # next group and is healed there.
+                    self.stats["failed_rounds"] += 1
+                    logger.exception("Skipped averaging: averaging round failed with an unexpected %r", e)
             if self._needs_resync:
                 # the round died after it had begun to change this peer's state: neither a local step nor a progress
                 # report makes sense on torn parameters. step() downloads a consistent state before anything else.
