@@ -23,7 +23,8 @@ def _has_main_grads(*params) -> bool:
 
 def embed_supported(emb_module, input_ids: torch.Tensor) -> bool:
     w = emb_module.word_embeddings.weight
-    return (input_ids.is_cuda and w.dtype == torch.bfloat16 and w.shape[1] == 128 and native.available()
+    return (input_ids.is_cuda and input_ids.dtype == torch.int64 and input_ids.dim() == 2
+            and w.dtype == torch.bfloat16 and w.shape[1] == 128 and native.available()
             and _has_main_grads(w, emb_module.position_embeddings.weight, emb_module.token_type_embeddings.weight,
                                 emb_module.LayerNorm.weight, emb_module.LayerNorm.bias))
 
@@ -33,6 +34,10 @@ class _EmbedLNFn(torch.autograd.Function):
     def forward(ctx, ids, tts, word, pos, typ, gamma, beta, eps, pad_id, grads):
         B, S = ids.shape
         M, E = B * S, word.shape[1]
+        if S > pos.shape[0]:
+            raise ValueError(f"sequence length {S} exceeds the {pos.shape[0]} position embeddings")
+        if tts.shape != ids.shape:
+            raise ValueError("input_ids and token_type_ids must have one shape")
         ids1 = ids.reshape(-1).contiguous()
         tts1 = tts.reshape(-1).contiguous()
         y = torch.empty(M, E, dtype=torch.bfloat16, device=ids.device)
@@ -71,6 +76,8 @@ def embed_layer_norm(emb_module, input_ids: torch.Tensor, token_type_ids: torch.
     ln = emb_module.LayerNorm
     pad = emb_module.word_embeddings.padding_idx
     grads = (w.main_grad, p.main_grad, t.main_grad, ln.weight.main_grad, ln.bias.main_grad)
+    if token_type_ids.dtype != torch.int64 or token_type_ids.shape != input_ids.shape:      # the kernel reads int64
+        token_type_ids = token_type_ids.to(torch.int64).expand_as(input_ids)
     # the output must require grad so that autograd calls backward: hang it on the word table
     return _EmbedLNFn.apply(input_ids, token_type_ids, w, p, t, ln.weight, ln.bias, ln.eps,
                             -1 if pad is None else pad, grads)
