@@ -190,6 +190,24 @@ def write_report(args, events, t0, coord_log):
         (ta, sa), (tb, sb) = window[0], window[-1]
         report.update(window_s=round(tb - ta, 1), collaborative_steps_in_window=sb - sa,
                       samples_per_second=round((sb - sa) * args.target_batch_size / max(tb - ta, 1e-9), 1))
+    # the same figure from the trainers' own per-round lines (1 s stamps instead of the coordinator's polling period):
+    # a collaborative step counts when the FIRST trainer reports it
+    first_seen = {}
+    for i in range(args.trainers):
+        path = os.path.join(args.log_dir, f"trainer_{i}.log")
+        if not os.path.exists(path):
+            continue
+        for line in open(path, errors="replace"):
+            m = re.search(r"collaborative step (\d+) done", line)
+            ts = _stamp(line)
+            if m and ts is not None:
+                step = int(m.group(1))
+                first_seen[step] = min(first_seen.get(step, ts), ts)
+    in_window = sorted((ts - t0, step) for step, ts in first_seen.items() if ts - t0 >= args.measure_after)
+    if len(in_window) >= 2:
+        (ta, sa), (tb, sb) = in_window[0], in_window[-1]
+        report.update(trainer_log_window_s=round(tb - ta, 1), trainer_log_steps=sb - sa,
+                      samples_per_second_from_trainer_logs=round((sb - sa) * args.target_batch_size / max(tb - ta, 1e-9), 1))
     per_trainer = {}
     rejoin = []
     for i in range(args.trainers):
