@@ -12,7 +12,7 @@ import sys
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 LIB = os.path.join(ROOT, "dedloc_b200", "lib", "libdedloc_b200.so")
 OUT = os.path.join(ROOT, "profiles", "sass")
-KEY = re.compile(r"UTCHMMA|UTMALDG|UTMASTG|UTMAPF|LDTM|STTM|UTCBAR|UTCCP|SYNCS|UCGABAR|MUFU|REDG|RED\.|ATOMG|LDG\.E\.128|STG\.E\.128|LD\.E\.128")
+KEY = re.compile(r"LDGMC|MULTIMEM|\.MC|MEMBAR|FENCE|ERRBAR|CCTL|UTCHMMA|UTMALDG|UTMASTG|UTMAPF|LDTM|STTM|UTCBAR|UTCCP|SYNCS|UCGABAR|MUFU|REDG|RED\.|ATOMG|LDG\.E\.128|STG\.E\.128|LD\.E\.128")
 
 
 def demangle(name: str) -> str:
