@@ -83,6 +83,28 @@ class Matchmaking:
 
         return max(0, math.ceil(math.log2(num_peers / self.target_group_size)))
 
+    def assign_group_bits(self, live_keys, my_key: bytes, round_salt: int) -> Optional[str]:
+        """Balanced buckets: order the live peers by hash(key, round) -- every peer that sees the same records computes
+        the same order -- and cut the order into 2^bits consecutive blocks. Against hash(group id) -> bucket (random
+        occupancy: with 8 peers and groups of 4 a bucket of 5 leaves one peer without a group every other round) the
+        blocks differ by at most one peer, and the salt reshuffles them every round, which is what merges the work of
+        different groups over time. Returns None when this peer cannot place itself (its own record is not among the
+        live ones yet): the caller falls back to `rederive_group_bits`."""
+        import hashlib
+
+        keys = list(live_keys)
+        nbits = self.num_group_bits(len(keys))
+        if nbits == 0:
+            self.group_bits = ""
+            return self.group_bits
+        if my_key not in keys:
+            return None
+        salt = int(round_salt).to_bytes(8, "little", signed=True)
+        order = sorted(keys, key=lambda k: hashlib.sha256(salt + k).digest())
+        bucket = order.index(my_key) * (1 << nbits) // len(order)
+        self.group_bits = format(bucket, f"0{nbits}b")
+        return self.group_bits
+
     def rederive_group_bits(self, group: Optional["GroupInfo"], num_peers: Optional[int]) -> str:
         """After a round, every member moves to a bucket chosen by hash(group id, its index in the group): members of
         one group scatter over the buckets, so the next round mixes different peers (hivemind re-derives the bits from

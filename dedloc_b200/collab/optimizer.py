@@ -412,6 +412,10 @@ class CollaborativeOptimizer:
             self._params_parked = True
             group: Optional[GroupInfo] = None
             if state.num_peers > 1:  # num_peers counts this peer's own progress record too
+                # more live peers than target_group_size: balanced, per-round reshuffled buckets from the records that
+                # everybody reads (falls back to the bits derived from the last group when we are not in them yet)
+                self._balanced_bits = (state.live_keys and self._matchmaking.assign_group_bits(
+                    state.live_keys, bytes(self.peer_key), self.local_step) is not None)
                 # wait for the peers that are still reporting, not for the records dead peers left behind
                 # ... and, when the collaboration is split into buckets, for this bucket's share of them
                 buckets = 1 << len(self._matchmaking.group_bits)
@@ -447,7 +451,8 @@ class CollaborativeOptimizer:
                                 "group": group.group_size if group is not None else 0, "matchmaking_s": t1 - t0}
             # next round's bucket: members of one group scatter, so large collaborations reshuffle every round
             # (counted over live peers: the record of a dead peer must not push the collaboration over target_group_size)
-            self._matchmaking.rederive_group_bits(group, state.live_peers)
+            if not getattr(self, "_balanced_bits", False):
+                self._matchmaking.rederive_group_bits(group, state.live_peers)
             averaged = False
             if group is not None and group.group_size > 1:
                 try:

@@ -48,6 +48,7 @@ class CollaborationState:
     next_fetch_time: float
     num_aux: int = 0
     num_live_peers: int = -1   # peers whose record is fresh (see ProgressTracker.liveness_window); -1 = not computed
+    live_keys: tuple = ()      # their record keys, sorted (every peer that reads the same records gets the same tuple)
 
     @property
     def live_peers(self) -> int:
@@ -66,7 +67,7 @@ class CollaborationState:
     def register_step(self, local_step: int) -> "CollaborationState":
         return CollaborationState(max(local_step, self.optimizer_step), 0, self.target_batch_size, self.num_peers,
                                   self.num_clients, float("inf"), self.next_fetch_time, self.num_aux,
-                                  self.num_live_peers)
+                                  self.num_live_peers, self.live_keys)
 
 
 class PerformanceEMA:
@@ -239,6 +240,7 @@ class ProgressTracker:
                 global_step = max(global_step, s.step)
         total_samples, estimated_samples, total_sps, num_live = 0, 0.0, 0.0, 0
         mono = time.monotonic()
+        live_keys: list = []
         for key in [k for k in self._last_change if k not in valid]:
             del self._last_change[key]
         for key, s in valid.items():
@@ -250,6 +252,8 @@ class ProgressTracker:
             window = max(self.liveness_window, 4.0 * s.report_period)
             live = key == self.peer_key or now - s.time <= window or mono - seen[1] <= window
             num_live += live
+            if live:
+                live_keys.append(bytes(key) if isinstance(key, (bytes, bytearray)) else str(key).encode())
             if live:
                 total_sps += s.samples_per_second
             if s.step == global_step:
@@ -264,4 +268,4 @@ class ProgressTracker:
                                            self.min_refresh_period, self.max_refresh_period))
         return CollaborationState(global_step, total_samples, self.target_batch_size, num_peers, num_clients,
                                   eta_next_step=now + eta_seconds, next_fetch_time=now + time_to_next_fetch,
-                                  num_aux=num_aux, num_live_peers=num_live)
+                                  num_aux=num_aux, num_live_peers=num_live, live_keys=tuple(sorted(live_keys)))

@@ -477,3 +477,50 @@ def test_malformed_member_blob_is_a_failed_round_not_a_crash():
                 dict(good, lineage=["x"]), dict(good, throughput="fast"), "not a dict", None):
         with pytest.raises(AllreduceException):
             CollaborativeOptimizer._check_blobs([good, bad])
+
+
+def test_eight_peers_in_balanced_groups_of_four():
+    """More peers than target_group_size (swav/README.md:26 runs groups of 4): buckets come from the live records
+    (Matchmaking.assign_group_bits), so every round has two full groups, the salt reshuffles them, parameter averaging
+    merges their work and nobody's step is replaced by a state copy."""
+    from dedloc_b200.collab.matchmaking import Matchmaking
+
+    # the assignment itself: blocks differ by at most one peer, every peer computes the same split, rounds differ
+    keys = [bytes([i]) * 4 for i in range(11)]
+    mm = Matchmaking.__new__(Matchmaking)
+    mm.target_group_size, mm.group_bits = 4, ""
+    splits = []
+    for salt in range(6):
+        buckets = {}
+        for k in keys:
+            buckets.setdefault(mm.assign_group_bits(keys, k, salt), []).append(k)
+        sizes = sorted(len(v) for v in buckets.values())
+        assert len(buckets) == 4 and sizes[-1] - sizes[0] <= 1, sizes           # 11 peers -> 3, 3, 3, 2
+        splits.append(tuple(sorted(tuple(v) for v in buckets.values())))
+    assert len(set(splits)) > 1, "the salt must reshuffle the buckets"
+    assert mm.assign_group_bits(keys[:4], keys[0], 0) == "" and mm.assign_group_bits(keys, b"stranger", 0) is None
+
+    kw = dict(target=64, target_group_size=4, averaging_expiration=3.0, metadata_expiration=30.0)
+    first, m0, c0 = make_peer(None, "cfg1e8", **kw)
+    peers = [(first, m0, c0)] + [make_peer(first, "cfg1e8", **kw) for _ in range(7)]
+    n_rounds, log = 6, []
+    sizes = {i: [] for i in range(8)}
+    for i, (_, _, c) in enumerate(peers):
+        def wrap(orig=c._finish_global_step, c=c, i=i):
+            sizes[i].append((getattr(c, "_last_round", None) or {}).get("group", 0))
+            return orig()
+        c._finish_global_step = wrap
+    threads = [threading.Thread(target=run_trainer, args=(i, m, c, n_rounds, log)) for i, (_, m, c) in enumerate(peers)]
+    try:
+        [t.start() for t in threads]
+        [t.join(timeout=300) for t in threads]
+        assert all(c.local_step == n_rounds for _, _, c in peers), [c.local_step for _, _, c in peers]
+        flat = [s for v in sizes.values() for s in v]
+        assert sum(s == 4 for s in flat) >= 0.85 * len(flat), sizes          # a starved CI box may cost a round or two
+        copies = sum(c.stats["lineage_resyncs"] + c.stats["state_downloads"] for _, _, c in peers)
+        assert copies <= 1, [c.stats for _, _, c in peers]
+        assert sum(c.stats.get("parameter_averagings", 0) for _, _, c in peers) >= 8
+    finally:
+        for d, _, c in peers:
+            c.shutdown()
+            d.shutdown()
