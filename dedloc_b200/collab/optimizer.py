@@ -411,7 +411,8 @@ class CollaborativeOptimizer:
         with self.performance_ema.pause(), self.state_lock:
             self._params_parked = True
             group: Optional[GroupInfo] = None
-            if state.num_peers > 1:  # num_peers counts this peer's own progress record too
+            alone = self.expected_group_size_from_tracker and 0 <= state.num_live_peers <= 1
+            if state.num_peers > 1 and not alone:  # num_peers counts this peer's own progress record too
                 # more live peers than target_group_size: balanced, per-round reshuffled buckets from the records that
                 # everybody reads (falls back to the bits derived from the last group when we are not in them yet)
                 self._balanced_bits = (state.live_keys and self._matchmaking.assign_group_bits(
