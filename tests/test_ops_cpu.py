@@ -92,3 +92,33 @@ def test_ops_fall_back_to_pytorch_on_cpu():
     x = torch.randn(4, 256, generator=g)
     assert torch.allclose(layer_norm(x, ln), ln(x))
     assert not attention_supported(torch.zeros(1, 128, 3 * 2 * 64, dtype=torch.bfloat16), 2)   # CPU tensor
+
+
+def test_public_api_surface_of_the_reference_is_importable():
+    """every symbol the reference's scripts import from hivemind has a counterpart with the same call
+    shape (constructor keywords, method names, attributes)."""
+    import inspect
+
+    from dedloc_b200 import DHT, CollaborativeOptimizer, CompressionType, get_dht_time
+    from dedloc_b200.collab.auth import AccessToken, TokenAuthorizerBase  # noqa: F401
+    from dedloc_b200.dht import BytesWithPublicKey, RecordValidatorBase, RSASignatureValidator, SchemaValidator  # noqa: F401
+    from dedloc_b200.dht.validation import RSAPrivateKey, RSAPublicKey  # noqa: F401
+    from dedloc_b200.p2p import P2P  # noqa: F401
+    from dedloc_b200.utils.logging import get_logger
+
+    dht_kw = inspect.signature(DHT.__init__).parameters
+    assert all(k in dht_kw for k in ("start", "initial_peers", "listen", "listen_on", "endpoint", "record_validators"))
+    assert {"key", "value", "expiration_time", "subkey", "return_future"} <= set(inspect.signature(DHT.store).parameters)
+    assert {"key", "latest"} <= set(inspect.signature(DHT.get).parameters)
+    opt_kw = inspect.signature(CollaborativeOptimizer.__init__).parameters
+    for k in ("opt", "dht", "prefix", "target_batch_size", "batch_size_per_step", "scheduler", "compression_type",
+              "compression", "throughput", "bandwidth", "client_mode", "auxiliary", "allow_state_sharing", "verbose", "start",
+              "averaging_expiration", "averaging_timeout", "metadata_expiration", "target_group_size",
+              "min_refresh_period", "max_refresh_period", "default_refresh_period", "expected_drift_peers",
+              "expected_drift_rate", "performance_ema_alpha", "listen_on"):
+        assert k in opt_kw, k
+    for attr in ("step", "zero_grad", "step_aux", "load_state_from_peers", "state_dict", "load_state_dict",
+                 "is_synchronized", "collaboration_state", "shutdown"):
+        assert hasattr(CollaborativeOptimizer, attr), attr
+    assert [CompressionType.Value(n) for n in ("NONE", "FLOAT16", "MEANSTD_16BIT", "UNIFORM_8BIT", "QUANTILE_8BIT")]
+    assert get_dht_time() > 0 and get_logger("dedloc.test") is get_logger("dedloc.test")
