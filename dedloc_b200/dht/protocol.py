@@ -15,6 +15,9 @@ import msgpack
 
 _LEN = struct.Struct("!I")
 MAX_FRAME = 1 << 30
+# DEDLOC_EMULATED_RTT_MS: add that much latency to every outgoing RPC (DHT, matchmaking, socket rounds) -- the
+# counterpart of the link shaping in parallel/cpu_backend.py for studying the protocol under internet round-trip times
+_EMULATED_RTT_S = float(__import__("os").environ.get("DEDLOC_EMULATED_RTT_MS", "0") or 0) / 1e3
 
 
 async def read_frame(reader: asyncio.StreamReader) -> Any:
@@ -156,6 +159,8 @@ class RPCClient:
                 host, port = split_endpoint(endpoint)
                 reader, writer = await asyncio.wait_for(asyncio.open_connection(host, port), self.connect_timeout)
                 conn = self._conns[endpoint] = _Connection(reader, writer)
+        if _EMULATED_RTT_S > 0:      # experiments on one machine: every call pays a network round trip
+            await asyncio.sleep(_EMULATED_RTT_S)
         return await conn.call(method, payload, timeout)
 
     async def shutdown(self) -> None:
