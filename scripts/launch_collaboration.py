@@ -51,6 +51,8 @@ def main():
                          "100,100,100,100,100,100,100,100,50,50,50,50): sets --bandwidth (load balancing) and "
                          "--emulated_uplink_mbps (pacing of the socket all-reduce) of each trainer; --aux_uplink for aux peers")
     ap.add_argument("--aux_uplink", type=float, default=0.0)
+    ap.add_argument("--rtt_ms", type=float, default=0.0,
+                    help="every RPC of every process waits this long first (DEDLOC_EMULATED_RTT_MS): internet round trips")
     ap.add_argument("--run_for", type=float, default=0, help="seconds; 0 = until interrupted")
     ap.add_argument("--kill_every", type=float, default=0)
     ap.add_argument("--pause_every", type=float, default=0)
@@ -60,6 +62,8 @@ def main():
     ap.add_argument("--fleet_report", default="", help="write the elasticity report here when the run ends")
     ap.add_argument("--measure_after", type=float, default=60.0, help="seconds of start-up excluded from the report")
     args, passthrough = ap.parse_known_args()
+    if args.rtt_ms > 0:
+        os.environ["DEDLOC_EMULATED_RTT_MS"] = str(args.rtt_ms)      # inherited by everything spawn() starts
     os.makedirs(args.log_dir, exist_ok=True)
     pkg = f"dedloc_b200.trainers.{args.family}"
 
