@@ -84,12 +84,15 @@ class Matchmaking:
         return max(0, math.ceil(math.log2(num_peers / self.target_group_size)))
 
     def assign_group_bits(self, live_keys, my_key: bytes, round_salt: int) -> Optional[str]:
-        """Balanced buckets: order the live peers by hash(key, round) -- every peer that sees the same records computes
-        the same order -- and cut the order into 2^bits consecutive blocks. Against hash(group id) -> bucket (random
-        occupancy: with 8 peers and groups of 4 a bucket of 5 leaves one peer without a group every other round) the
-        blocks differ by at most one peer, and the salt reshuffles them every round, which is what merges the work of
-        different groups over time. Returns None when this peer cannot place itself (its own record is not among the
-        live ones yet): the caller falls back to `rederive_group_bits`."""
+        """Balanced buckets that are guaranteed to change every round: put the live peers in a fixed order (by the
+        hash of their record key -- every peer that sees the same records computes the same order), keep the first one
+        in place and rotate the others by `round * stride` (the circle method of round-robin tournaments), then cut the
+        row into 2^bits consecutive blocks. Blocks differ by at most one peer; two consecutive rounds never have the
+        same blocks, so the work of different groups is merged (parameter averaging) from one round to the next, and
+        over n - 1 rounds everybody has been grouped with everybody. Against hash(group id) -> bucket (hivemind's
+        scheme: random occupancy -- with 8 peers and groups of 4 a bucket of 5 leaves one peer without a group every
+        other round -- and random repetition of the same groups). Returns None when this peer cannot place itself (its
+        own record is not among the live ones yet): the caller falls back to `rederive_group_bits`."""
         import hashlib
 
         keys = list(live_keys)
@@ -99,9 +102,14 @@ class Matchmaking:
             return self.group_bits
         if my_key not in keys:
             return None
-        salt = int(round_salt).to_bytes(8, "little", signed=True)
-        order = sorted(keys, key=lambda k: hashlib.sha256(salt + k).digest())
-        bucket = order.index(my_key) * (1 << nbits) // len(order)
+        order = sorted(keys, key=lambda k: hashlib.sha256(k).digest())
+        rest = order[1:]
+        stride = max(1, len(keys) // (1 << nbits) // 2)        # half a block moves per round
+        if stride % len(rest) == 0:
+            stride = 1
+        shift = (int(round_salt) * stride) % len(rest)
+        row = [order[0]] + rest[shift:] + rest[:shift]
+        bucket = row.index(my_key) * (1 << nbits) // len(row)
         self.group_bits = format(bucket, f"0{nbits}b")
         return self.group_bits
 

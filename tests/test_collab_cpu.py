@@ -498,15 +498,25 @@ def test_eight_peers_in_balanced_groups_of_four():
     keys = [bytes([i]) * 4 for i in range(11)]
     mm = Matchmaking.__new__(Matchmaking)
     mm.target_group_size, mm.group_bits = 4, ""
-    splits = []
-    for salt in range(6):
+    def split(keys, step):
         buckets = {}
         for k in keys:
-            buckets.setdefault(mm.assign_group_bits(keys, k, salt), []).append(k)
+            buckets.setdefault(mm.assign_group_bits(keys, k, step), []).append(k)
+        return buckets
+
+    splits = []
+    for step in range(12):
+        buckets = split(keys, step)
         sizes = sorted(len(v) for v in buckets.values())
         assert len(buckets) == 4 and sizes[-1] - sizes[0] <= 1, sizes           # 11 peers -> 3, 3, 3, 2
-        splits.append(tuple(sorted(tuple(v) for v in buckets.values())))
-    assert len(set(splits)) > 1, "the salt must reshuffle the buckets"
+        splits.append(frozenset(frozenset(v) for v in buckets.values()))
+    assert all(a != b for a, b in zip(splits, splits[1:])), "two consecutive rounds must never have the same groups"
+    # four peers in pairs: the three possible pairings come round in turn, so everybody meets everybody in 3 rounds
+    four = keys[:4]
+    mm.target_group_size = 2
+    pairings = [frozenset(frozenset(v) for v in split(four, step).values()) for step in range(3)]
+    assert len(set(pairings)) == 3 and all(len(b) == 2 for p in pairings for b in p)
+    mm.target_group_size = 4
     assert mm.assign_group_bits(keys[:4], keys[0], 0) == "" and mm.assign_group_bits(keys, b"stranger", 0) is None
 
     kw = dict(target=64, target_group_size=4, averaging_expiration=3.0, metadata_expiration=30.0)
